@@ -1,0 +1,176 @@
+/*
+ * ssn.h — C ABI of the B200 tumor/normal pileup-column scorer (libssn.so).
+ *
+ * The reference (genome/somatic-sniper) has no plugin/FFI layer: its hot path sits behind the
+ * in-process per-column callback
+ *
+ *     typedef int (*bam_sspileup_f)(uint32_t tid, uint32_t pos, int n1, int n2,
+ *                                   const bam_pileup1_t *pl1, const bam_pileup1_t *pl2,
+ *                                   void *data, FILE *snp_fh);          -- src/lib/sniper/somatic_sniper.h:42
+ *
+ * installed at src/exe/bam-somaticsniper/main.c:146 (glf_somatic) and invoked once per column at
+ * src/lib/sniper/sniper_pileup.c:258.  This library replaces that callback at BATCH granularity:
+ * the host packer writes both samples' columns as structure-of-arrays batches into pinned memory,
+ * submits them, and drains `ssn_site` records (one per site that glf_somatic would have handed to
+ * output_formatter_write, somatic_sniper.c:264) in column order.
+ *
+ * Plain C types only; no CUDA or torch types appear in any signature.  All functions return
+ * SSN_OK (0) or a negative ssn_status; ssn_last_error() gives the message of the calling thread's
+ * last failure.  The library never exits the process and has NO CPU fallback: without a usable
+ * CUDA device ssn_create() fails with SSN_ERR_CUDA.
+ *
+ * Threading: one ssn_ctx per GPU; one submitting thread per ctx (the reference's callback is
+ * single-threaded and non-reentrant, somatic_sniper.c:13-16).
+ */
+#ifndef SSN_H
+#define SSN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSN_ABI_VERSION 1
+
+typedef enum {
+    SSN_OK = 0,
+    SSN_ERR_ARG = -1,      /* bad argument / batch contents */
+    SSN_ERR_CUDA = -2,     /* CUDA runtime failure (fatal for the ctx) */
+    SSN_ERR_NOMEM = -3,
+    SSN_ERR_STATE = -4,    /* call out of order (e.g. results_next with nothing submitted) */
+    SSN_ERR_OVERFLOW = -5  /* more passing sites than the batch's site ring holds */
+} ssn_status;
+
+/* Every knob of pu_data2_t (somatic_sniper.h:21-40) and sniper_maqcns_t (sniper_maqcns.h:13-21)
+ * that affects scoring.  Defaults: main.c:69-78 and sniper_maqcns_init (sniper_maqcns.c:102-113). */
+typedef struct {
+    float theta;                  /* -T, 0.85  (float field in the reference) */
+    float het_rate;               /* -r, 0.001 (float field) */
+    float eta;                    /* 0.03, not settable from the reference CLI */
+    int32_t n_hap;                /* -N, 2 */
+    int32_t cap_mapq;             /* 60 */
+    int32_t min_somatic_qual;     /* -Q, 15 */
+    int32_t include_loh;          /* 1; -L clears */
+    int32_t include_gor;          /* 1; -G clears */
+    int32_t use_priors;           /* 1; -p clears (prior[][] stays all zero, main.c:122-125) */
+    int32_t use_joint_priors;     /* 0; -J / -s set */
+    double somatic_mutation_rate; /* -s, 0.01 */
+} ssn_params;
+
+/* Host views of the model tables the ctx built (for parity checks against the reference's
+ * sniper_cal_coef / sniper_cal_het / makeSoloPrior / make_joint_prior / qAddTableInit). */
+typedef struct {
+    const double *coef;        /* [q<<16 | n<<8 | k], 64*256*256   sniper_maqcns.c:59-100 */
+    const double *lhet;        /* [n1<<8 | n2], 256*256             sniper_maqcns.c:27-53  */
+    const double *fk;          /* 256                               sniper_maqcns.c:70-74  */
+    float q_r;                 /*                                   sniper_maqcns.c:54-55  */
+    const int32_t *prior;      /* [16][10]                          somatic_sniper.c:29-45 */
+    const int32_t *jointprior; /* [16][10][10]                      somatic_sniper.c:47-77 */
+    const int32_t *qadd;       /* [1024]                            somatic_sniper.c:101-107 */
+} ssn_tables;
+
+/* Per-sample part of a site: sample_data_t + dqstats_t (output_format.h:13-23, dqstats.h:14-27).
+ * rms_mapq is the RMS mapping quality packed in the consensus word (sniper_maqcns.c:176,268),
+ * computed by the reference but never printed. */
+typedef struct {
+    int32_t genotype;                 /* independent consensus genotype, 4-bit allele mask */
+    int32_t joint_genotype;           /* 0 unless -J */
+    int32_t joint_consensus_quality;
+    int32_t consensus_quality;
+    int32_t variant_allele_quality;
+    int32_t somatic_score;            /* -1 for the normal sample */
+    int32_t variant_status;           /* variant_status_t, allele_util.h:16-22 */
+    uint32_t mean_baseQ[4];
+    uint32_t mean_mapQ[4];
+    uint32_t base_occ[4];
+    uint32_t dp4[4];
+    uint32_t total_depth;
+    uint32_t total_mean_mapQ;
+    int32_t rms_mapq;
+} ssn_sample;
+
+/* One passing site = one sniper_output_t (output_format.h:25-35) minus the strings. */
+typedef struct {
+    uint32_t column;     /* column index inside the batch */
+    int32_t ref_base4;   /* bam_nt16_table[ref char] */
+    ssn_sample tumor;
+    ssn_sample normal;
+} ssn_site;
+
+/* Optional per-column dump (SSN_SUBMIT_COLUMN_DUMP): both samples' quantised GLFs and the
+ * value glf_somatic returns (somatic_sniper.c:268-272). 29 uint32 per column:
+ *   [0..9] tumor lk, [10] min_lk, [11] rms mapQ, [12] depth, [13] consensus word,
+ *   [14..27] the same for the normal sample, [28] (int32) return value. */
+#define SSN_COLUMN_DUMP_WORDS 29
+
+/* Pinned host arrays of one batch, filled by the packer.  Column c owns entries
+ * off[2c]..off[2c+1] (tumor) and off[2c+1]..off[2c+2] (normal) of bs/bq/mq.  Deleted bases and
+ * reads rejected by the flag/mapQ filter are not entries (sniper_maqcns.c:147, sniper_pileup.c:208). */
+typedef struct {
+    uint32_t *off;       /* 2*max_columns+1 */
+    uint8_t *bs;         /* nt16 base code | strand<<4 */
+    uint8_t *bq;         /* base quality */
+    uint8_t *mq;         /* mapping quality */
+    uint8_t *ref_nt16;   /* bam_nt16_table[reference char] per column; 15 => no call (somatic_sniper.c:127,156) */
+    uint32_t max_columns;
+    uint64_t max_entries;
+} ssn_batch_view;
+
+typedef struct ssn_ctx ssn_ctx;
+typedef struct ssn_batch ssn_batch;
+
+#define SSN_SUBMIT_COLUMN_DUMP 1u  /* also produce the per-column dump (parity tests) */
+
+int ssn_abi_version(void);
+const char *ssn_last_error(void);
+ssn_status ssn_params_default(ssn_params *p);
+
+/* Builds the model tables on the host (x87 long double where the reference uses it), uploads them,
+ * pins coef+lhet in L2 with a persisting access-policy window, creates `n_slots` batch slots of the
+ * given capacity (pinned host + device buffers, one stream each). */
+ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slots, uint32_t max_columns,
+                      uint64_t max_entries, ssn_ctx **out);
+void ssn_destroy(ssn_ctx *ctx);
+ssn_status ssn_get_tables(const ssn_ctx *ctx, ssn_tables *out);
+/* The same tables without a device (host-only; used by parity tests and by tools that only need the
+ * model): *handle owns the memory behind *view until ssn_host_tables_destroy. */
+ssn_status ssn_host_tables_create(const ssn_params *p, ssn_tables *view, void **handle);
+void ssn_host_tables_destroy(void *handle);
+/* bam_nt16_table[ch] (samtools-0.1.6 bam_import.c:23-40): reference character -> ref_nt16 */
+int ssn_nt16_of_char(int ch);
+
+/* Slot ring: acquire a free batch (blocks on the oldest in-flight one only if none is free and
+ * its results were already drained), fill the view, set its size, submit. */
+ssn_status ssn_batch_acquire(ssn_ctx *ctx, ssn_batch **out);
+ssn_status ssn_batch_view_get(ssn_batch *b, ssn_batch_view *out);
+ssn_status ssn_batch_set_size(ssn_batch *b, uint32_t n_columns, uint64_t n_entries);
+/* Asynchronous: H2D copy of the batch, the scoring kernel, D2H copy of the site ring. */
+ssn_status ssn_batch_submit(ssn_ctx *ctx, ssn_batch *b, uint32_t flags);
+/* Blocks until the OLDEST submitted batch is done; returns its sites sorted by column.  The
+ * pointers stay valid until that batch is acquired again.  *batch (optional) receives the batch. */
+ssn_status ssn_results_next(ssn_ctx *ctx, const ssn_site **sites, uint32_t *n_sites, ssn_batch **batch);
+/* Per-column dump of a finished batch that was submitted with SSN_SUBMIT_COLUMN_DUMP. */
+ssn_status ssn_batch_column_dump(ssn_batch *b, const uint32_t **words);
+ssn_status ssn_batch_release(ssn_ctx *ctx, ssn_batch *b);
+
+/* Device-resident path (kernel-only measurement): upload once, score many times. */
+ssn_status ssn_batch_upload(ssn_ctx *ctx, ssn_batch *b);                 /* H2D + sync */
+ssn_status ssn_batch_score_resident(ssn_ctx *ctx, ssn_batch *b, uint32_t flags); /* kernel only, async */
+ssn_status ssn_batch_fetch(ssn_ctx *ctx, ssn_batch *b, const ssn_site **sites, uint32_t *n_sites); /* D2H + sync */
+
+/* Device-side timing across all of the ctx's streams (CUDA events), and launch accounting. */
+ssn_status ssn_timer_start(ssn_ctx *ctx);
+ssn_status ssn_timer_stop(ssn_ctx *ctx, float *elapsed_ms);
+ssn_status ssn_sync(ssn_ctx *ctx);
+uint64_t ssn_kernel_launches(const ssn_ctx *ctx);   /* kernels launched by this ctx so far */
+/* Sum of the scoring kernel's own durations (events on its launch stream) since the last reset. */
+ssn_status ssn_kernel_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_launches, int reset);
+/* Writes a buffer larger than L2 on the ctx's device (cold-cache timing). */
+ssn_status ssn_flush_l2(ssn_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSN_H */

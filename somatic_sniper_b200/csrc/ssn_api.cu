@@ -1,0 +1,636 @@
+/*
+ * ssn_api.cu — the C ABI of include/ssn.h: context, model upload, pinned SoA batch slots,
+ * stream/event pipeline (H2D -> fused scoring kernel -> D2H of the compacted site ring).
+ * There is no CPU path in this file or anywhere else in libssn.so.
+ */
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "ssn_internal.h"
+#include "ssn_kernels.cuh"
+
+using namespace ssn;
+
+/* ------------------------------------------------------------------------------------------------ */
+
+static thread_local char g_err[512] = "";
+
+extern "C" void ssn_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char *ssn_last_error(void) { return g_err; }
+extern "C" int ssn_abi_version(void) { return SSN_ABI_VERSION; }
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            ssn_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return SSN_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+
+enum SlotState { SLOT_FREE = 0, SLOT_FILLING, SLOT_SUBMITTED, SLOT_DONE };
+
+struct ssn_batch {
+    ssn_ctx *ctx;
+    int index;
+    SlotState state;
+    uint64_t seq;
+    uint32_t max_columns;
+    uint64_t max_entries;
+    uint32_t ncol;
+    uint64_t nent;
+    uint32_t flags;
+    bool resident;            /* device copy matches the host arrays */
+    /* pinned host */
+    uint32_t *h_off; uint8_t *h_bs, *h_bq, *h_mq, *h_ref;
+    uint32_t *h_count;        /* 2 words */
+    ssn_site *h_sites; uint32_t h_sites_cap;
+    uint32_t *h_dump; size_t h_dump_words;
+    /* device */
+    uint32_t *d_off; uint8_t *d_bs, *d_bq, *d_mq, *d_ref;
+    uint32_t *d_count;
+    ssn_site *d_sites; uint32_t site_cap;
+    uint32_t *d_dump; size_t d_dump_words;
+    uint32_t max_tile_words;
+    cudaStream_t stream;
+    cudaEvent_t done;
+    uint32_t n_sites;
+};
+
+struct KernelTimer {
+    cudaEvent_t a, b;
+    bool pending;
+};
+
+struct ssn_ctx {
+    int device;
+    ssn_params params;
+    ssn_host_tables tab;
+    /* device tables: coef and lhet share one allocation so one access-policy window covers both */
+    double *d_coef_lhet; double *d_fk;
+    int32_t *d_prior, *d_jointprior, *d_qadd;
+    DevModel model;
+    std::vector<ssn_batch*> slots;
+    uint64_t next_seq;
+    cudaStream_t main_stream;
+    cudaEvent_t t0, t1;
+    uint64_t launches;
+    int num_sms, ctas_per_sm_cap;
+    size_t smem_optin;
+    uint32_t smem_words_default;
+    uint32_t *d_scratch; size_t scratch_words;   /* global key store, all warps */
+    uint32_t grid_cap;                          /* largest grid ever launched (scratch sizing) */
+    void *d_flush; size_t flush_bytes;
+    std::vector<KernelTimer> timers;
+    size_t timer_next;
+    double kernel_ms; uint64_t kernel_n;
+    size_t l2_window_bytes;
+};
+
+extern "C" ssn_status ssn_params_default(ssn_params *p)
+{
+    if (!p) { ssn_set_error("null params"); return SSN_ERR_ARG; }
+    memset(p, 0, sizeof(*p));
+    p->theta = 0.85f; p->het_rate = 0.001f; p->eta = 0.03f; p->n_hap = 2; p->cap_mapq = 60;
+    p->min_somatic_qual = 15; p->include_loh = 1; p->include_gor = 1; p->use_priors = 1;
+    p->use_joint_priors = 0; p->somatic_mutation_rate = 0.01;
+    return SSN_OK;
+}
+
+extern "C" int ssn_nt16_of_char(int ch)
+{
+    static const char rev[] = "=ACMGRSVTWYHKDBN";
+    ch &= 0xff;
+    if (ch >= '0' && ch <= '3') return 1 << (ch - '0');
+    for (int i = 0; i < 16; ++i) {
+        if (ch == rev[i]) return i;
+        if (rev[i] >= 'A' && rev[i] <= 'Z' && ch == rev[i] + ('a' - 'A')) return i;
+    }
+    return 15;
+}
+
+static size_t smem_bytes_for(uint32_t words_per_warp)
+{
+    return 2048 + (1024 + 64) * 4 + 160 * 4 + (size_t)kWarpsPerCta * (kSlotWords + words_per_warp) * 4;
+}
+
+static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, uint64_t max_entries)
+{
+    b->ctx = ctx; b->state = SLOT_FREE; b->max_columns = max_columns; b->max_entries = max_entries;
+    const size_t ent = (size_t)max_entries + 64;
+    CU(cudaMallocHost(&b->h_off, sizeof(uint32_t) * (2 * (size_t)max_columns + 1)));
+    CU(cudaMallocHost(&b->h_bs, ent));
+    CU(cudaMallocHost(&b->h_bq, ent));
+    CU(cudaMallocHost(&b->h_mq, ent));
+    CU(cudaMallocHost(&b->h_ref, (size_t)max_columns + 64));
+    CU(cudaMallocHost(&b->h_count, 2 * sizeof(uint32_t)));
+    CU(cudaMalloc(&b->d_off, sizeof(uint32_t) * (2 * (size_t)max_columns + 1)));
+    CU(cudaMalloc(&b->d_bs, ent));
+    CU(cudaMalloc(&b->d_bq, ent));
+    CU(cudaMalloc(&b->d_mq, ent));
+    CU(cudaMalloc(&b->d_ref, (size_t)max_columns + 64));
+    CU(cudaMalloc(&b->d_count, 2 * sizeof(uint32_t)));
+    b->site_cap = std::max<uint32_t>(4096u, max_columns / 16u);
+    CU(cudaMalloc(&b->d_sites, sizeof(ssn_site) * (size_t)b->site_cap));
+    b->h_sites_cap = 4096;
+    CU(cudaMallocHost(&b->h_sites, sizeof(ssn_site) * (size_t)b->h_sites_cap));
+    CU(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+    return SSN_OK;
+}
+
+static void slot_free(ssn_batch *b)
+{
+    if (!b) return;
+    cudaFreeHost(b->h_off); cudaFreeHost(b->h_bs); cudaFreeHost(b->h_bq); cudaFreeHost(b->h_mq);
+    cudaFreeHost(b->h_ref); cudaFreeHost(b->h_count); cudaFreeHost(b->h_sites); cudaFreeHost(b->h_dump);
+    cudaFree(b->d_off); cudaFree(b->d_bs); cudaFree(b->d_bq); cudaFree(b->d_mq); cudaFree(b->d_ref);
+    cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump);
+    if (b->stream) cudaStreamDestroy(b->stream);
+    if (b->done) cudaEventDestroy(b->done);
+    delete b;
+}
+
+extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slots, uint32_t max_columns,
+                                 uint64_t max_entries, ssn_ctx **out)
+{
+    if (!p || !out || n_slots == 0 || max_columns == 0) { ssn_set_error("ssn_create: bad argument"); return SSN_ERR_ARG; }
+    if (max_entries >= (1ull << 32) - 64) { ssn_set_error("ssn_create: max_entries must stay below 2^32"); return SSN_ERR_ARG; }
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { ssn_set_error("ssn_create: no CUDA device %d (found %d)", device, ndev); return SSN_ERR_CUDA; }
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) { ssn_set_error("ssn_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return SSN_ERR_CUDA; }
+
+    ssn_ctx *ctx = new ssn_ctx();
+    ctx->device = device; ctx->params = *p; ctx->next_seq = 1; ctx->launches = 0;
+    ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->d_scratch = nullptr; ctx->scratch_words = 0; ctx->grid_cap = 0; ctx->d_flush = nullptr; ctx->flush_bytes = 0;
+    ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
+    const char *env = getenv("SSN_SMEM_WORDS");
+    ctx->smem_words_default = env ? (uint32_t)atoi(env) : 2048u;
+    if (ssn_tables_build(p, &ctx->tab) != 0) { ssn_set_error("ssn_create: table construction failed (n_hap=%d)", p->n_hap); delete ctx; return SSN_ERR_ARG; }
+
+    const size_t coef_n = (size_t)64 * 65536, lhet_n = 65536;
+    CU(cudaMalloc(&ctx->d_coef_lhet, sizeof(double) * (coef_n + lhet_n)));
+    CU(cudaMemcpy(ctx->d_coef_lhet, ctx->tab.coef, sizeof(double) * coef_n, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(ctx->d_coef_lhet + coef_n, ctx->tab.lhet, sizeof(double) * lhet_n, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_fk, sizeof(double) * 256));
+    CU(cudaMemcpy(ctx->d_fk, ctx->tab.fk, sizeof(double) * 256, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_prior, sizeof(ctx->tab.prior)));
+    CU(cudaMemcpy(ctx->d_prior, ctx->tab.prior, sizeof(ctx->tab.prior), cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_jointprior, sizeof(ctx->tab.jointprior)));
+    CU(cudaMemcpy(ctx->d_jointprior, ctx->tab.jointprior, sizeof(ctx->tab.jointprior), cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_qadd, sizeof(ctx->tab.qadd)));
+    CU(cudaMemcpy(ctx->d_qadd, ctx->tab.qadd, sizeof(ctx->tab.qadd), cudaMemcpyHostToDevice));
+    DevModel &M = ctx->model;
+    M.coef = ctx->d_coef_lhet; M.lhet = ctx->d_coef_lhet + coef_n; M.fk = ctx->d_fk;
+    M.prior = ctx->d_prior; M.jointprior = ctx->d_jointprior; M.qadd = ctx->d_qadd;
+    M.q_r_int = (int)(ctx->tab.q_r + 0.5);                 /* sniper_maqcns_call, sniper_maqcns.c:279 */
+    M.cap_mapq = p->cap_mapq; M.min_somatic_qual = p->min_somatic_qual;
+    M.include_loh = p->include_loh; M.include_gor = p->include_gor; M.use_joint = p->use_joint_priors;
+
+    CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&ctx->t0));
+    CU(cudaEventCreate(&ctx->t1));
+    CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_optin));
+    CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_optin));
+
+    /* keep coef+lhet resident in L2: persisting carve-out + per-stream access-policy window */
+    size_t want = sizeof(double) * (coef_n + lhet_n);
+    size_t persist = std::min<size_t>(want, (size_t)prop.persistingL2CacheMaxSize);
+    if (persist > 0 && prop.accessPolicyMaxWindowSize > 0) {
+        CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist));
+        ctx->l2_window_bytes = std::min<size_t>(want, (size_t)prop.accessPolicyMaxWindowSize);
+    }
+    for (uint32_t i = 0; i < n_slots; ++i) {
+        ssn_batch *b = new ssn_batch();
+        memset((void*)b, 0, sizeof(*b));
+        b->index = (int)i;
+        ctx->slots.push_back(b);
+        ssn_status st = slot_alloc(ctx, b, max_columns, max_entries);
+        if (st != SSN_OK) { ssn_destroy(ctx); return st; }
+        if (ctx->l2_window_bytes) {
+            cudaStreamAttrValue attr;
+            memset(&attr, 0, sizeof(attr));
+            attr.accessPolicyWindow.base_ptr = ctx->d_coef_lhet;
+            attr.accessPolicyWindow.num_bytes = ctx->l2_window_bytes;
+            attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)ctx->l2_window_bytes);
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            CU(cudaStreamSetAttribute(b->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        }
+    }
+    ctx->timers.resize(64);
+    for (auto &t : ctx->timers) {
+        CU(cudaEventCreate(&t.a));
+        CU(cudaEventCreate(&t.b));
+        t.pending = false;
+    }
+    *out = ctx;
+    return SSN_OK;
+}
+
+extern "C" void ssn_destroy(ssn_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (ssn_batch *b : ctx->slots) slot_free(b);
+    for (auto &t : ctx->timers) { if (t.a) cudaEventDestroy(t.a); if (t.b) cudaEventDestroy(t.b); }
+    cudaFree(ctx->d_coef_lhet); cudaFree(ctx->d_fk); cudaFree(ctx->d_prior); cudaFree(ctx->d_jointprior);
+    cudaFree(ctx->d_qadd); cudaFree(ctx->d_scratch); cudaFree(ctx->d_flush);
+    if (ctx->main_stream) cudaStreamDestroy(ctx->main_stream);
+    if (ctx->t0) cudaEventDestroy(ctx->t0);
+    if (ctx->t1) cudaEventDestroy(ctx->t1);
+    ssn_tables_free(&ctx->tab);
+    delete ctx;
+}
+
+extern "C" ssn_status ssn_get_tables(const ssn_ctx *ctx, ssn_tables *out)
+{
+    if (!ctx || !out) { ssn_set_error("ssn_get_tables: null"); return SSN_ERR_ARG; }
+    out->coef = ctx->tab.coef; out->lhet = ctx->tab.lhet; out->fk = ctx->tab.fk; out->q_r = ctx->tab.q_r;
+    out->prior = ctx->tab.prior; out->jointprior = ctx->tab.jointprior; out->qadd = ctx->tab.qadd;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_host_tables_create(const ssn_params *p, ssn_tables *view, void **handle)
+{
+    if (!p || !view || !handle) { ssn_set_error("ssn_host_tables_create: null"); return SSN_ERR_ARG; }
+    ssn_host_tables *t = new ssn_host_tables();
+    if (ssn_tables_build(p, t) != 0) { delete t; ssn_set_error("table construction failed (n_hap=%d)", p->n_hap); return SSN_ERR_ARG; }
+    view->coef = t->coef; view->lhet = t->lhet; view->fk = t->fk; view->q_r = t->q_r;
+    view->prior = t->prior; view->jointprior = t->jointprior; view->qadd = t->qadd;
+    *handle = t;
+    return SSN_OK;
+}
+
+extern "C" void ssn_host_tables_destroy(void *handle)
+{
+    ssn_host_tables *t = (ssn_host_tables*)handle;
+    if (!t) return;
+    ssn_tables_free(t);
+    delete t;
+}
+
+/* ------------------------------------------------------------------------------------------------ */
+
+extern "C" ssn_status ssn_batch_acquire(ssn_ctx *ctx, ssn_batch **out)
+{
+    if (!ctx || !out) { ssn_set_error("ssn_batch_acquire: null"); return SSN_ERR_ARG; }
+    ssn_batch *pick = nullptr;
+    for (ssn_batch *b : ctx->slots) if (b->state == SLOT_FREE) { pick = b; break; }
+    if (!pick) {
+        for (ssn_batch *b : ctx->slots)
+            if (b->state == SLOT_DONE && (!pick || b->seq < pick->seq)) pick = b;
+    }
+    if (!pick) { ssn_set_error("ssn_batch_acquire: all %zu slots are in flight; drain ssn_results_next first", ctx->slots.size()); return SSN_ERR_STATE; }
+    pick->state = SLOT_FILLING; pick->ncol = 0; pick->nent = 0; pick->resident = false; pick->n_sites = 0;
+    *out = pick;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_release(ssn_ctx *ctx, ssn_batch *b)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_release: bad batch"); return SSN_ERR_ARG; }
+    if (b->state == SLOT_SUBMITTED) { ssn_set_error("ssn_batch_release: batch still in flight"); return SSN_ERR_STATE; }
+    b->state = SLOT_FREE;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_view_get(ssn_batch *b, ssn_batch_view *out)
+{
+    if (!b || !out) { ssn_set_error("ssn_batch_view_get: null"); return SSN_ERR_ARG; }
+    out->off = b->h_off; out->bs = b->h_bs; out->bq = b->h_bq; out->mq = b->h_mq; out->ref_nt16 = b->h_ref;
+    out->max_columns = b->max_columns; out->max_entries = b->max_entries;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_set_size(ssn_batch *b, uint32_t n_columns, uint64_t n_entries)
+{
+    if (!b) { ssn_set_error("ssn_batch_set_size: null"); return SSN_ERR_ARG; }
+    if (n_columns > b->max_columns || n_entries > b->max_entries) {
+        ssn_set_error("ssn_batch_set_size: %u columns / %llu entries exceed the slot capacity %u / %llu", n_columns,
+                      (unsigned long long)n_entries, b->max_columns, (unsigned long long)b->max_entries);
+        return SSN_ERR_ARG;
+    }
+    b->ncol = n_columns; b->nent = n_entries; b->resident = false;
+    return SSN_OK;
+}
+
+/* Validates the offsets and finds the largest key-store footprint of any 32-column tile. */
+static ssn_status scan_offsets(ssn_batch *b)
+{
+    const uint32_t *off = b->h_off;
+    const uint32_t ncol = b->ncol;
+    if (ncol == 0) { b->max_tile_words = 0; return SSN_OK; }
+    if (off[2 * (size_t)ncol] != b->nent) { ssn_set_error("batch: off[2*ncol]=%u but n_entries=%llu", off[2 * (size_t)ncol], (unsigned long long)b->nent); return SSN_ERR_ARG; }
+    uint32_t max_tile = 0;
+    for (uint32_t t = 0; t < ncol; t += 32) {
+        const uint32_t e = std::min(ncol, t + 32);
+        uint32_t words = 0;
+        for (uint32_t c = t; c < e; ++c) {
+            const uint32_t a = off[2 * (size_t)c], m = off[2 * (size_t)c + 1], z = off[2 * (size_t)c + 2];
+            if (m < a || z < m) { ssn_set_error("batch: offsets of column %u decrease", c); return SSN_ERR_ARG; }
+            const uint32_t n = z - a;
+            if (n > (uint32_t)kRunLen * kMaxRuns) { ssn_set_error("batch: column %u holds %u read-bases; this build supports %d", c, n, kRunLen * kMaxRuns); return SSN_ERR_ARG; }
+            words += (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
+        }
+        max_tile = std::max(max_tile, words);
+    }
+    b->max_tile_words = max_tile;
+    return SSN_OK;
+}
+
+static ssn_status copy_in(ssn_ctx *ctx, ssn_batch *b)
+{
+    (void)ctx;
+    if (b->ncol == 0) return SSN_OK;
+    CU(cudaMemcpyAsync(b->d_off, b->h_off, sizeof(uint32_t) * (2 * (size_t)b->ncol + 1), cudaMemcpyHostToDevice, b->stream));
+    CU(cudaMemcpyAsync(b->d_bs, b->h_bs, b->nent, cudaMemcpyHostToDevice, b->stream));
+    CU(cudaMemcpyAsync(b->d_bq, b->h_bq, b->nent, cudaMemcpyHostToDevice, b->stream));
+    CU(cudaMemcpyAsync(b->d_mq, b->h_mq, b->nent, cudaMemcpyHostToDevice, b->stream));
+    CU(cudaMemcpyAsync(b->d_ref, b->h_ref, b->ncol, cudaMemcpyHostToDevice, b->stream));
+    return SSN_OK;
+}
+
+static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
+{
+    const bool dump = (flags & SSN_SUBMIT_COLUMN_DUMP) != 0;
+    b->flags = flags;
+    CU(cudaMemsetAsync(b->d_count, 0, 2 * sizeof(uint32_t), b->stream));
+    if (b->ncol == 0) return SSN_OK;
+    if (dump) {
+        const size_t need = (size_t)b->ncol * SSN_COLUMN_DUMP_WORDS;
+        if (b->d_dump_words < need) {
+            CU(cudaStreamSynchronize(b->stream));
+            cudaFree(b->d_dump); cudaFreeHost(b->h_dump);
+            b->d_dump = nullptr; b->h_dump = nullptr; b->d_dump_words = b->h_dump_words = 0;
+            CU(cudaMalloc(&b->d_dump, need * 4));
+            CU(cudaMallocHost(&b->h_dump, need * 4));
+            b->d_dump_words = b->h_dump_words = need;
+        }
+    }
+    /* shared-memory key store per warp: big enough for the batch's largest tile when that is
+     * affordable, else the default and the oversized tiles go through the global scratch */
+    uint32_t words = ((b->max_tile_words + 63u) / 64u) * 64u;
+    if (words > ctx->smem_words_default) words = ctx->smem_words_default;
+    if (words < 64u) words = 64u;
+    size_t smem = smem_bytes_for(words);
+    if (smem > ctx->smem_optin) { ssn_set_error("shared memory request %zu exceeds %zu", smem, ctx->smem_optin); return SSN_ERR_ARG; }
+    int per_sm = 0;
+    if (dump) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ssn_score_kernel<true>, kWarpsPerCta * 32, smem));
+    else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ssn_score_kernel<false>, kWarpsPerCta * 32, smem));
+    if (per_sm < 1) { ssn_set_error("kernel does not fit on an SM with %zu bytes of shared memory", smem); return SSN_ERR_CUDA; }
+    const uint32_t ntiles = (b->ncol + 31u) / 32u;
+    uint32_t grid = (uint32_t)(ctx->num_sms * per_sm);
+    const uint32_t need_ctas = (ntiles + kWarpsPerCta - 1) / kWarpsPerCta;
+    if (grid > need_ctas) grid = need_ctas;
+    if (b->max_tile_words > words) {
+        const size_t per_warp = ((size_t)b->max_tile_words + 63) / 64 * 64;
+        const size_t need = per_warp * grid * kWarpsPerCta;
+        if (ctx->scratch_words < need) {
+            CU(cudaDeviceSynchronize());
+            cudaFree(ctx->d_scratch); ctx->d_scratch = nullptr; ctx->scratch_words = 0;
+            CU(cudaMalloc(&ctx->d_scratch, need * 4));
+            ctx->scratch_words = need;
+        }
+    }
+    DevBatch B;
+    B.off = b->d_off; B.bs = b->d_bs; B.bq = b->d_bq; B.mq = b->d_mq; B.ref_nt16 = b->d_ref; B.ncol = b->ncol;
+    B.sites = b->d_sites; B.site_count = b->d_count; B.site_cap = b->site_cap;
+    B.coldump = dump ? b->d_dump : nullptr;
+    B.scratch = b->max_tile_words > words ? ctx->d_scratch : nullptr;
+    B.scratch_words_per_warp = (uint32_t)(((size_t)b->max_tile_words + 63) / 64 * 64);
+    B.smem_words_per_warp = words;
+    KernelTimer &kt = ctx->timers[ctx->timer_next];
+    ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
+    if (kt.pending) {
+        float ms = 0;
+        CU(cudaEventSynchronize(kt.b));
+        CU(cudaEventElapsedTime(&ms, kt.a, kt.b));
+        ctx->kernel_ms += ms; ctx->kernel_n += 1; kt.pending = false;
+    }
+    CU(cudaEventRecord(kt.a, b->stream));
+    if (dump) ssn_score_kernel<true><<<grid, kWarpsPerCta * 32, smem, b->stream>>>(ctx->model, B);
+    else ssn_score_kernel<false><<<grid, kWarpsPerCta * 32, smem, b->stream>>>(ctx->model, B);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(kt.b, b->stream));
+    kt.pending = true;
+    ctx->launches += 1;
+    return SSN_OK;
+}
+
+static ssn_status copy_out_async(ssn_batch *b)
+{
+    CU(cudaMemcpyAsync(b->h_count, b->d_count, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, b->stream));
+    if ((b->flags & SSN_SUBMIT_COLUMN_DUMP) && b->ncol)
+        CU(cudaMemcpyAsync(b->h_dump, b->d_dump, (size_t)b->ncol * SSN_COLUMN_DUMP_WORDS * 4, cudaMemcpyDeviceToHost, b->stream));
+    CU(cudaEventRecord(b->done, b->stream));
+    return SSN_OK;
+}
+
+/* after the batch's stream work is done: handle ring overflow, copy the sites, sort by column */
+static ssn_status collect(ssn_ctx *ctx, ssn_batch *b)
+{
+    CU(cudaEventSynchronize(b->done));
+    uint32_t n = b->h_count[0];
+    if (n > b->site_cap) {
+        /* ring too small: grow it and score the (still resident) batch again */
+        CU(cudaStreamSynchronize(b->stream));
+        cudaFree(b->d_sites); b->d_sites = nullptr;
+        b->site_cap = n + n / 8 + 64;
+        CU(cudaMalloc(&b->d_sites, sizeof(ssn_site) * (size_t)b->site_cap));
+        ssn_status st = launch(ctx, b, b->flags);
+        if (st != SSN_OK) return st;
+        st = copy_out_async(b);
+        if (st != SSN_OK) return st;
+        CU(cudaEventSynchronize(b->done));
+        n = b->h_count[0];
+        if (n > b->site_cap) { ssn_set_error("site ring overflow persists (%u > %u)", n, b->site_cap); return SSN_ERR_OVERFLOW; }
+    }
+    if (n > b->h_sites_cap) {
+        cudaFreeHost(b->h_sites); b->h_sites = nullptr;
+        b->h_sites_cap = n + n / 8 + 64;
+        CU(cudaMallocHost(&b->h_sites, sizeof(ssn_site) * (size_t)b->h_sites_cap));
+    }
+    if (n) {
+        CU(cudaMemcpyAsync(b->h_sites, b->d_sites, sizeof(ssn_site) * (size_t)n, cudaMemcpyDeviceToHost, b->stream));
+        CU(cudaStreamSynchronize(b->stream));
+        std::sort(b->h_sites, b->h_sites + n, [](const ssn_site &x, const ssn_site &y) { return x.column < y.column; });
+    }
+    b->n_sites = n;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_submit(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_submit: bad batch"); return SSN_ERR_ARG; }
+    if (b->state != SLOT_FILLING) { ssn_set_error("ssn_batch_submit: batch was not acquired"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = scan_offsets(b);
+    if (st != SSN_OK) return st;
+    if ((st = copy_in(ctx, b)) != SSN_OK) return st;
+    b->resident = true;
+    if ((st = launch(ctx, b, flags)) != SSN_OK) return st;
+    if ((st = copy_out_async(b)) != SSN_OK) return st;
+    b->state = SLOT_SUBMITTED; b->seq = ctx->next_seq++;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_results_next(ssn_ctx *ctx, const ssn_site **sites, uint32_t *n_sites, ssn_batch **batch)
+{
+    if (!ctx || !sites || !n_sites) { ssn_set_error("ssn_results_next: null"); return SSN_ERR_ARG; }
+    ssn_batch *pick = nullptr;
+    for (ssn_batch *b : ctx->slots)
+        if (b->state == SLOT_SUBMITTED && (!pick || b->seq < pick->seq)) pick = b;
+    if (!pick) { ssn_set_error("ssn_results_next: nothing submitted"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = collect(ctx, pick);
+    if (st != SSN_OK) return st;
+    pick->state = SLOT_DONE;
+    *sites = pick->h_sites; *n_sites = pick->n_sites;
+    if (batch) *batch = pick;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_column_dump(ssn_batch *b, const uint32_t **words)
+{
+    if (!b || !words) { ssn_set_error("ssn_batch_column_dump: null"); return SSN_ERR_ARG; }
+    if (!(b->flags & SSN_SUBMIT_COLUMN_DUMP) || !b->h_dump) { ssn_set_error("batch was not scored with SSN_SUBMIT_COLUMN_DUMP"); return SSN_ERR_STATE; }
+    *words = b->h_dump;
+    return SSN_OK;
+}
+
+/* ---- device-resident path ------------------------------------------------------------------------- */
+
+extern "C" ssn_status ssn_batch_upload(ssn_ctx *ctx, ssn_batch *b)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_upload: bad batch"); return SSN_ERR_ARG; }
+    if (b->state != SLOT_FILLING) { ssn_set_error("ssn_batch_upload: batch was not acquired"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = scan_offsets(b);
+    if (st != SSN_OK) return st;
+    if ((st = copy_in(ctx, b)) != SSN_OK) return st;
+    CU(cudaStreamSynchronize(b->stream));
+    b->resident = true;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_score_resident(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_score_resident: bad batch"); return SSN_ERR_ARG; }
+    if (!b->resident) { ssn_set_error("ssn_batch_score_resident: call ssn_batch_upload first"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    return launch(ctx, b, flags);
+}
+
+extern "C" ssn_status ssn_batch_fetch(ssn_ctx *ctx, ssn_batch *b, const ssn_site **sites, uint32_t *n_sites)
+{
+    if (!ctx || !b || b->ctx != ctx || !sites || !n_sites) { ssn_set_error("ssn_batch_fetch: bad argument"); return SSN_ERR_ARG; }
+    if (!b->resident) { ssn_set_error("ssn_batch_fetch: batch is not resident"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = copy_out_async(b);
+    if (st != SSN_OK) return st;
+    if ((st = collect(ctx, b)) != SSN_OK) return st;
+    *sites = b->h_sites; *n_sites = b->n_sites;
+    return SSN_OK;
+}
+
+/* ---- timing / accounting ----------------------------------------------------------------------------- */
+
+static ssn_status join_streams(ssn_ctx *ctx, cudaEvent_t ev)
+{
+    /* main_stream waits for everything queued so far on every slot stream, then records ev */
+    for (ssn_batch *b : ctx->slots) {
+        cudaEvent_t tmp;
+        CU(cudaEventCreateWithFlags(&tmp, cudaEventDisableTiming));
+        CU(cudaEventRecord(tmp, b->stream));
+        CU(cudaStreamWaitEvent(ctx->main_stream, tmp, 0));
+        CU(cudaEventDestroy(tmp));
+    }
+    CU(cudaEventRecord(ev, ctx->main_stream));
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_timer_start(ssn_ctx *ctx)
+{
+    if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = join_streams(ctx, ctx->t0);
+    if (st != SSN_OK) return st;
+    /* every slot stream starts after t0 */
+    for (ssn_batch *b : ctx->slots) CU(cudaStreamWaitEvent(b->stream, ctx->t0, 0));
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_timer_stop(ssn_ctx *ctx, float *elapsed_ms)
+{
+    if (!ctx || !elapsed_ms) { ssn_set_error("null argument"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    ssn_status st = join_streams(ctx, ctx->t1);
+    if (st != SSN_OK) return st;
+    CU(cudaEventSynchronize(ctx->t1));
+    CU(cudaEventElapsedTime(elapsed_ms, ctx->t0, ctx->t1));
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_sync(ssn_ctx *ctx)
+{
+    if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaDeviceSynchronize());
+    return SSN_OK;
+}
+
+extern "C" uint64_t ssn_kernel_launches(const ssn_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" ssn_status ssn_kernel_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_launches, int reset)
+{
+    if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    for (auto &kt : ctx->timers) {
+        if (!kt.pending) continue;
+        float ms = 0;
+        CU(cudaEventSynchronize(kt.b));
+        CU(cudaEventElapsedTime(&ms, kt.a, kt.b));
+        ctx->kernel_ms += ms; ctx->kernel_n += 1; kt.pending = false;
+    }
+    if (total_ms) *total_ms = (float)ctx->kernel_ms;
+    if (n_launches) *n_launches = ctx->kernel_n;
+    if (reset) { ctx->kernel_ms = 0; ctx->kernel_n = 0; }
+    return SSN_OK;
+}
+
+__global__ void ssn_flush_kernel(uint4 *p, size_t n)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = make_uint4((unsigned)i, 1u, 2u, 3u);
+}
+
+extern "C" ssn_status ssn_flush_l2(ssn_ctx *ctx)
+{
+    if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    if (!ctx->d_flush) {
+        ctx->flush_bytes = (size_t)256 << 20;
+        CU(cudaMalloc(&ctx->d_flush, ctx->flush_bytes));
+    }
+    ssn_flush_kernel<<<ctx->num_sms * 4, 256, 0, ctx->main_stream>>>((uint4*)ctx->d_flush, ctx->flush_bytes / 16);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->main_stream));
+    return SSN_OK;
+}

@@ -1,0 +1,663 @@
+/*
+ * ssn_kernels.cuh — the fused per-column scoring kernel (sm_100a).
+ *
+ * One launch scores a whole SoA batch.  A persistent grid of warps pulls TILES of 32 consecutive
+ * columns from an atomic counter.  Each tile runs in two phases inside one warp:
+ *
+ *  FRONT (warp-per-column, 32 lanes = 32 read-bases at a time; looped over the tile's columns)
+ *    load bs/bq/mq coalesced -> 16-bit sort key per read-base -> packed (2 keys / register)
+ *    bitonic sort in registers with VIMNMX.U16x2 + SHFL -> sorted keys to the warp's key store
+ *    (shared memory; a per-warp global scratch when a tile does not fit) ; REDUX for the mapQ sums.
+ *    Tumor and normal are sorted together (sample bit on top of the key).
+ *  BACK (lane-per-column, 32 columns in flight per warp)
+ *    walk the sorted keys: the strictly sequential float<-double error-dependency chains
+ *    (sniper_maqcns.c:160-176), then the 10 genotype likelihoods, the p[k,k] correction, the
+ *    quantisation, the consensus call (both samples), then the rare somatic-score branch
+ *    (somatic_sniper.c:156-227) and, for sites that pass the gate, warp-cooperative site statistics
+ *    (dqstats.c:6-53) and a compacted ssn_site record.  GLFs never leave registers.
+ *
+ * The 16-bit key.  The reference sorts x = q<<24 | valid<<21 | strand<<18 | b4<<16 | baseQ<<8 | mapQ
+ * ascending and consumes it from the top (sniper_maqcns.c:144-162).  All state touched by an entry
+ * (esum/fsum/c of its base, w of its strand/base class) belongs to its base b4, so the four bases'
+ * chains are independent and may be walked one after another; inside one base the reference order is
+ * q desc, valid desc, strand desc, baseQ desc.  mapQ never changes a contribution, and baseQ only
+ * matters for q in {1,2,3}, where entries with baseQ in {64,128,192} keep q while their neighbours
+ * are promoted to 4 (:165).  Hence
+ *     key = sample<<15 | b4<<13 | q<<5 | valid<<4 | strand<<3 | sub
+ * with sub = 7 for q==0 or q>=4, and 1 + (rank of the baseQ group in
+ * {[q,63], 64, [65,127], 128, [129,191], 192, [193,255]}) for q in 1..3.  Entries that contribute
+ * nothing (q_eff == 0) get key 0 and sink to the bottom together with the padding.  Descending key
+ * order reproduces the reference's chain for every base exactly.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ssn.h"
+
+#ifndef SSN_ROUND_MAGIC
+#define SSN_ROUND_MAGIC 1 /* 1: (s+M)-M rounding in the FP64 pipe; 0: F2F.F32.F64 + F2F.F64.F32 */
+#endif
+
+namespace ssn {
+
+constexpr int kWarpsPerCta = 4;
+constexpr int kRunLen = 1024;          /* keys per sorted run (R = 16 packed registers) */
+constexpr int kMaxRuns = 64;           /* => at most 65536 read-bases per column (tumor + normal) */
+constexpr int kSlotWords = 24 * 32;    /* per warp: 8 (sample,base) slots x {esum,fsum,count} x 32 lanes */
+constexpr unsigned kFull = 0xffffffffu;
+
+struct DevModel {
+    const double *coef, *lhet, *fk;
+    const int32_t *prior, *jointprior, *qadd;
+    int32_t q_r_int, cap_mapq, min_somatic_qual, include_loh, include_gor, use_joint;
+};
+
+struct DevBatch {
+    const uint32_t *off;
+    const uint8_t *bs, *bq, *mq, *ref_nt16;
+    uint32_t ncol;
+    ssn_site *sites;
+    uint32_t *site_count;   /* [0] = sites wanted, [1] = tile counter */
+    uint32_t site_cap;
+    uint32_t *coldump;      /* ncol * SSN_COLUMN_DUMP_WORDS or null */
+    uint32_t *scratch;      /* per-warp global key store for tiles that exceed shared memory */
+    uint32_t scratch_words_per_warp;
+    uint32_t smem_words_per_warp;
+};
+
+/* -------------------------------------------------------------------------------------------- */
+/* key construction (sniper_maqcns.c:144-156 + the :165 promotion rule folded in)              */
+
+__device__ __forceinline__ uint32_t make_key(uint32_t bs, uint32_t bq, uint32_t mq, uint32_t ref16, uint32_t is_tumor)
+{
+    uint32_t nt = bs & 15u, strand = (bs >> 4) & 1u;
+    uint32_t q = min(bq, mq);
+    nt = nt ? nt : ref16;
+    uint32_t valid = (nt != 0u && (nt & (nt - 1u)) == 0u) ? 1u : 0u;   /* bam_nt16_nt4_table < 4 */
+    uint32_t b4 = valid ? ((nt >> 1) - (nt >> 3)) : 0u;                /* 1,2,4,8 -> 0,1,2,3 */
+    uint32_t low6 = bq & 0x3fu;
+    uint32_t sub = 7u;
+    if (q >= 1u && q <= 3u) sub = 1u + (bq < 64u ? 0u : 2u * (bq >> 6) - (low6 == 0u ? 1u : 0u));
+    uint32_t key = is_tumor << 15 | b4 << 13 | q << 5 | valid << 4 | strand << 3 | sub;
+    bool contributes = q != 0u || low6 != 0u;
+    return contributes ? key : 0u;
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* packed bitonic sort: R registers per lane, 2 keys per register.                              */
+/* half h, register r, lane l hold element e = r + R*l of half h; low halves sort ascending,    */
+/* high halves hold complemented keys (so they sort descending in true order), then one merge.  */
+
+template <int R, int K>   /* one bitonic merge level of block size K over the 32R elements of each half */
+__device__ __forceinline__ void merge_level(uint32_t (&v)[R], int lane)
+{
+#pragma unroll
+    for (int j = K >> 1; j > 0; j >>= 1) {
+        if (j >= R) {
+            const int jl = j / R, kl = K / R;
+            const bool keep_min = ((lane & jl) == 0) == ((lane & kl) == 0);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                uint32_t o = __shfl_xor_sync(kFull, v[r], jl);
+                v[r] = keep_min ? __vminu2(v[r], o) : __vmaxu2(v[r], o);
+            }
+        } else {
+            const bool lane_asc = (K >= R) ? ((lane & (K / R)) == 0) : true;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if ((r & j) == 0) {
+                    uint32_t a = v[r], b = v[r | j];
+                    uint32_t lo = __vminu2(a, b), hi = __vmaxu2(a, b);
+                    bool asc = (K >= R) ? lane_asc : ((r & K) == 0);
+                    v[r] = asc ? lo : hi;
+                    v[r | j] = asc ? hi : lo;
+                }
+            }
+        }
+    }
+}
+
+template <int R, int K>
+struct SortLevels {
+    __device__ static __forceinline__ void run(uint32_t (&v)[R], int lane)
+    {
+        SortLevels<R, K / 2>::run(v, lane);
+        merge_level<R, K>(v, lane);
+    }
+};
+template <int R>
+struct SortLevels<R, 1> {
+    __device__ static __forceinline__ void run(uint32_t (&)[R], int) {}
+};
+
+template <int R>
+__device__ __forceinline__ void sort_packed(uint32_t (&v)[R], int lane)
+{
+    SortLevels<R, 32 * R>::run(v, lane);           /* both halves, lockstep */
+#pragma unroll
+    for (int r = 0; r < R; ++r) {                  /* un-complement, then the half<->half stage */
+        uint32_t x = v[r] ^ 0xffff0000u;
+        uint32_t sw = __byte_perm(x, x, 0x1032);
+        uint32_t mn = __vminu2(x, sw), mx = __vmaxu2(x, sw);
+        v[r] = __byte_perm(mn, mx, 0x7610);
+    }
+    merge_level<R, 32 * R>(v, lane);               /* finish the 64R-element merge inside each half */
+}
+
+/* Load one run of `len` (<= 64R) read-bases starting at entry `e0`, build keys, sort, and store the top
+ * ceil(len/2) words (ascending) at store32[0..).  tumor_len = how many of the run's entries are tumor. */
+template <int R>
+__device__ __forceinline__ void sort_run(const DevBatch &B, uint32_t e0, int len, int tumor_len, uint32_t ref16,
+                                         uint32_t *store32, int lane, uint32_t &rms_t, uint32_t &rms_n, int cap_mapq)
+{
+    uint32_t v[R];
+#pragma unroll
+    for (int row = 0; row < 2 * R; ++row) {
+        const int i = row * 32 + lane;
+        uint32_t key = 0;
+        if (i < len) {
+            const uint32_t bs = B.bs[e0 + i], bq = B.bq[e0 + i], mq = B.mq[e0 + i];
+            const uint32_t is_t = i < tumor_len ? 1u : 0u;
+            key = make_key(bs, bq, mq, ref16, is_t);
+            const uint32_t m = min(mq & 0x7fu, (uint32_t)cap_mapq);      /* sniper_maqcns.c:173-174 */
+            if (is_t) rms_t += m * m; else rms_n += m * m;
+        }
+        const int r = row % R;
+        if (row < R) v[r] = key;
+        else v[r] |= (~key) << 16;
+    }
+    sort_packed<R>(v, lane);
+    const int wfirst = (64 * R - len) >> 1;
+    if (R == 1) {
+        uint16_t *s16 = reinterpret_cast<uint16_t*>(store32);
+        const int p0 = lane, p1 = 32 + lane;
+        if (p0 >= 2 * wfirst) s16[p0 - 2 * wfirst] = (uint16_t)(v[0] & 0xffffu);
+        if (p1 >= 2 * wfirst) s16[p1 - 2 * wfirst] = (uint16_t)(v[0] >> 16);
+    } else {
+#pragma unroll
+        for (int r = 0; r < R; r += 2) {
+            const int wi_lo = (lane * R + r) >> 1, wi_hi = 16 * R + wi_lo;
+            const uint32_t lo = __byte_perm(v[r], v[(r + 1) % R], 0x5410);
+            const uint32_t hi = __byte_perm(v[r], v[(r + 1) % R], 0x7632);
+            if (wi_lo >= wfirst) store32[wi_lo - wfirst] = lo;
+            if (wi_hi >= wfirst) store32[wi_hi - wfirst] = hi;
+        }
+    }
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* the sequential chain (lane-per-column)                                                       */
+
+/* round a positive double to float precision, staying in double: (s + 2^(e+29)) - 2^(e+29) rounds to
+ * nearest-even at the float ulp of s's binade, i.e. equals (double)(float)s for normal floats. */
+__device__ __forceinline__ double round_to_f32(double s)
+{
+#if SSN_ROUND_MAGIC
+    const int hi = __double2hiint(s);
+    const double m = __hiloint2double((hi & 0x7ff00000) + 0x01d00000, 0);
+    return __dsub_rn(__dadd_rn(s, m), m);
+#else
+    return (double)__double2float_rn(s);
+#endif
+}
+
+struct Chain {
+    double e, f;        /* float-valued accumulators held in double */
+    uint32_t c, w0, w1; /* count; per-strand dependency ranks */
+    int sb;             /* current (sample<<2 | base) slot, -1 = none */
+};
+
+__device__ __forceinline__ void chain_flush(const Chain &ch, uint32_t *slots, int lane)
+{
+    if (ch.sb >= 0) {
+        uint32_t *s = slots + ch.sb * 96 + lane;
+        s[0] = __float_as_uint(__double2float_rn(ch.e));
+        s[32] = __float_as_uint(__double2float_rn(ch.f));
+        s[64] = ch.c;
+    }
+}
+
+__device__ __forceinline__ void chain_step(Chain &ch, uint32_t key, const double *fk_s, uint32_t *slots, int lane)
+{
+    const int sb = (int)(key >> 13);
+    if (sb != ch.sb) {
+        chain_flush(ch, slots, lane);
+        ch.sb = sb; ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0;
+    }
+    uint32_t q = (key >> 5) & 0xffu;
+    if (q < 4u) {                                        /* sniper_maqcns.c:165 */
+        const uint32_t sub = key & 7u;
+        q = (q != 0u && (sub & 1u) == 0u) ? q : 4u;      /* sub-1 odd <=> baseQ in {64,128,192} */
+    }
+    const bool rev = (key >> 3) & 1u;
+    const uint32_t w = rev ? ch.w1 : ch.w0;
+    const double fkw = fk_s[w];
+    const double qd = __hiloint2double(0x43300000, (int)q) - 4503599627370496.0;   /* exact int -> double */
+    ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fkw, qd)));      /* esum += fk[w]*q  (:168) */
+    ch.f = round_to_f32(__dadd_rn(ch.f, fkw));                     /* fsum += fk[w]    (:169) */
+    const uint32_t wn = min(w + 1u, 255u);                         /* :170 */
+    if (rev) ch.w1 = wn; else ch.w0 = wn;
+    ++ch.c;
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* likelihoods, quantisation, consensus for one sample (lane-local)                             */
+
+struct Glf {
+    uint32_t lk[3];   /* 10 bytes packed: lk[i>>2] >> 8*(i&3) */
+    uint32_t min_lk, rms, cns;
+};
+
+__device__ __forceinline__ uint32_t glf_lk(const Glf &g, int i) { return (g.lk[i >> 2] >> (8 * (i & 3))) & 0xffu; }
+
+__device__ __forceinline__ int bar_error(float t1, float t3)
+{
+    int bar = (int)((double)__fdiv_rn(t1, t3) + 0.5);    /* sniper_maqcns.c:191-193 */
+    return min(max(bar, 4), 63);
+}
+
+__device__ void sample_glf(const DevModel &M, const uint32_t *slots, int lane, int sample, uint32_t n,
+                           uint32_t rms_sum, Glf &g)
+{
+    float es[4], fs[4];
+    int c[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        const uint32_t *s = slots + (sample * 4 + b) * 96 + lane;
+        es[b] = __uint_as_float(s[0]); fs[b] = __uint_as_float(s[32]); c[b] = (int)s[64];
+    }
+    g.rms = (uint32_t)(uint8_t)(int)(sqrt((double)rms_sum / (double)(int)n) + .499);   /* :176 */
+    int tot = c[0] + c[1] + c[2] + c[3];
+    if (tot > 255) {                                                                  /* :179-182 */
+#pragma unroll
+        for (int b = 0; b < 4; ++b) c[b] = (int)(254.0 * (double)c[b] / (double)tot + 0.5);
+        tot = c[0] + c[1] + c[2] + c[3];
+    }
+    /* gather the 10 terms' table indices first so the 16 loads are in flight together */
+    float t1v[10];
+    int cidx[10], hidx[10];
+    {
+        int g_i = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int k = j; k < 4; ++k) {
+                float t1 = 0.0f, t3 = 0.0f;
+                int t2 = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (i == j || i == k) continue;
+                    t1 = __fadd_rn(t1, es[i]); t2 += c[i]; t3 = __fadd_rn(t3, fs[i]);
+                }
+                t1v[g_i] = t1;
+                cidx[g_i] = t2 ? (bar_error(t1, t3) << 16 | tot << 8 | t2) : -1;
+                hidx[g_i] = (j == k) ? -1 : (c[j] << 8 | c[k]);
+                ++g_i;
+            }
+        }
+    }
+    double cf[10], lh[10];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        cf[i] = cidx[i] >= 0 ? __ldg(M.coef + cidx[i]) : 0.0;
+        lh[i] = hidx[i] >= 0 ? __ldg(M.lhet + hidx[i]) : 0.0;
+    }
+    float p[10];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        float v;
+        if (hidx[i] < 0) {                                            /* homozygous :186-197 */
+            v = cidx[i] >= 0 ? __double2float_rn(__dadd_rn((double)t1v[i], cf[i])) : 0.0f;
+        } else {                                                      /* heterozygous :199-210 */
+            const double base = __dmul_rn(-4.343, lh[i]);
+            v = cidx[i] >= 0 ? __double2float_rn(__dadd_rn(__dadd_rn(base, (double)t1v[i]), cf[i]))
+                             : __double2float_rn(base);
+        }
+        p[i] = v < 0.0f ? 0.0f : v;                                   /* :212-213 */
+    }
+    /* the p[k,k] correction, :216-233. diagonal positions in GLF order: 0,4,7,9 */
+    {
+        float max1 = -1.0f, max2 = -1.0f, min1 = 1e30f, min2 = 1e30f;
+        int max_k = -1, min_k = -1;
+        const float d[4] = {p[0], p[4], p[7], p[9]};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (es[k] > max1) { max2 = max1; max1 = es[k]; max_k = k; }
+            else if (es[k] > max2) max2 = es[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (d[k] < min1) { min2 = min1; min1 = d[k]; min_k = k; }
+            else if (d[k] < min2) min2 = d[k];
+        }
+        if (max1 > max2 && (min_k != max_k || (double)min1 + 1.0 > (double)min2)) {
+            const float nv = min1 > 1.0f ? __double2float_rn((double)min1 - 1.0) : 0.0f;
+            if (max_k == 0) p[0] = nv;
+            else if (max_k == 1) p[4] = nv;
+            else if (max_k == 2) p[7] = nv;
+            else p[9] = nv;
+        }
+    }
+    /* quantisation :235-244 */
+    float min_p = 1e30f;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) min_p = p[i] < min_p ? p[i] : min_p;
+    g.min_lk = min_p > 255.0f ? 255u : (uint32_t)(int)((double)min_p + 0.5);
+    g.lk[0] = g.lk[1] = g.lk[2] = 0;
+    int lkv[10];
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const float dlt = __fsub_rn(p[i], min_p);
+        lkv[i] = dlt > 255.0f ? 255 : (int)((double)dlt + 0.5);
+        g.lk[i >> 2] |= (uint32_t)lkv[i] << (8 * (i & 3));
+    }
+    /* consensus, sniper_glf2cns :250-273: scan order i<<2|j over i<=j == GLF order */
+    {
+        int mn = 10000, mn2 = 10000, mn3 = 10000, g1 = -1, g2 = -1;
+        int gi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int j = i; j < 4; ++j) {
+                const int t = lkv[gi] + (i == j ? 0 : M.q_r_int);
+                const int code = (1 << i) | (1 << j);
+                if (t < mn) { mn3 = mn2; mn2 = mn; mn = t; g2 = g1; g1 = code; }
+                else if (t < mn2) { mn3 = mn2; mn2 = t; g2 = code; }
+                else if (t < mn3) mn3 = t;
+                ++gi;
+            }
+        }
+        uint32_t x = (uint32_t)(g1 >= 0 ? g1 : 0xf) << 28;
+        x |= (uint32_t)(g2 >= 0 ? g2 : 0xf) << 24;
+        x |= g.rms << 16;
+        x |= (uint32_t)(mn2 < 10000 ? min(mn2 - mn, 255) : 0xff) << 8;
+        x |= (uint32_t)((mn2 < 10000 && mn3 < 10000) ? min(mn3 - mn2, 255) : 0xff);
+        g.cns = x;
+    }
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* somatic score (lane-local, rare branch)                                                      */
+
+__device__ __forceinline__ int qadd(const int32_t *qt, int x, int y) { return x + qt[512 + y - x]; }
+
+__device__ __forceinline__ int genotype_mask_of(int i)
+{
+    /* glfBase, somatic_sniper.c:26 */
+    return (int)((0x8C4A629531ull >> (4 * (unsigned)i)) & 0xf);
+}
+
+struct Call {
+    int score, t_vaq, n_vaq, jT, jN, jgq, tg, ng;
+    bool candidate, pass;
+};
+
+__device__ void score_column(const DevModel &M, const int32_t *qadd_s, const int32_t *prior_s, int rb4,
+                             const Glf &gt, const Glf &gn, Call &out)
+{
+    const int tb1 = gt.cns >> 28, tb2 = (gt.cns >> 24) & 0xf, ts1 = (gt.cns >> 8) & 0xff, ts2 = gt.cns & 0xff;
+    const int nb1 = gn.cns >> 28, nb2 = (gn.cns >> 24) & 0xf, ns1 = (gn.cns >> 8) & 0xff, ns2 = gn.cns & 0xff;
+    out.score = 255; out.t_vaq = 0; out.n_vaq = 0; out.jT = 0; out.jN = 0; out.jgq = 255;
+    out.tg = tb1; out.ng = nb1; out.pass = false;
+    out.candidate = rb4 != 15 && tb1 != 15 && nb1 != 15 && tb1 != nb1;             /* somatic_sniper.c:156 */
+    if (!out.candidate) return;
+    out.t_vaq = min(tb2 == rb4 ? ts1 : ts1 + ts2, 255);                             /* :157-164 */
+    if (nb1 != rb4) out.n_vaq = min(nb2 == rb4 ? ns1 : ns1 + ns2, 255);
+    int score = 255;
+    if (M.use_joint) {                                                              /* :170-208 */
+        int marg = 255, best = 1000, bi = -1, bj = -1;
+        const int32_t *jp = M.jointprior + rb4 * 100;
+        for (int i = 0; i < 10; ++i) {
+            const int ln = (int)glf_lk(gn, i);
+            for (int j = 0; j < 10; ++j) {
+                int v = min(ln + (int)glf_lk(gt, j) + __ldg(jp + i * 10 + j), 255);
+                if (v < best) { best = v; bi = i; bj = j; }
+                marg = qadd(qadd_s, marg, v);
+            }
+        }
+        int jgq = 255;
+        for (int j = 0; j < 10; ++j) {
+            const int v = min((int)glf_lk(gn, j) + (int)glf_lk(gt, j) + __ldg(jp + j * 11), 255);
+            const int l = v - marg;
+            score = qadd(qadd_s, score, l);
+            if (j != bj) jgq = qadd(qadd_s, jgq, l);     /* the reference's other test is always true (:196) */
+        }
+        out.jgq = min(jgq, 255);
+        out.jN = genotype_mask_of(bi); out.jT = genotype_mask_of(bj);
+    } else {                                                                        /* :79-99, :209-214 */
+        int post_t[10], post_n[10], qs_t = 255, qs_n = 255;
+        const int32_t *pr = prior_s + rb4 * 10;
+#pragma unroll
+        for (int j = 0; j < 10; ++j) {
+            post_t[j] = (int)glf_lk(gt, j) + pr[j]; qs_t = qadd(qadd_s, post_t[j], qs_t);
+            post_n[j] = (int)glf_lk(gn, j) + pr[j]; qs_n = qadd(qadd_s, post_n[j], qs_n);
+        }
+#pragma unroll
+        for (int j = 0; j < 10; ++j) {
+            const int y = min(post_t[j] - qs_t, 255) + min(post_n[j] - qs_n, 255);
+            score = qadd(qadd_s, score, y);
+        }
+    }
+    out.score = score;
+    const int tg = out.jT ? out.jT : tb1, ng = out.jN ? out.jN : nb1;               /* :216-223 */
+    out.tg = tg; out.ng = ng;
+    const bool loh = ng != tg && (tg & ng) == tg;                                   /* allele_util.c:19-22 */
+    const bool gor = !(ng != rb4 && (rb4 & ng) == rb4) && (tg & ~ng) == rb4;        /* allele_util.c:25-28 */
+    out.pass = M.min_somatic_qual <= score && (M.include_loh || !loh) && (M.include_gor || !gor);
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* warp-cooperative site statistics for one sample of one column (dqstats.c:6-53)               */
+
+__device__ void site_stats(const DevBatch &B, uint32_t e0, int n, int rb4, uint32_t wanted, int lane, uint32_t *st /*18, smem*/)
+{
+    uint32_t sum_mq = 0, dp4[4] = {0, 0, 0, 0}, occ[4] = {0, 0, 0, 0}, sbq[4] = {0, 0, 0, 0}, smq[4] = {0, 0, 0, 0};
+    for (int i = lane; i < n; i += 32) {
+        const uint32_t bs = B.bs[e0 + i], bq = B.bq[e0 + i], mq = B.mq[e0 + i];
+        const uint32_t base = bs & 15u, strand = (bs >> 4) & 1u;
+        sum_mq += mq;
+        const uint32_t d = ((int)base == rb4 ? 0u : 2u) + strand;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            dp4[j] += d == (uint32_t)j;
+            if ((base & (1u << j)) == base) {
+                ++occ[j];
+                if (wanted & (1u << j)) { sbq[j] += bq; smq[j] += mq; }
+            }
+        }
+    }
+    sum_mq = __reduce_add_sync(kFull, sum_mq);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        dp4[j] = __reduce_add_sync(kFull, dp4[j]); occ[j] = __reduce_add_sync(kFull, occ[j]);
+        sbq[j] = __reduce_add_sync(kFull, sbq[j]); smq[j] = __reduce_add_sync(kFull, smq[j]);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            st[j] = occ[j] ? (uint32_t)((double)sbq[j] / (double)occ[j] + .499) : sbq[j];
+            st[4 + j] = occ[j] ? (uint32_t)((double)smq[j] / (double)occ[j] + .499) : smq[j];
+            st[8 + j] = occ[j]; st[12 + j] = dp4[j];
+        }
+        st[16] = (uint32_t)n;
+        st[17] = n > 0 ? (uint32_t)((double)sum_mq / (double)n + .499) : 0u;
+    }
+}
+
+/* -------------------------------------------------------------------------------------------- */
+
+__device__ __forceinline__ int run_R(int len) { return len <= 64 ? 1 : len <= 128 ? 2 : len <= 256 ? 4 : len <= 512 ? 8 : 16; }
+
+template <bool DUMP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+ssn_score_kernel(const DevModel M, const DevBatch B)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *fk_s = reinterpret_cast<double*>(smem_raw);                       /* 256 doubles */
+    int32_t *qadd_s = reinterpret_cast<int32_t*>(smem_raw + 2048);            /* 1024 + pad  */
+    int32_t *prior_s = qadd_s + 1024 + 64;                                    /* 160         */
+    uint32_t *warp_base = reinterpret_cast<uint32_t*>(prior_s + 160);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) fk_s[i] = M.fk[i];
+    for (int i = threadIdx.x; i < 1024 + 64; i += blockDim.x) qadd_s[i] = M.qadd[i];
+    for (int i = threadIdx.x; i < 160; i += blockDim.x) prior_s[i] = M.prior[i];
+    __syncthreads();
+    uint32_t *slots = warp_base + (size_t)warp * (kSlotWords + B.smem_words_per_warp);
+    uint32_t *keys_s = slots + kSlotWords;
+    const uint32_t gwarp = blockIdx.x * kWarpsPerCta + warp;
+    uint32_t *keys_g = B.scratch ? B.scratch + (size_t)gwarp * B.scratch_words_per_warp : nullptr;
+    const uint32_t ntiles = (B.ncol + 31u) >> 5;
+
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(B.site_count + 1, 1u);
+        tile = __shfl_sync(kFull, tile, 0);
+        if (tile >= ntiles) break;
+        const uint32_t col = tile * 32u + lane;
+        const bool live = col < B.ncol;
+        uint32_t o0 = 0, o1 = 0, o2 = 0, ref16 = 15;
+        if (live) {
+            o0 = B.off[2 * col]; o1 = B.off[2 * col + 1]; o2 = B.off[2 * col + 2];
+            ref16 = B.ref_nt16[col] & 15u;
+        }
+        const uint32_t nT = o1 - o0, nN = o2 - o1, n = nT + nN;
+        /* words of key store this column needs: full runs take kRunLen/2, the tail ceil(len/2) */
+        const uint32_t nruns = (n + kRunLen - 1) / kRunLen;
+        const uint32_t words = (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
+        uint32_t incl = words;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(kFull, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const uint32_t wbase = incl - words;
+        const uint32_t tile_words = __shfl_sync(kFull, incl, 31);
+        uint32_t *store = tile_words <= B.smem_words_per_warp ? keys_s : keys_g;
+
+        /* ---------------- FRONT: one column at a time, whole warp ---------------- */
+        uint32_t my_rms_t = 0, my_rms_n = 0;
+        for (int j = 0; j < 32; ++j) {
+            const uint32_t nj = __shfl_sync(kFull, n, j);
+            if (nj == 0) continue;
+            const uint32_t e0 = __shfl_sync(kFull, o0, j);
+            const int nTj = (int)__shfl_sync(kFull, nT, j);
+            const uint32_t refj = __shfl_sync(kFull, ref16, j);
+            uint32_t *dst = store + __shfl_sync(kFull, wbase, j);
+            uint32_t rt = 0, rn = 0;
+            for (uint32_t done = 0; done < nj; done += kRunLen) {
+                const int len = (int)min(nj - done, (uint32_t)kRunLen);
+                const int tl = nTj - (int)done;
+                switch (run_R(len)) {
+                case 1: sort_run<1>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+                case 2: sort_run<2>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+                case 4: sort_run<4>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+                case 8: sort_run<8>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+                default: sort_run<16>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+                }
+                dst += (len + 1) >> 1;
+            }
+            rt = __reduce_add_sync(kFull, rt);
+            rn = __reduce_add_sync(kFull, rn);
+            if (lane == j) { my_rms_t = rt; my_rms_n = rn; }
+        }
+        for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
+        __syncwarp();
+
+        /* ---------------- BACK: one column per lane ---------------- */
+        {
+            Chain ch; ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0; ch.sb = -1;
+            const uint16_t *k16 = reinterpret_cast<const uint16_t*>(store + wbase);
+            if (nruns <= 1) {
+                for (int idx = 2 * (int)words - 1; idx >= 0; --idx) {
+                    const uint32_t key = k16[idx];
+                    if (key == 0) break;
+                    chain_step(ch, key, fk_s, slots, lane);
+                }
+            } else {
+                /* k-way merge of the sorted runs (deep columns): heads live in local memory */
+                int hp[kMaxRuns];
+                uint16_t hk[kMaxRuns];
+                for (uint32_t r = 0; r < nruns; ++r) {
+                    const uint32_t len = min(n - r * kRunLen, (uint32_t)kRunLen);
+                    hp[r] = (int)(r * kRunLen + 2 * ((len + 1) >> 1)) - 1;
+                    hk[r] = k16[hp[r]];
+                }
+                for (;;) {
+                    uint32_t best = 0, br = 0;
+                    for (uint32_t r = 0; r < nruns; ++r)
+                        if (hk[r] > best) { best = hk[r]; br = r; }
+                    if (best == 0) break;
+                    chain_step(ch, best, fk_s, slots, lane);
+                    const int np = hp[br] - 1;
+                    hp[br] = np;
+                    hk[br] = np >= (int)(br * kRunLen) ? k16[np] : (uint16_t)0;
+                }
+            }
+            chain_flush(ch, slots, lane);
+        }
+        __syncwarp();
+
+        Glf gt, gn;
+        gt.lk[0] = gt.lk[1] = gt.lk[2] = 0; gt.min_lk = 0; gt.rms = 0; gt.cns = 0xff000000u;
+        gn = gt;
+        if (nT) sample_glf(M, slots, lane, 1, nT, my_rms_t, gt);
+        if (nN) sample_glf(M, slots, lane, 0, nN, my_rms_n, gn);
+        Call call;
+        call.score = -1; call.pass = false; call.candidate = false;
+        if (nT && nN && ref16 != 15u) score_column(M, qadd_s, prior_s, (int)ref16, gt, gn, call);
+
+        if (DUMP && live) {
+            uint32_t *o = B.coldump + (size_t)col * SSN_COLUMN_DUMP_WORDS;
+#pragma unroll
+            for (int i = 0; i < 10; ++i) { o[i] = glf_lk(gt, i); o[14 + i] = glf_lk(gn, i); }
+            o[10] = gt.min_lk; o[11] = gt.rms; o[12] = min(nT, 16777215u); o[13] = gt.cns;
+            o[24] = gn.min_lk; o[25] = gn.rms; o[26] = min(nN, 16777215u); o[27] = gn.cns;
+            o[28] = (uint32_t)call.score;
+        }
+
+        /* ---------------- EMIT: compact passing sites (warp ballot), stats warp-cooperatively ---------------- */
+        uint32_t pass_mask = __ballot_sync(kFull, call.pass);
+        if (pass_mask) {
+            uint32_t base_slot = 0;
+            if (lane == 0) base_slot = atomicAdd(B.site_count, (uint32_t)__popc(pass_mask));
+            base_slot = __shfl_sync(kFull, base_slot, 0);
+            uint32_t rank = 0;
+            while (pass_mask) {
+                const int j = __ffs(pass_mask) - 1;
+                pass_mask &= pass_mask - 1;
+                uint32_t *rec = slots;   /* 54-word staging area, chains are done with it */
+                __syncwarp();
+                const uint32_t e0 = __shfl_sync(kFull, o0, j), e1 = __shfl_sync(kFull, o1, j);
+                const int nTj = (int)__shfl_sync(kFull, nT, j), nNj = (int)__shfl_sync(kFull, nN, j);
+                const int rb4 = (int)__shfl_sync(kFull, ref16, j);
+                const uint32_t wanted = (uint32_t)(rb4 | __shfl_sync(kFull, call.tg, j) | __shfl_sync(kFull, call.ng, j));
+                site_stats(B, e0, nTj, rb4, wanted, lane, rec + 9);
+                site_stats(B, e1, nNj, rb4, wanted, lane, rec + 9 + 26);
+                if (lane == j) {
+                    const int tb1 = gt.cns >> 28, nb1 = gn.cns >> 28;
+                    rec[0] = col; rec[1] = (uint32_t)rb4;
+                    uint32_t *t = rec + 2, *nn = rec + 28;
+                    t[0] = tb1; t[1] = call.jT; t[2] = call.jgq; t[3] = (gt.cns >> 8) & 0xff; t[4] = call.t_vaq;
+                    t[5] = (uint32_t)call.score;
+                    const bool loh = call.ng != call.tg && (call.tg & call.ng) == call.tg;
+                    t[6] = call.tg == call.ng ? 1u : loh ? 3u : call.score > 0 ? 2u : 4u;   /* somatic_sniper.c:241-248 */
+                    t[25] = gt.rms;
+                    nn[0] = nb1; nn[1] = call.jN; nn[2] = call.jgq; nn[3] = (gn.cns >> 8) & 0xff; nn[4] = call.n_vaq;
+                    nn[5] = (uint32_t)-1;
+                    nn[6] = nb1 == rb4 ? 0u : 1u;                                            /* :258-261 */
+                    nn[25] = gn.rms;
+                }
+                __syncwarp();
+                const uint32_t slot = base_slot + rank++;
+                if (slot < B.site_cap) {
+                    uint32_t *dst = reinterpret_cast<uint32_t*>(B.sites + slot);
+                    for (int i = lane; i < (int)(sizeof(ssn_site) / 4); i += 32) dst[i] = rec[i];
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
+
+}  // namespace ssn

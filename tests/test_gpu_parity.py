@@ -1,0 +1,163 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bar: bit-exact. Every quantity compared is an integer (quantised GLFs, consensus words, Phred scores,
+site statistics); the float intermediates only exist in registers and are pinned through them.
+"""
+import numpy as np
+import pytest
+
+from conftest import CONFIGS, oracle_kwargs, ssn_params
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mods(built):
+    from oracle.loader import Oracle
+    from somatic_sniper_b200 import api, synth
+    return api, synth, Oracle
+
+
+def _normalise_oracle_score(score, ref_char, api):
+    """The kernel sees only ref_nt16; a lower-case 'n' (nt16 15) reports -1 like 'N' does (no call either way)."""
+    s = score.copy()
+    s[api.nt16_lut()[ref_char] == 15] = -1
+    return s
+
+
+def check_batch(api, Oracle, cols, cfg="default", scorer=None):
+    own = scorer is None
+    sc = scorer or api.Scorer(ssn_params(cfg), n_slots=1, max_columns=max(cols["ncol"], 1),
+                              max_entries=int(cols["n_entries"]) + 64)
+    try:
+        sites, dump = sc.score(cols, dump=True)
+    finally:
+        if own:
+            sc.close()
+    want = Oracle(**oracle_kwargs(cfg)).score_batch(cols["off"], cols["bs"], cols["bq"], cols["mq"], cols["ref_char"],
+                                                    want_glf=True)
+    bad = np.nonzero((dump[:, :28] != want["glf"]).any(axis=1))[0]
+    assert bad.size == 0, "GLF/consensus mismatch in %d columns, first %d:\n got %s\nwant %s" % (
+        bad.size, bad[0], dump[bad[0], :28], want["glf"][bad[0]])
+    wscore = _normalise_oracle_score(want["score"], cols["ref_char"], api)
+    assert np.array_equal(dump[:, 28].astype(np.int32), wscore)
+    assert np.array_equal(sites["column"].astype(np.int64), want["emit_col"].astype(np.int64)), "called-site set differs"
+    got = api.sites_to_records(sites, cols["ref_char"])
+    assert np.array_equal(got, want["recs"]), "site records differ"
+    # RMS mapQ travels in the site too (north star: 'RMS mapQ')
+    if len(sites):
+        assert np.array_equal(sites["tumor"]["rms_mapq"], want["glf"][want["emit_col"], 11])
+        assert np.array_equal(sites["normal"]["rms_mapq"], want["glf"][want["emit_col"], 25])
+    return len(sites)
+
+
+def test_known_answer_columns(mods):
+    api, synth, Oracle = mods
+    cols = synth.kat_columns()
+    sc = api.Scorer(ssn_params("default"), n_slots=1, max_columns=8, max_entries=8192)
+    sites, dump = sc.score(cols, dump=True)
+    sc.close()
+    # SURVEY.md App. C.3 (values dumped from the unmodified reference)
+    assert list(dump[0, :14]) == [30, 0, 54, 54, 161, 167, 167, 230, 230, 230, 14, 60, 10, 0x313c0333]
+    assert list(dump[1, :14]) == [238, 255, 0, 255, 255, 255, 255, 255, 255, 255, 28, 60, 58, 0x513cd311]
+    assert list(dump[1, 14:28]) == [0, 90, 90, 90, 255, 255, 255, 255, 255, 255, 0, 60, 30, 0x133c7500]
+    assert list(dump[2, :14]) == [0, 155, 255, 255, 255, 255, 255, 255, 255, 255, 255, 52, 1458, 0x1334b649]
+    assert list(dump[2, 14:28]) == [0, 255, 255, 255, 255, 255, 255, 255, 255, 255, 0, 60, 1502, 0x123cff00]
+    assert list(dump[3, :14]) == [2, 8, 8, 0, 40, 40, 29, 40, 29, 13, 8, 32, 7, 0x18200b0e]
+    assert list(dump[3, 14:28]) == [0, 6, 6, 1, 74, 74, 69, 74, 69, 66, 4, 60, 3, 0x193c1c05]
+    assert list(sites["column"]) == [1]
+    t, n = sites["tumor"][0], sites["normal"][0]
+    assert (t["somatic_score"], t["genotype"], n["genotype"], t["consensus_quality"], t["variant_allele_quality"],
+            n["consensus_quality"], n["variant_allele_quality"], t["variant_status"]) == (120, 5, 1, 211, 211, 117, 0, 2)
+    assert (t["total_mean_mapQ"], n["total_mean_mapQ"]) == (60, 60)
+    check_batch(api, Oracle, cols)
+    check_batch(api, Oracle, cols, "joint")
+
+
+@pytest.mark.parametrize("cfg", list(CONFIGS))
+def test_random_columns_all_configs(mods, cfg):
+    api, synth, Oracle = mods
+    cols = synth.make_columns(20000, seed=11, p_som=5e-3, p_het=5e-3, p_loh=2e-3, p_gor=2e-3)
+    n = check_batch(api, Oracle, cols, cfg)
+    assert n > 0 or cfg == "joint"
+
+
+@pytest.mark.parametrize("seed,binned", [(1, True), (2, False), (3, True)])
+def test_edge_case_columns(mods, seed, binned):
+    api, synth, Oracle = mods
+    cols = synth.make_columns(20000, seed=seed, binned=binned, edge=1.0, p_som=5e-3, p_het=5e-3, p_loh=2e-3, p_gor=2e-3)
+    check_batch(api, Oracle, cols, "nopriors_q0")
+    check_batch(api, Oracle, cols, "joint_s")
+
+
+def test_ragged_and_boundary_depths(mods):
+    api, synth, Oracle = mods
+    rng = np.random.default_rng(5)
+    depths = [1, 2, 3, 31, 32, 33, 63, 64, 65, 127, 128, 129, 255, 256, 257, 511, 512, 513, 1023, 1024, 1025, 2047,
+              2048, 2049, 3000, 5000]
+    cols = []
+    for i, d in enumerate(depths):
+        for nn in (1, d, max(1, d // 2)):
+            def ent(k, alt_frac):
+                out = []
+                for _ in range(k):
+                    b = "ACGT"[(i + (rng.random() < alt_frac)) & 3]
+                    out.append((b, int(rng.choice([2, 12, 23, 37, 41])), int(rng.choice([0, 20, 60, 60, 60])), int(rng.random() < 0.5)))
+                return out
+            cols.append(("ACGT"[i & 3], ent(d, 0.3), ent(nn, 0.02)))
+    batch = synth.columns_from_lists(cols)
+    check_batch(api, Oracle, batch, "nopriors_q0")
+    check_batch(api, Oracle, batch, "joint_s")
+
+
+def test_deep_panel_columns(mods):
+    api, synth, Oracle = mods
+    cols = synth.make_columns(600, depth_t=1500, depth_n=1200, seed=21, binned=False, p_som=2e-2, p_het=2e-2)
+    check_batch(api, Oracle, cols, "nopriors_q0")
+    cols = synth.make_columns(300, depth_t=2000, depth_n=1000, seed=22, binned=True, edge=0.5, p_som=2e-2)
+    check_batch(api, Oracle, cols, "default")
+
+
+def test_empty_and_single(mods):
+    api, synth, Oracle = mods
+    sc = api.Scorer(ssn_params("default"), n_slots=2, max_columns=64, max_entries=4096)
+    empty = dict(off=np.zeros(1, np.uint32), bs=np.zeros(0, np.uint8), bq=np.zeros(0, np.uint8), mq=np.zeros(0, np.uint8),
+                 ref_char=np.zeros(0, np.uint8), ncol=0, n_entries=0)
+    sites, _ = sc.score(empty)
+    assert len(sites) == 0
+    one = synth.columns_from_lists([("A", [("C", 40, 60, 0)] * 12 + [("C", 40, 60, 1)] * 9, [("A", 40, 60, 0)] * 8 + [("A", 38, 60, 1)] * 9)])
+    check_batch(api, Oracle, one, scorer=sc)
+    # a column where one sample has no bases scores nothing
+    half = synth.columns_from_lists([("A", [("C", 40, 60, 0)] * 5, []), ("A", [], [("A", 40, 60, 0)] * 5)])
+    sites, dump = sc.score(half, dump=True)
+    assert len(sites) == 0 and list(dump[:, 28].astype(np.int32)) == [-1, -1]
+    sc.close()
+
+
+def test_full_size_properties(mods):
+    """BASELINE config #2 size (1 Mb, 30x/60x): size-independent properties + oracle on a sample of tiles."""
+    api, synth, Oracle = mods
+    cols = synth.make_columns(1_000_000, seed=1234)
+    sc = api.Scorer(ssn_params("default"), n_slots=2, max_columns=1_000_000, max_entries=int(cols["n_entries"]) + 64)
+    s1, d1 = sc.score(cols, dump=True)
+    s2, d2 = sc.score(cols, dump=True)
+    assert np.array_equal(d1, d2) and np.array_equal(s1, s2)          # idempotent / deterministic
+    # order of read-bases inside a sample is not observable: shuffle each sample segment
+    rng = np.random.default_rng(9)
+    off = cols["off"].astype(np.int64)
+    seg = np.repeat(np.arange(len(off) - 1), np.diff(off))
+    perm = np.lexsort((rng.random(len(seg)), seg))
+    shuf = dict(cols, bs=cols["bs"][perm], bq=cols["bq"][perm], mq=cols["mq"][perm])
+    s3, d3 = sc.score(shuf, dump=True)
+    assert np.array_equal(d1, d3) and np.array_equal(s1, s3)
+    sc.close()
+    # oracle on every 16th block of 4096 columns
+    o = Oracle()
+    for start in range(0, cols["ncol"], 16 * 4096):
+        c0, c1 = start, min(start + 4096, cols["ncol"])
+        e0, e1 = int(off[2 * c0]), int(off[2 * c1])
+        want = o.score_batch((off[2 * c0:2 * c1 + 1] - e0).astype(np.uint32), cols["bs"][e0:e1], cols["bq"][e0:e1],
+                             cols["mq"][e0:e1], cols["ref_char"][c0:c1], want_glf=True)
+        assert np.array_equal(d1[c0:c1, :28], want["glf"])
+        sel = (s1["column"] >= c0) & (s1["column"] < c1)
+        assert np.array_equal(s1["column"][sel] - c0, want["emit_col"])
