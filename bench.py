@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py — pileup columns/s scored (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (libssn.so, C ABI)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU code on the host cores
+
+A step = one pass of the hot path over one batch of synthetic columns.  Workload at every N:
+BASELINE.json configs[1] — a synthetic 1 Mb region, normal 30x / tumor 60x, default options
+(-Q 15, independent priors): 1,000,000 columns per GPU (weak scaling: region shards are independent,
+no collective on the data path; torch.distributed only carries the barrier and the max-over-ranks).
+
+value      columns/s, all ranks, batches already resident in HBM, timed with CUDA events
+e2e        the same through ssn_batch_submit/ssn_results_next with pinned HOST batches:
+           H2D of every column + kernel + D2H of the site ring inside the timed region
+roofline   HBM: algorithmic bytes (3 B per read-base + 9 B per column) per launch /
+           the kernel's mean launch duration (events around each launch on its own stream)
+cpu_baseline  the unmodified reference (oracle/_ref, 1 thread) on a bounded sample, rank 0, N=1 only
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pileup_columns_per_sec_scored"
+UNIT = "columns/s"
+COLUMNS = 1_000_000
+CHUNKS = 8                      # e2e: the step's columns travel as 8 pinned batches on 8 streams
+WORKLOAD = "synthetic 1 Mb region, normal 30x / tumor 60x, -Q 15 independent priors (BASELINE configs[1])"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--columns", type=int, default=COLUMNS)
+    ap.add_argument("--depth-t", type=float, default=60.0)
+    ap.add_argument("--depth-n", type=float, default=30.0)
+    ap.add_argument("--cpu-sample", type=int, default=1_000_000, help="columns of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """dram bytes per launch of the scoring kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.proc, self.rows = device, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 7:
+                self.rows.append(f)
+        self.proc = None
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for f in self.rows:
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def slice_columns(cols, c0, c1):
+    off = cols["off"].astype(np.int64)
+    e0, e1 = int(off[2 * c0]), int(off[2 * c1])
+    return dict(off=(off[2 * c0:2 * c1 + 1] - e0).astype(np.uint32), bs=cols["bs"][e0:e1], bq=cols["bq"][e0:e1],
+                mq=cols["mq"][e0:e1], ref_char=cols["ref_char"][c0:c1], ncol=c1 - c0, n_entries=e1 - e0)
+
+
+def dist_setup(n):
+    """torch.distributed is plumbing only: barrier + max over ranks."""
+    if n <= 1:
+        return None, 0, 0
+    import torch
+    import torch.distributed as dist
+    rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return dist, rank, local
+
+
+def dist_barrier(dist):
+    if dist is not None:
+        import torch
+        dist.barrier()
+        torch.cuda.synchronize()
+
+
+def dist_max(dist, x):
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def dist_sum(dist, x):
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arms (the only places bench.py executes anything under oracle/)
+
+_W = {}
+
+
+def _cpu_worker_init(kind):
+    from oracle.loader import Oracle, Reference
+    _W["impl"] = Reference() if kind == "reference" else Oracle()
+
+
+def _cpu_worker_run(shard):
+    if isinstance(shard, int):          # forked workers inherit the shards; only the index travels
+        shard = _W["shards"][shard]
+    r = _W["impl"].score_batch(shard["off"], shard["bs"], shard["bq"], shard["mq"], shard["ref_char"], max_recs=4096)
+    return int(r["n_emit"])
+
+
+def cpu_kind():
+    from oracle.loader import Reference
+    return "reference" if Reference.available() else "port"
+
+
+def cpu_baseline_single(cols, sample_cols):
+    """The reference's per-column path (glf_somatic over fabricated pileups), 1 thread, bounded sample."""
+    kind = cpu_kind()
+    _cpu_worker_init(kind)
+    shard = slice_columns(cols, 0, min(sample_cols, cols["ncol"]))
+    t = time.perf_counter()
+    _cpu_worker_run(shard)
+    dt = time.perf_counter() - t
+    return {"value": shard["ncol"] / dt, "unit": UNIT, "cores": 1, "kind": kind,
+            "sample": "first %d columns of the step's batch, %.1f s, oracle/%s" % (
+                shard["ncol"], dt, "_ref/libref_harness.so (unmodified reference)" if kind == "reference" else "ssn_oracle.c")}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    from somatic_sniper_b200 import synth
+    kind = cpu_kind()
+    cores = len(os.sched_getaffinity(0))
+    sample_cols = min(args.columns, args.cpu_sample)
+    cols = synth.make_columns(sample_cols, depth_t=args.depth_t, depth_n=args.depth_n, seed=1234)
+    bounds = np.linspace(0, sample_cols, cores + 1).astype(int)
+    shards = [slice_columns(cols, int(bounds[i]), int(bounds[i + 1])) for i in range(cores)]
+    ctx = mp.get_context("fork")
+    _W["shards"] = shards
+    idx = list(range(cores))
+    with ctx.Pool(cores, initializer=_cpu_worker_init, initargs=(kind,)) as pool:
+        for _ in range(args.warmup):
+            pool.map(_cpu_worker_run, idx, chunksize=1)
+        t = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_cpu_worker_run, idx, chunksize=1)
+        dt = time.perf_counter() - t
+    value = sample_cols * args.steps / dt
+    sample = "%d columns per step region-split over %d processes, oracle/%s" % (
+        sample_cols, cores, "_ref (unmodified reference glf_somatic)" if kind == "reference" else "ssn_oracle.c port")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64/f32+int", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "columns_per_step": sample_cols, "depth_tumor": args.depth_t,
+                       "depth_normal": args.depth_n},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+
+def run_b200(args):
+    from somatic_sniper_b200 import api, synth
+    dist, rank, local = dist_setup(args.gpus)
+    ncol = args.columns
+    cols = synth.make_columns(ncol, depth_t=args.depth_t, depth_n=args.depth_n, seed=1234 + rank)
+    nent = int(cols["n_entries"])
+    alg_bytes = synth.algorithmic_bytes(cols)
+    bounds = np.linspace(0, ncol, CHUNKS + 1).astype(int)
+    chunks = [slice_columns(cols, int(bounds[i]), int(bounds[i + 1])) for i in range(CHUNKS)]
+
+    # ---- value: resident batch, kernel only --------------------------------------------------------
+    sc = api.Scorer(api.default_params(), device=local, n_slots=1, max_columns=ncol, max_entries=nent + 64)
+    b = sc.acquire()
+    b.fill(cols)
+    sc.upload(b)
+    for _ in range(max(args.warmup, 3)):
+        sc.score_resident(b)
+    sc.sync()
+    sites_ref = sc.fetch(b)
+    sc.kernel_time(reset=True)
+    l0 = sc.kernel_launches()
+    sampler = ClockSampler(local)
+    sampler.start()
+    dist_barrier(dist)
+    sc.sync()
+    sc.timer_start()
+    for _ in range(args.steps):
+        sc.score_resident(b)
+    ms = sc.timer_stop()
+    dist_barrier(dist)
+    sampler.stop()
+    launches = sc.kernel_launches() - l0
+    kms, kn = sc.kernel_time(reset=True)
+    n_sites = len(sites_ref)
+    sc.release(b)
+    sc.close()
+    ms_max = dist_max(dist, ms)
+    total_cols = dist_sum(dist, float(ncol))
+    value = total_cols * args.steps / (ms_max * 1e-3)
+    peak, peak_src = measured_peak()
+    k_avg_ms = kms / max(kn, 1)
+    achieved = alg_bytes / (k_avg_ms * 1e-3) / 1e9
+
+    # ---- e2e: pinned host batches through submit/results_next ----------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        cmax = max(c["ncol"] for c in chunks)
+        emax = max(int(c["n_entries"]) for c in chunks)
+        sc = api.Scorer(api.default_params(), device=local, n_slots=CHUNKS, max_columns=cmax, max_entries=emax + 64)
+        slots = []
+        for c in chunks:                       # the packer's job: columns land in pinned memory once
+            bb = sc.acquire()
+            bb.fill(c)
+            slots.append((bb, c["ncol"], int(c["n_entries"])))
+
+        def one_step():
+            got = 0
+            for bb, nc, ne in slots:
+                sc.submit(bb)
+            for _ in slots:
+                s, _h = sc.results_next()
+                got += len(s)
+            for i, (bb, nc, ne) in enumerate(slots):   # same pinned contents travel again next step
+                nb = sc.acquire()
+                assert nb.h.value == bb.h.value
+                nb.set_size(nc, ne)
+                slots[i] = (nb, nc, ne)
+            return got
+
+        for _ in range(max(args.warmup, 3)):
+            got = one_step()
+        assert got == n_sites, "e2e path found %d sites, resident path %d" % (got, n_sites)
+        dist_barrier(dist)
+        sc.sync()
+        sc.timer_start()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            one_step()
+        ems = sc.timer_stop()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        dist_barrier(dist)
+        sc.close()
+        ems = max(ems, wall_ms)                # host work (submit, sort of sites) counts too
+        ems_max = dist_max(dist, ems)
+        e2e = {"value": total_cols * args.steps / (ems_max * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": 3 * nent + 4 * (2 * ncol + CHUNKS) + ncol,
+               "d2h_bytes_per_step": 8 * CHUNKS + 216 * n_sites, "ms_per_step": ems_max / args.steps,
+               "batches_per_step": CHUNKS}
+
+    if rank != 0:
+        return
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64/f32+int", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "columns_per_gpu_per_step": ncol, "read_bases_per_step": nent,
+                       "depth_tumor": args.depth_t, "depth_normal": args.depth_n, "sites_per_step": n_sites,
+                       "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (alg_bytes / 1e6),
+                       "parallelism": "region shards, %d GPU(s), no collective" % args.gpus},
+            "clocks": sampler.summary(),
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "ssn_score_kernel<false>",
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": k_avg_ms},
+            }
+    if e2e is not None:
+        line["e2e"] = e2e
+    if args.gpus == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_single(cols, args.cpu_sample)
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
