@@ -161,3 +161,45 @@ def test_full_size_properties(mods):
         assert np.array_equal(d1[c0:c1, :28], want["glf"])
         sel = (s1["column"] >= c0) & (s1["column"] < c1)
         assert np.array_equal(s1["column"][sel] - c0, want["emit_col"])
+
+
+# ---- committed golden fixtures (outputs of the UNMODIFIED reference, tests/golden/make_golden.py) -------------
+
+import os
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _npz_cols(name):
+    c = dict(np.load(os.path.join(GOLD, name)))
+    c.pop("pos", None)
+    c["ncol"] = len(c["ref_char"])
+    c["n_entries"] = len(c["bs"])
+    return c
+
+
+def _check_against_golden(api, cols, want, cfg):
+    sc = api.Scorer(ssn_params(cfg), n_slots=1, max_columns=cols["ncol"], max_entries=cols["n_entries"] + 64)
+    sites, dump = sc.score(cols, dump=True)
+    sc.close()
+    assert np.array_equal(dump[:, :28], want["glf"])
+    assert np.array_equal(dump[:, 28].astype(np.int32), _normalise_oracle_score(want["score"], cols["ref_char"], api))
+    assert np.array_equal(sites["column"].astype(np.int64), want["emit_col"].astype(np.int64))
+    assert np.array_equal(api.sites_to_records(sites, cols["ref_char"])[:, :53], want["recs"][:, :53])
+
+
+@pytest.mark.parametrize("cfg", list(CONFIGS))
+def test_reference_golden_columns(mods, cfg):
+    api, _, _ = mods
+    _check_against_golden(api, _npz_cols("columns_in.npz"), np.load(os.path.join(GOLD, "columns_%s.npz" % cfg)), cfg)
+
+
+@pytest.mark.parametrize("cfg", ["default", "joint_s", "nopriors_q0"])
+def test_reference_integration_columns(mods, cfg):
+    """The pileup columns of the reference's integration-test BAM pair; 'default' holds the 3 expected.vcf sites."""
+    api, _, _ = mods
+    want = np.load(os.path.join(GOLD, "integration_%s.npz" % cfg))
+    _check_against_golden(api, _npz_cols("integration.npz"), want, cfg)
+    if cfg == "default":
+        pos = np.load(os.path.join(GOLD, "integration.npz"))["pos"]
+        assert [int(pos[c]) + 1 for c in want["emit_col"]] == [63, 73, 260]
