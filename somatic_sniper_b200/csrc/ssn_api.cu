@@ -86,7 +86,7 @@ struct ssn_ctx {
     cudaEvent_t t0, t1;
     uint64_t launches;
     int num_sms, ctas_per_sm_cap;
-    size_t smem_optin;
+    size_t smem_optin, smem_static;
     uint32_t smem_words_default;
     uint32_t *d_scratch; size_t scratch_words;   /* global key store, all warps */
     uint32_t grid_cap;                          /* largest grid ever launched (scratch sizing) */
@@ -121,7 +121,8 @@ extern "C" int ssn_nt16_of_char(int ch)
 
 static size_t smem_bytes_for(uint32_t words_per_warp)
 {
-    return 2048 + (1024 + 64) * 4 + 160 * 4 + (size_t)kWarpsPerCta * (kSlotWords + words_per_warp) * 4;
+    /* dynamic part only; the model tables and key LUTs are static shared memory (CtaTables) */
+    return (size_t)kWarpsPerCta * (kAuxWords + words_per_warp) * 4;
 }
 
 static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, uint64_t max_entries)
@@ -180,7 +181,8 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->d_scratch = nullptr; ctx->scratch_words = 0; ctx->grid_cap = 0; ctx->d_flush = nullptr; ctx->flush_bytes = 0;
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
     const char *env = getenv("SSN_SMEM_WORDS");
-    ctx->smem_words_default = env ? (uint32_t)atoi(env) : 2048u;
+    ctx->smem_words_default = env ? (uint32_t)atoi(env) : (uint32_t)kFastWords * 32u;
+    ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
     if (ssn_tables_build(p, &ctx->tab) != 0) { ssn_set_error("ssn_create: table construction failed (n_hap=%d)", p->n_hap); delete ctx; return SSN_ERR_ARG; }
 
     const size_t coef_n = (size_t)64 * 65536, lhet_n = 65536;
@@ -205,8 +207,12 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&ctx->t0));
     CU(cudaEventCreate(&ctx->t1));
-    CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_optin));
-    CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_optin));
+    cudaFuncAttributes fa;
+    CU(cudaFuncGetAttributes(&fa, ssn_score_kernel<true>));
+    ctx->smem_static = fa.sharedSizeBytes;
+    const int max_dyn = (int)(ctx->smem_optin - ctx->smem_static);
+    CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+    CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
 
     /* keep coef+lhet resident in L2: persisting carve-out + per-stream access-policy window */
     size_t want = sizeof(double) * (coef_n + lhet_n);
@@ -384,13 +390,11 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
             b->d_dump_words = b->h_dump_words = need;
         }
     }
-    /* shared-memory key store per warp: big enough for the batch's largest tile when that is
-     * affordable, else the default and the oversized tiles go through the global scratch */
-    uint32_t words = ((b->max_tile_words + 63u) / 64u) * 64u;
-    if (words > ctx->smem_words_default) words = ctx->smem_words_default;
-    if (words < 64u) words = 64u;
+    /* shared-memory key store per warp: kFastWords*32 words serve every fast tile (<= 128 key slots per
+     * column); deeper tiles use it too when they fit and the global scratch otherwise */
+    const uint32_t words = ctx->smem_words_default;
     size_t smem = smem_bytes_for(words);
-    if (smem > ctx->smem_optin) { ssn_set_error("shared memory request %zu exceeds %zu", smem, ctx->smem_optin); return SSN_ERR_ARG; }
+    if (smem + ctx->smem_static > ctx->smem_optin) { ssn_set_error("shared memory request %zu exceeds %zu", smem, ctx->smem_optin); return SSN_ERR_ARG; }
     int per_sm = 0;
     if (dump) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ssn_score_kernel<true>, kWarpsPerCta * 32, smem));
     else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ssn_score_kernel<false>, kWarpsPerCta * 32, smem));

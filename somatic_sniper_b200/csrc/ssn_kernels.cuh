@@ -5,12 +5,9 @@
  * columns from an atomic counter.  Each tile runs in two phases inside one warp:
  *
  *  FRONT (warp-per-column, 32 lanes = 32 read-bases at a time; looped over the tile's columns)
- *    load bs/bq/mq coalesced -> 16-bit sort key per read-base -> packed (2 keys / register)
- *    bitonic sort in registers with VIMNMX.U16x2 + SHFL -> sorted keys to the warp's key store
- *    (shared memory; a per-warp global scratch when a tile does not fit) ; REDUX for the mapQ sums.
- *    Tumor and normal are sorted together (sample bit on top of the key).
+ *    load bs/bq/mq coalesced -> 16-bit sort key per read-base -> keys of the tile to shared memory
  *  BACK (lane-per-column, 32 columns in flight per warp)
- *    walk the sorted keys: the strictly sequential float<-double error-dependency chains
+ *    sort the column's keys, walk them: the strictly sequential float<-double error-dependency chains
  *    (sniper_maqcns.c:160-176), then the 10 genotype likelihoods, the p[k,k] correction, the
  *    quantisation, the consensus call (both samples), then the rare somatic-score branch
  *    (somatic_sniper.c:156-227) and, for sites that pass the gate, warp-cooperative site statistics
@@ -24,16 +21,30 @@
  * matters for q in {1,2,3}, where entries with baseQ in {64,128,192} keep q while their neighbours
  * are promoted to 4 (:165).  Hence
  *     key = sample<<15 | b4<<13 | q<<5 | valid<<4 | strand<<3 | sub
- * with sub = 7 for q==0 or q>=4, and 1 + (rank of the baseQ group in
- * {[q,63], 64, [65,127], 128, [129,191], 192, [193,255]}) for q in 1..3.  Entries that contribute
- * nothing (q_eff == 0) get key 0 and sink to the bottom together with the padding.  Descending key
- * order reproduces the reference's chain for every base exactly.
+ * with sub = 1 + rank of baseQ's group in {[0,63], 64, [65,127], 128, [129,191], 192, [193,255]} (1..7, so
+ * a contributing key is never 0; even <=> baseQ in {64,128,192}, the entries that keep q < 4).  For q >= 4 or q == 0 sub only reorders
+ * entries whose contributions are identical.  Entries that contribute nothing (q_eff == 0) get key 0
+ * and sink to the bottom together with the padding.  Descending key order reproduces the reference's
+ * chain for every base exactly.  The class bits come from a shared-memory LUT indexed by
+ * (sample, reference nt16, bs), sub from a 256-entry LUT: a handful of integer instructions per read-base.
+ *
+ * FAST TILES (every column of the tile holds <= 2*NW read-bases per the checks in tile_fits, NW in
+ * {16,32,64}; all of WGS 30x/60x): FRONT writes the keys transposed into a per-warp
+ * [NW words][32 columns] shared-memory array (XOR-swizzled: conflict-free for the column-wise writes
+ * and the lane-wise reads); then each LANE loads its column's NW packed words into registers and
+ * sorts them with a generated odd-even merge-sort network (ssn_sortnet.cuh: VIMNMX.U16x2 only, no
+ * shuffles — 4x fewer issue slots per comparator than a warp-cooperative bitonic sort), stores them
+ * back in walk order and runs the chain.  The tumor keys live in slots [0,nT), the normal keys in
+ * slots from roundup2(nT).
+ * DEEP TILES (panel depths) take the generic path: warp-cooperative bitonic sort of 1024-key runs in
+ * registers (SHFL + VIMNMX) and a per-lane k-way merge during the walk.
  */
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "ssn.h"
+#include "ssn_sortnet.cuh"
 
 #ifndef SSN_ROUND_MAGIC
 #define SSN_ROUND_MAGIC 1 /* 1: (s+M)-M rounding in the FP64 pipe; 0: F2F.F32.F64 + F2F.F64.F32 */
@@ -41,11 +52,25 @@
 
 namespace ssn {
 
-constexpr int kWarpsPerCta = 4;
-constexpr int kRunLen = 1024;          /* keys per sorted run (R = 16 packed registers) */
+constexpr int kWarpsPerCta = 12;        /* one CTA per SM: 12 x (keys 8 KB + raw/slots 9.4 KB) + tables = 223 KB */
+constexpr int kRunLen = 1024;          /* keys per sorted run of the generic path (R = 16 packed registers) */
 constexpr int kMaxRuns = 64;           /* => at most 65536 read-bases per column (tumor + normal) */
 constexpr int kSlotWords = 24 * 32;    /* per warp: 8 (sample,base) slots x {esum,fsum,count} x 32 lanes */
+constexpr int kFastWords = 64;         /* largest NW of the fast path: 128 key slots per column */
+constexpr int kRawBytes = 3200;        /* per array: staged read-bases of one fast tile (16-byte aligned window) */
+constexpr int kAuxWords = 3 * kRawBytes / 4;   /* raw staging; the chain slots alias its head once FRONT is done */
+static_assert(kAuxWords >= kSlotWords, "slots must fit in the raw staging area");
 constexpr unsigned kFull = 0xffffffffu;
+
+/* static shared memory of a CTA: model tables + key LUTs */
+struct CtaTables {
+    double2 fk2[256];            /* {fk[w], fk[w]/32}: the walk multiplies by q*32 taken straight from the key */
+    unsigned long long mbar[kWarpsPerCta];   /* one mbarrier per warp for its bulk copies */
+    int32_t qadd[1024 + 64];
+    int32_t prior[160];
+    uint16_t cls[2 * 16 * 32];   /* [sample][ref nt16][bs & 31] -> sample<<15 | b4<<13 | valid<<4 | strand<<3 */
+    uint8_t sub[256];            /* [baseQ] -> sub */
+};
 
 struct DevModel {
     const double *coef, *lhet, *fk;
@@ -69,23 +94,30 @@ struct DevBatch {
 /* -------------------------------------------------------------------------------------------- */
 /* key construction (sniper_maqcns.c:144-156 + the :165 promotion rule folded in)              */
 
-__device__ __forceinline__ uint32_t make_key(uint32_t bs, uint32_t bq, uint32_t mq, uint32_t ref16, uint32_t is_tumor)
+__device__ __forceinline__ void build_key_luts(CtaTables &T, int tid, int nthreads)
 {
-    uint32_t nt = bs & 15u, strand = (bs >> 4) & 1u;
-    uint32_t q = min(bq, mq);
-    nt = nt ? nt : ref16;
-    uint32_t valid = (nt != 0u && (nt & (nt - 1u)) == 0u) ? 1u : 0u;   /* bam_nt16_nt4_table < 4 */
-    uint32_t b4 = valid ? ((nt >> 1) - (nt >> 3)) : 0u;                /* 1,2,4,8 -> 0,1,2,3 */
-    uint32_t low6 = bq & 0x3fu;
-    uint32_t sub = 7u;
-    if (q >= 1u && q <= 3u) sub = 1u + (bq < 64u ? 0u : 2u * (bq >> 6) - (low6 == 0u ? 1u : 0u));
-    uint32_t key = is_tumor << 15 | b4 << 13 | q << 5 | valid << 4 | strand << 3 | sub;
-    bool contributes = q != 0u || low6 != 0u;
-    return contributes ? key : 0u;
+    for (int i = tid; i < 2 * 16 * 32; i += nthreads) {
+        const uint32_t sample = i >> 9, ref16 = (i >> 5) & 15u, strand = (i >> 4) & 1u;
+        uint32_t nt = i & 15u;
+        nt = nt ? nt : ref16;                                               /* '=' -> reference base */
+        const uint32_t valid = (nt != 0u && (nt & (nt - 1u)) == 0u) ? 1u : 0u;  /* bam_nt16_nt4_table < 4 */
+        const uint32_t b4 = valid ? ((nt >> 1) - (nt >> 3)) : 0u;               /* 1,2,4,8 -> 0,1,2,3 */
+        T.cls[i] = (uint16_t)(sample << 15 | b4 << 13 | valid << 4 | strand << 3);
+    }
+    for (int i = tid; i < 256; i += nthreads)
+        T.sub[i] = (uint8_t)(1 + (i < 64 ? 0 : 2 * (i >> 6) - ((i & 63) == 0 ? 1 : 0)));
+}
+
+/* cls_col = T.cls + (sample*16 + ref16)*32 */
+__device__ __forceinline__ uint32_t make_key(const uint16_t *cls_col, const uint8_t *sub_lut, uint32_t bs, uint32_t bq, uint32_t mq)
+{
+    const uint32_t q = min(bq, mq);
+    const uint32_t key = (uint32_t)cls_col[bs & 31u] + q * 32u + (uint32_t)sub_lut[bq];
+    return (q | (bq & 63u)) ? key : 0u;        /* q == 0 and baseQ & 0x3f == 0: contributes nothing (:165,:167) */
 }
 
 /* -------------------------------------------------------------------------------------------- */
-/* packed bitonic sort: R registers per lane, 2 keys per register.                              */
+/* generic path: packed bitonic sort over the warp, R registers per lane, 2 keys per register.  */
 /* half h, register r, lane l hold element e = r + R*l of half h; low halves sort ascending,    */
 /* high halves hold complemented keys (so they sort descending in true order), then one merge.  */
 
@@ -148,18 +180,19 @@ __device__ __forceinline__ void sort_packed(uint32_t (&v)[R], int lane)
 /* Load one run of `len` (<= 64R) read-bases starting at entry `e0`, build keys, sort, and store the top
  * ceil(len/2) words (ascending) at store32[0..).  tumor_len = how many of the run's entries are tumor. */
 template <int R>
-__device__ __forceinline__ void sort_run(const DevBatch &B, uint32_t e0, int len, int tumor_len, uint32_t ref16,
+__device__ __forceinline__ void sort_run(const DevBatch &B, const CtaTables &T, uint32_t e0, int len, int tumor_len, uint32_t ref16,
                                          uint32_t *store32, int lane, uint32_t &rms_t, uint32_t &rms_n, int cap_mapq)
 {
     uint32_t v[R];
+    const uint16_t *cls_t = T.cls + (16 + ref16) * 32, *cls_n = T.cls + ref16 * 32;
 #pragma unroll
     for (int row = 0; row < 2 * R; ++row) {
         const int i = row * 32 + lane;
         uint32_t key = 0;
         if (i < len) {
             const uint32_t bs = B.bs[e0 + i], bq = B.bq[e0 + i], mq = B.mq[e0 + i];
-            const uint32_t is_t = i < tumor_len ? 1u : 0u;
-            key = make_key(bs, bq, mq, ref16, is_t);
+            const bool is_t = i < tumor_len;
+            key = make_key(is_t ? cls_t : cls_n, T.sub, bs, bq, mq);
             const uint32_t m = min(mq & 0x7fu, (uint32_t)cap_mapq);      /* sniper_maqcns.c:173-174 */
             if (is_t) rms_t += m * m; else rms_n += m * m;
         }
@@ -193,7 +226,7 @@ __device__ __forceinline__ void sort_run(const DevBatch &B, uint32_t e0, int len
  * nearest-even at the float ulp of s's binade, i.e. equals (double)(float)s for normal floats. */
 __device__ __forceinline__ double round_to_f32(double s)
 {
-#if SSN_ROUND_MAGIC
+#if SSN_ROUND_MAGIC != 0
     const int hi = __double2hiint(s);
     const double m = __hiloint2double((hi & 0x7ff00000) + 0x01d00000, 0);
     return __dsub_rn(__dadd_rn(s, m), m);
@@ -202,11 +235,23 @@ __device__ __forceinline__ double round_to_f32(double s)
 #endif
 }
 
+/* the fsum chain: same rounding; SSN_ROUND_MAGIC == 2 sends it through the conversion pipe instead */
+__device__ __forceinline__ double round_to_f32f(double s)
+{
+#if SSN_ROUND_MAGIC == 2
+    return (double)__double2float_rn(s);
+#else
+    return round_to_f32(s);
+#endif
+}
+
 struct Chain {
     double e, f;        /* float-valued accumulators held in double */
     uint32_t c, w0, w1; /* count; per-strand dependency ranks */
     int sb;             /* current (sample<<2 | base) slot, -1 = none */
 };
+
+__device__ __forceinline__ void chain_init(Chain &ch) { ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0; ch.sb = -1; }
 
 __device__ __forceinline__ void chain_flush(const Chain &ch, uint32_t *slots, int lane)
 {
@@ -218,7 +263,7 @@ __device__ __forceinline__ void chain_flush(const Chain &ch, uint32_t *slots, in
     }
 }
 
-__device__ __forceinline__ void chain_step(Chain &ch, uint32_t key, const double *fk_s, uint32_t *slots, int lane)
+__device__ __forceinline__ void chain_step(Chain &ch, uint32_t key, const double2 *fk_s, uint32_t *slots, int lane)
 {
     const int sb = (int)(key >> 13);
     if (sb != ch.sb) {
@@ -226,19 +271,155 @@ __device__ __forceinline__ void chain_step(Chain &ch, uint32_t key, const double
         ch.sb = sb; ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0;
     }
     uint32_t q = (key >> 5) & 0xffu;
-    if (q < 4u) {                                        /* sniper_maqcns.c:165 */
-        const uint32_t sub = key & 7u;
-        q = (q != 0u && (sub & 1u) == 0u) ? q : 4u;      /* sub-1 odd <=> baseQ in {64,128,192} */
-    }
+    if (q < 4u) q = (q != 0u && !(key & 1u)) ? q : 4u;   /* sniper_maqcns.c:165; sub even <=> baseQ in {64,128,192} */
     const bool rev = (key >> 3) & 1u;
     const uint32_t w = rev ? ch.w1 : ch.w0;
-    const double fkw = fk_s[w];
+    const double fkw = fk_s[w].x;
     const double qd = __hiloint2double(0x43300000, (int)q) - 4503599627370496.0;   /* exact int -> double */
     ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fkw, qd)));      /* esum += fk[w]*q  (:168) */
     ch.f = round_to_f32(__dadd_rn(ch.f, fkw));                     /* fsum += fk[w]    (:169) */
     const uint32_t wn = min(w + 1u, 255u);                         /* :170 */
     if (rev) ch.w1 = wn; else ch.w0 = wn;
     ++ch.c;
+}
+
+/* -------------------------------------------------------------------------------------------- */
+/* fast path: bulk-copied raw tile -> transposed key store -> per-lane sorting network -> walk   */
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+/* One lane stages [a0, a0+bytes) of bs/bq/mq into the warp's raw area with three 1-D bulk copies (TMA unit)
+ * that complete on the warp's mbarrier.  a0 and bytes are multiples of 16. */
+__device__ __forceinline__ void stage_issue(const DevBatch &B, uint32_t raw_s, uint32_t mbar_s, uint32_t a0, uint32_t bytes)
+{
+    /* earlier generic-proxy accesses to the area (previous tile's slots) are ordered before the async-proxy writes */
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar_s), "r"(3u * bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(raw_s), "l"(B.bs + a0), "r"(bytes), "r"(mbar_s) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(raw_s + (uint32_t)kRawBytes), "l"(B.bq + a0), "r"(bytes), "r"(mbar_s) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(raw_s + 2u * (uint32_t)kRawBytes), "l"(B.mq + a0), "r"(bytes), "r"(mbar_s) : "memory");
+}
+
+__device__ __forceinline__ void stage_wait(uint32_t mbar_s, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" :: "r"(mbar_s), "r"(parity) : "memory");
+}
+
+/* FRONT of a fast tile: keys of all 32 columns -> keys[w*32 + (col ^ (w & 31))] (packed, hi half complemented).
+ * raw = staged bytes; column j's read-bases start at raw offset shfl(r0, j), tumor first. */
+template <int NW>
+__device__ __forceinline__ void fast_front(const CtaTables &T, const unsigned char *__restrict__ raw, uint32_t *__restrict__ keys,
+                                           int lane, uint32_t r0, uint32_t nT, uint32_t n, uint32_t ref16, int cap_mapq,
+                                           uint32_t &my_rms_t, uint32_t &my_rms_n)
+{
+#pragma unroll
+    for (int w = 0; w < NW; ++w) keys[w * 32 + lane] = 0xffff0000u;   /* padding: key 0 in both halves */
+    __syncwarp();
+    const uint32_t xmask = (lane & 1) ? 0xffffu : 0u;
+    unsigned char *kb = reinterpret_cast<unsigned char*>(keys) + (lane & 1) * 2;
+    const uint32_t cap = (uint32_t)cap_mapq;
+#pragma unroll 1
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t nj = __shfl_sync(kFull, n, j);
+        if (nj == 0u) continue;
+        const uint32_t nTj = __shfl_sync(kFull, nT, j), refj = __shfl_sync(kFull, ref16, j);
+        const unsigned char *src = raw + __shfl_sync(kFull, r0, j);
+        const uint16_t *cls_t = T.cls + (16 + refj) * 32, *cls_n = T.cls + refj * 32;
+        uint32_t rt = 0, rn = 0;
+#pragma unroll 1
+        for (uint32_t i = lane; i < nj; i += 32) {
+            const uint32_t bs = src[i], bq = src[kRawBytes + i], mq = src[2 * kRawBytes + i];
+            const bool is_t = i < nTj;
+            const uint32_t key = make_key(is_t ? cls_t : cls_n, T.sub, bs, bq, mq);
+            const uint32_t m = min(mq & 0x7fu, cap);                          /* sniper_maqcns.c:173-174 */
+            if (is_t) rt += m * m; else rn += m * m;
+            const uint32_t w = i >> 1;
+            *reinterpret_cast<uint16_t*>(kb + w * 128 + (((uint32_t)j ^ w) & 31u) * 4) = (uint16_t)(key ^ xmask);
+        }
+        rt = __reduce_add_sync(kFull, rt);
+        rn = __reduce_add_sync(kFull, rn);
+        if (lane == j) { my_rms_t = rt; my_rms_n = rn; }
+    }
+    __syncwarp();
+}
+
+/* BACK of a fast tile, first half: sort this lane's column and lay the keys out for the walk */
+template <int NW>
+__device__ __forceinline__ void fast_sort(uint32_t *keys, int lane)
+{
+    uint32_t v[NW];
+#pragma unroll
+    for (int w = 0; w < NW; ++w) v[w] = keys[w * 32 + ((lane ^ w) & 31)];
+    __syncwarp();                                   /* all lanes have read before anyone overwrites */
+    SortNet<NW>::lists(v);
+    SortNet<NW>::merge(v);
+    /* ascending sequence lo[0..NW) ++ hi[0..NW), two keys per word, word k of lane l at keys[k*32 + l] */
+#pragma unroll
+    for (int k = 0; k < NW / 2; ++k) {
+        keys[k * 32 + lane] = __byte_perm(v[2 * k], v[2 * k + 1], 0x5410);
+        keys[(NW / 2 + k) * 32 + lane] = __byte_perm(v[2 * k], v[2 * k + 1], 0x7632);
+    }
+}
+
+/* The walk of a fast tile.  Group changes (and the end: key 0) are detected by one compare against the
+ * current group's floor; q*32 is taken from the key unshifted and multiplied by fk/32 (exact scaling). */
+struct Walk {
+    double e, f;
+    uint32_t w0, w1, c, floor;
+    int sb;
+};
+
+__device__ __forceinline__ void walk_flush(const Walk &ch, uint32_t *slots, int lane)
+{
+    if (ch.sb >= 0) {
+        uint32_t *s = slots + ch.sb * 96 + lane;
+        s[0] = __float_as_uint(__double2float_rn(ch.e));
+        s[32] = __float_as_uint(__double2float_rn(ch.f));
+        s[64] = ch.c;
+    }
+}
+
+/* returns false when the column's keys are exhausted */
+__device__ __forceinline__ bool walk_step(Walk &ch, uint32_t key, const double2 *fk2, uint32_t *slots, int lane)
+{
+    if (key < ch.floor) {
+        walk_flush(ch, slots, lane);
+        ch.sb = -1;
+        if (key == 0u) return false;
+        ch.sb = (int)(key >> 13); ch.floor = max(key & 0xe000u, 1u);   /* group 0's real keys are >= 1 */
+        ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0;
+    }
+    uint32_t q32 = key & 0x1fe0u;
+    if (q32 < 128u) q32 = (q32 != 0u && !(key & 1u)) ? q32 : 128u;   /* sniper_maqcns.c:165; sub even <=> baseQ in {64,128,192} */
+    const bool rev = (key & 8u) != 0u;
+    const uint32_t w = rev ? ch.w1 : ch.w0;
+    const double2 fk = fk2[w];
+    const double qd = __hiloint2double(0x43300000, (int)q32) - 4503599627370496.0;   /* exact int -> double */
+    ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fk.y, qd)));     /* esum += fk[w]*q  (:168) */
+    ch.f = round_to_f32f(__dadd_rn(ch.f, fk.x));                   /* fsum += fk[w]    (:169) */
+    const uint32_t wn = min(w + 1u, 255u);                         /* :170 */
+    if (rev) ch.w1 = wn; else ch.w0 = wn;
+    ++ch.c;
+    return true;
+}
+
+template <int NW>
+__device__ __forceinline__ void fast_walk(const uint32_t *keys, const double2 *fk2, uint32_t *slots, int lane)
+{
+    Walk ch;
+    ch.e = 0.0; ch.f = 0.0; ch.w0 = 0; ch.w1 = 0; ch.c = 0; ch.floor = 0x10000u; ch.sb = -1;
+#pragma unroll 1
+    for (int k = NW - 1; k >= 0; --k) {
+        const uint32_t wd = keys[k * 32 + lane];
+        if (!walk_step(ch, wd >> 16, fk2, slots, lane)) break;
+        if (!walk_step(ch, wd & 0xffffu, fk2, slots, lane)) break;
+    }
+    walk_flush(ch, slots, lane);
 }
 
 /* -------------------------------------------------------------------------------------------- */
@@ -489,25 +670,111 @@ __device__ void site_stats(const DevBatch &B, uint32_t e0, int n, int rb4, uint3
 
 __device__ __forceinline__ int run_R(int len) { return len <= 64 ? 1 : len <= 128 ? 2 : len <= 256 ? 4 : len <= 512 ? 8 : 16; }
 
+/* generic FRONT + walk: any depth up to kRunLen*kMaxRuns per column */
+__device__ __noinline__ void generic_tile(const DevModel &M, const DevBatch &B, const CtaTables &T, uint32_t *slots, uint32_t *keys_s,
+                                          uint32_t *keys_g, int lane, uint32_t o0, uint32_t nT, uint32_t n, uint32_t ref16,
+                                          uint32_t &my_rms_t, uint32_t &my_rms_n)
+{
+    /* words of key store this column needs: full runs take kRunLen/2, the tail ceil(len/2) */
+    const uint32_t nruns = (n + kRunLen - 1) / kRunLen;
+    const uint32_t words = (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
+    uint32_t incl = words;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(kFull, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const uint32_t wbase = incl - words;
+    const uint32_t tile_words = __shfl_sync(kFull, incl, 31);
+    uint32_t *store = tile_words <= B.smem_words_per_warp ? keys_s : keys_g;
+
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t nj = __shfl_sync(kFull, n, j);
+        if (nj == 0) continue;
+        const uint32_t e0 = __shfl_sync(kFull, o0, j);
+        const int nTj = (int)__shfl_sync(kFull, nT, j);
+        const uint32_t refj = __shfl_sync(kFull, ref16, j);
+        uint32_t *dst = store + __shfl_sync(kFull, wbase, j);
+        uint32_t rt = 0, rn = 0;
+        for (uint32_t done = 0; done < nj; done += kRunLen) {
+            const int len = (int)min(nj - done, (uint32_t)kRunLen);
+            const int tl = nTj - (int)done;
+            switch (run_R(len)) {
+            case 1: sort_run<1>(B, T, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+            case 2: sort_run<2>(B, T, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+            case 4: sort_run<4>(B, T, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+            case 8: sort_run<8>(B, T, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+            default: sort_run<16>(B, T, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
+            }
+            dst += (len + 1) >> 1;
+        }
+        rt = __reduce_add_sync(kFull, rt);
+        rn = __reduce_add_sync(kFull, rn);
+        if (lane == j) { my_rms_t = rt; my_rms_n = rn; }
+    }
+    __syncwarp();
+
+    Chain ch;
+    chain_init(ch);
+    const uint16_t *k16 = reinterpret_cast<const uint16_t*>(store + wbase);
+    if (nruns <= 1) {
+        for (int idx = 2 * (int)words - 1; idx >= 0; --idx) {
+            const uint32_t key = k16[idx];
+            if (key == 0) break;
+            chain_step(ch, key, T.fk2, slots, lane);
+        }
+    } else {
+        /* k-way merge of the sorted runs (deep columns): heads live in local memory */
+        int hp[kMaxRuns];
+        uint16_t hk[kMaxRuns];
+        for (uint32_t r = 0; r < nruns; ++r) {
+            const uint32_t len = min(n - r * kRunLen, (uint32_t)kRunLen);
+            hp[r] = (int)(r * kRunLen + 2 * ((len + 1) >> 1)) - 1;
+            hk[r] = k16[hp[r]];
+        }
+        for (;;) {
+            uint32_t best = 0, br = 0;
+            for (uint32_t r = 0; r < nruns; ++r)
+                if (hk[r] > best) { best = hk[r]; br = r; }
+            if (best == 0) break;
+            chain_step(ch, best, T.fk2, slots, lane);
+            const int np = hp[br] - 1;
+            hp[br] = np;
+            hk[br] = np >= (int)(br * kRunLen) ? k16[np] : (uint16_t)0;
+        }
+    }
+    chain_flush(ch, slots, lane);
+}
+
 template <bool DUMP>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 1)
 ssn_score_kernel(const DevModel M, const DevBatch B)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    double *fk_s = reinterpret_cast<double*>(smem_raw);                       /* 256 doubles */
-    int32_t *qadd_s = reinterpret_cast<int32_t*>(smem_raw + 2048);            /* 1024 + pad  */
-    int32_t *prior_s = qadd_s + 1024 + 64;                                    /* 160         */
-    uint32_t *warp_base = reinterpret_cast<uint32_t*>(prior_s + 160);
+    __shared__ CtaTables T;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) fk_s[i] = M.fk[i];
-    for (int i = threadIdx.x; i < 1024 + 64; i += blockDim.x) qadd_s[i] = M.qadd[i];
-    for (int i = threadIdx.x; i < 160; i += blockDim.x) prior_s[i] = M.prior[i];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        const double f = M.fk[i];
+        T.fk2[i] = make_double2(f, f * 0.03125);          /* exact power-of-two scaling */
+    }
+    for (int i = threadIdx.x; i < 1024 + 64; i += blockDim.x) T.qadd[i] = M.qadd[i];
+    for (int i = threadIdx.x; i < 160; i += blockDim.x) T.prior[i] = M.prior[i];
+    build_key_luts(T, threadIdx.x, blockDim.x);
+    const uint32_t mbar_s = smem_u32(&T.mbar[warp]);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar_s) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
-    uint32_t *slots = warp_base + (size_t)warp * (kSlotWords + B.smem_words_per_warp);
-    uint32_t *keys_s = slots + kSlotWords;
+    /* per warp: [keys: smem_words_per_warp] [aux: kAuxWords = raw staging of a fast tile, then the chain slots] */
+    uint32_t *keys_s = reinterpret_cast<uint32_t*>(smem_raw) + (size_t)warp * (kAuxWords + B.smem_words_per_warp);
+    uint32_t *slots = keys_s + B.smem_words_per_warp;
+    const unsigned char *raw = reinterpret_cast<const unsigned char*>(slots);
+    const uint32_t raw_s = smem_u32(slots);
     const uint32_t gwarp = blockIdx.x * kWarpsPerCta + warp;
     uint32_t *keys_g = B.scratch ? B.scratch + (size_t)gwarp * B.scratch_words_per_warp : nullptr;
     const uint32_t ntiles = (B.ncol + 31u) >> 5;
+    uint32_t phase = 0;
 
     for (;;) {
         uint32_t tile = 0;
@@ -522,79 +789,31 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
             ref16 = B.ref_nt16[col] & 15u;
         }
         const uint32_t nT = o1 - o0, nN = o2 - o1, n = nT + nN;
-        /* words of key store this column needs: full runs take kRunLen/2, the tail ceil(len/2) */
-        const uint32_t nruns = (n + kRunLen - 1) / kRunLen;
-        const uint32_t words = (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
-        uint32_t incl = words;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t t = __shfl_up_sync(kFull, incl, d);
-            if (lane >= d) incl += t;
-        }
-        const uint32_t wbase = incl - words;
-        const uint32_t tile_words = __shfl_sync(kFull, incl, 31);
-        uint32_t *store = tile_words <= B.smem_words_per_warp ? keys_s : keys_g;
+        const uint32_t need = __reduce_max_sync(kFull, n);
+        /* the tile's read-bases are contiguous: [off of its first column, end of its last live column) */
+        const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
+        const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
+        const bool fast = need <= 2u * kFastWords && bytes <= (uint32_t)kRawBytes && B.smem_words_per_warp >= kFastWords * 32u;
 
-        /* ---------------- FRONT: one column at a time, whole warp ---------------- */
         uint32_t my_rms_t = 0, my_rms_n = 0;
-        for (int j = 0; j < 32; ++j) {
-            const uint32_t nj = __shfl_sync(kFull, n, j);
-            if (nj == 0) continue;
-            const uint32_t e0 = __shfl_sync(kFull, o0, j);
-            const int nTj = (int)__shfl_sync(kFull, nT, j);
-            const uint32_t refj = __shfl_sync(kFull, ref16, j);
-            uint32_t *dst = store + __shfl_sync(kFull, wbase, j);
-            uint32_t rt = 0, rn = 0;
-            for (uint32_t done = 0; done < nj; done += kRunLen) {
-                const int len = (int)min(nj - done, (uint32_t)kRunLen);
-                const int tl = nTj - (int)done;
-                switch (run_R(len)) {
-                case 1: sort_run<1>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
-                case 2: sort_run<2>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
-                case 4: sort_run<4>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
-                case 8: sort_run<8>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
-                default: sort_run<16>(B, e0 + done, len, tl, refj, dst, lane, rt, rn, M.cap_mapq); break;
-                }
-                dst += (len + 1) >> 1;
-            }
-            rt = __reduce_add_sync(kFull, rt);
-            rn = __reduce_add_sync(kFull, rn);
-            if (lane == j) { my_rms_t = rt; my_rms_n = rn; }
-        }
-        for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
-        __syncwarp();
-
-        /* ---------------- BACK: one column per lane ---------------- */
-        {
-            Chain ch; ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0; ch.sb = -1;
-            const uint16_t *k16 = reinterpret_cast<const uint16_t*>(store + wbase);
-            if (nruns <= 1) {
-                for (int idx = 2 * (int)words - 1; idx >= 0; --idx) {
-                    const uint32_t key = k16[idx];
-                    if (key == 0) break;
-                    chain_step(ch, key, fk_s, slots, lane);
-                }
-            } else {
-                /* k-way merge of the sorted runs (deep columns): heads live in local memory */
-                int hp[kMaxRuns];
-                uint16_t hk[kMaxRuns];
-                for (uint32_t r = 0; r < nruns; ++r) {
-                    const uint32_t len = min(n - r * kRunLen, (uint32_t)kRunLen);
-                    hp[r] = (int)(r * kRunLen + 2 * ((len + 1) >> 1)) - 1;
-                    hk[r] = k16[hp[r]];
-                }
-                for (;;) {
-                    uint32_t best = 0, br = 0;
-                    for (uint32_t r = 0; r < nruns; ++r)
-                        if (hk[r] > best) { best = hk[r]; br = r; }
-                    if (best == 0) break;
-                    chain_step(ch, best, fk_s, slots, lane);
-                    const int np = hp[br] - 1;
-                    hp[br] = np;
-                    hk[br] = np >= (int)(br * kRunLen) ? k16[np] : (uint16_t)0;
-                }
-            }
-            chain_flush(ch, slots, lane);
+        __syncwarp();                                   /* the previous tile is done with slots / keys */
+        if (need != 0u && fast) {
+            if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
+            stage_wait(mbar_s, phase);
+            phase ^= 1u;
+            const uint32_t r0 = o0 - a0;
+            if (need <= 32u) fast_front<16>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
+            else if (need <= 64u) fast_front<32>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
+            else fast_front<64>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
+            for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;      /* raw staging is dead: it becomes the slots */
+            __syncwarp();
+            if (need <= 32u) { fast_sort<16>(keys_s, lane); fast_walk<16>(keys_s, T.fk2, slots, lane); }
+            else if (need <= 64u) { fast_sort<32>(keys_s, lane); fast_walk<32>(keys_s, T.fk2, slots, lane); }
+            else { fast_sort<64>(keys_s, lane); fast_walk<64>(keys_s, T.fk2, slots, lane); }
+        } else {
+            for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
+            __syncwarp();
+            if (need != 0u) generic_tile(M, B, T, slots, keys_s, keys_g, lane, o0, nT, n, ref16, my_rms_t, my_rms_n);
         }
         __syncwarp();
 
@@ -605,7 +824,7 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         if (nN) sample_glf(M, slots, lane, 0, nN, my_rms_n, gn);
         Call call;
         call.score = -1; call.pass = false; call.candidate = false;
-        if (nT && nN && ref16 != 15u) score_column(M, qadd_s, prior_s, (int)ref16, gt, gn, call);
+        if (nT && nN && ref16 != 15u) score_column(M, T.qadd, T.prior, (int)ref16, gt, gn, call);
 
         if (DUMP && live) {
             uint32_t *o = B.coldump + (size_t)col * SSN_COLUMN_DUMP_WORDS;
