@@ -80,7 +80,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
@@ -258,6 +258,7 @@ def run_b200(args):
     l0 = sc.kernel_launches()
     sampler = ClockSampler(local)
     sampler.start()
+    time.sleep(0.25)                    # nvidia-smi needs a moment before its first sample
     dist_barrier(dist)
     sc.sync()
     sc.timer_start()
@@ -265,7 +266,6 @@ def run_b200(args):
         sc.score_resident(b)
     ms = sc.timer_stop()
     dist_barrier(dist)
-    sampler.stop()
     launches = sc.kernel_launches() - l0
     kms, kn = sc.kernel_time(reset=True)
     n_sites = len(sites_ref)
@@ -324,6 +324,7 @@ def run_b200(args):
                "d2h_bytes_per_step": 8 * CHUNKS + 216 * n_sites, "ms_per_step": ems_max / args.steps,
                "batches_per_step": CHUNKS}
 
+    sampler.stop()
     if rank != 0:
         return
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
