@@ -1,0 +1,70 @@
+/*
+ * ssn_host.h — C ABI of the host packer (libssn_host.so; no CUDA dependency).
+ *
+ * Replaces the reference's dual-BAM pileup walk
+ *     bam_sspileup_file(fp1, fp2, mask, mapQ, glf_somatic, d, snp_fh)      src/lib/sniper/sniper_pileup.c:226-266
+ *     get_next_pos / resolve_cigar                                          src/lib/sniper/sniper_pileup.c:57-104,172-224
+ * and the per-column reference-base lookup of glf_somatic (src/lib/sniper/somatic_sniper.c:112-117):
+ * instead of one callback per column it emits structure-of-arrays batches in the layout of
+ * ssn_batch_view (include/ssn.h), straight into the pinned arrays of a scorer batch.
+ *
+ * A column is emitted when both samples hold at least one non-deleted read base there and the
+ * reference base is callable (bam_nt16_table[ref] != 15): exactly the columns for which glf_somatic can
+ * produce output (somatic_sniper.c:127,156).  Read filter, sortedness check and the keep rule that drops
+ * the first read of every later target follow the reference (see csrc/host/ssn_bamread.h).
+ */
+#ifndef SSN_HOST_H
+#define SSN_HOST_H
+
+#include "ssn.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ssn_packer ssn_packer;
+
+/* column -> genome map of one batch; arrays of view.max_columns elements owned by the caller */
+typedef struct {
+    int32_t *tid;        /* target index (tumor header numbering, as the reference compares tids numerically) */
+    uint32_t *pos;       /* 0-based position */
+    uint8_t *ref_char;   /* raw FASTA character (case preserved), what the writers print */
+} ssn_colmap;
+
+typedef struct {
+    uint64_t records[2];      /* BAM records framed so far: tumor, normal */
+    uint64_t columns, entries, batches;
+    double t_wait, t_count, t_fill;   /* seconds inside ssn_packer_next: waiting for readers, counting, filling */
+} ssn_packer_stats;
+
+/* tumor may be "-" (stdin), like the reference (main.c:128).  fasta may be NULL (every base 'N': nothing is
+ * emitted, main.c requires -f).  min_mapq = -q.  n_threads = worker threads shared by inflate and packing
+ * (0: everything on the calling thread plus the two reader threads). */
+ssn_status ssn_packer_open(const char *tumor_bam, const char *normal_bam, const char *fasta, int min_mapq,
+                           int n_threads, ssn_packer **out);
+void ssn_packer_close(ssn_packer *p);
+/* header of the tumor (which = 0) or normal (1) BAM */
+int32_t ssn_packer_n_targets(const ssn_packer *p, int which);
+const char *ssn_packer_target_name(const ssn_packer *p, int which, int32_t tid);
+/* Fills the next batch (at most view->max_columns columns / view->max_entries read bases).  *n_columns = 0
+ * at the end of the walk. */
+ssn_status ssn_packer_next(ssn_packer *p, const ssn_batch_view *view, const ssn_colmap *map,
+                           uint32_t *n_columns, uint64_t *n_entries);
+void ssn_packer_get_stats(const ssn_packer *p, ssn_packer_stats *out);
+const char *ssn_host_last_error(void);
+
+/* ---- writers: one passing site -> one line, byte-identical to the reference ---------------------------
+ * output_classic.c:9-55, output_vcf.c:135-192, output_bed.c:5-19; format names as in output_format.c:9-17 */
+typedef struct ssn_writer ssn_writer;
+/* fh is a FILE*; returns NULL for an unknown format name (caller prints the reference's message) */
+ssn_writer *ssn_writer_create(const char *format, void *fh);
+void ssn_writer_header(ssn_writer *w, const char *refseq, const char *normal_id, const char *tumor_id);
+void ssn_writer_site(ssn_writer *w, const char *seq_name, uint32_t pos, int ref_char, const ssn_site *site);
+void ssn_writer_destroy(ssn_writer *w);
+int ssn_writer_n_formats(void);
+const char *ssn_writer_format_name(int i);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSN_HOST_H */

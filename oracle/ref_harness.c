@@ -196,3 +196,63 @@ int ref_should_filter_as_loh(int r, int t, int n) { return should_filter_as_loh(
 int ref_should_filter_as_gor(int r, int t, int n) { return should_filter_as_gor(r, t, n); }
 int ref_count_alleles(int a) { return count_alleles(a); }
 int ref_nt16_of_char(int ch) { return bam_nt16_table[ch & 0xff]; }
+
+/* ---- the reference's own dual-BAM walk with a capturing callback ------------------------------------------
+ * Runs bam_sspileup_file (sniper_pileup.c:226-266) over two BAM files and records every column the walker
+ * hands to its callback: (tid, pos, n1, n2) plus the non-deleted entries of both samples in the product's
+ * entry encoding.  Used to pin the host packer (tests/test_packer.py). */
+typedef struct {
+    int32_t *cols; size_t n_cols, m_cols;            /* 6 ints per column: tid, pos, n1, n2, entries tumor, entries normal */
+    uint8_t *ent; size_t n_ent, m_ent;               /* 3 bytes per entry: bs, bq, mq (tumor entries first) */
+} pileup_dump_t;
+static pileup_dump_t g_dump;
+
+static void dump_entries(const bam_pileup1_t *pl, int n, int32_t *count)
+{
+    int i;
+    *count = 0;
+    for (i = 0; i < n; ++i) {
+        const bam_pileup1_t *p = pl + i;
+        if (p->is_del || (p->b->core.flag & BAM_FUNMAP)) continue;
+        if (g_dump.n_ent + 3 > g_dump.m_ent) {
+            g_dump.m_ent = g_dump.m_ent ? g_dump.m_ent * 2 : (1u << 20);
+            g_dump.ent = (uint8_t*)realloc(g_dump.ent, g_dump.m_ent);
+        }
+        g_dump.ent[g_dump.n_ent++] = (uint8_t)(bam1_seqi(bam1_seq(p->b), p->qpos) | (bam1_strand(p->b) ? 16 : 0));
+        g_dump.ent[g_dump.n_ent++] = bam1_qual(p->b)[p->qpos];
+        g_dump.ent[g_dump.n_ent++] = (uint8_t)p->b->core.qual;
+        ++*count;
+    }
+}
+
+static int dump_cb(uint32_t tid, uint32_t pos, int n1, int n2, const bam_pileup1_t *pl1, const bam_pileup1_t *pl2, void *data, FILE *fh)
+{
+    int32_t *c;
+    (void)data; (void)fh;
+    if (g_dump.n_cols + 6 > g_dump.m_cols) {
+        g_dump.m_cols = g_dump.m_cols ? g_dump.m_cols * 2 : (1u << 16);
+        g_dump.cols = (int32_t*)realloc(g_dump.cols, sizeof(int32_t) * g_dump.m_cols);
+    }
+    c = g_dump.cols + g_dump.n_cols;
+    g_dump.n_cols += 6;
+    c[0] = (int32_t)tid; c[1] = (int32_t)pos; c[2] = n1; c[3] = n2;
+    dump_entries(pl1, n1, &c[4]);
+    c = g_dump.cols + g_dump.n_cols - 6;              /* realloc inside dump_entries does not move cols, but stay safe */
+    dump_entries(pl2, n2, &c[5]);
+    return 0;
+}
+
+/* returns the number of columns; pointers stay valid until the next call */
+long ref_pileup_dump(const char *tumor_bam, const char *normal_bam, int mapq, const int32_t **cols, const uint8_t **ent, long *n_ent)
+{
+    bamFile fp1 = bam_open(tumor_bam, "r"), fp2 = bam_open(normal_bam, "r");
+    bam_header_t *h1, *h2;
+    if (!fp1 || !fp2) return -1;
+    h1 = bam_header_read(fp1); h2 = bam_header_read(fp2);
+    g_dump.n_cols = 0; g_dump.n_ent = 0;
+    bam_sspileup_file(fp1, fp2, BAM_DEF_MASK, mapq, dump_cb, 0, 0);
+    bam_close(fp1); bam_close(fp2);
+    bam_header_destroy(h1); bam_header_destroy(h2);
+    *cols = g_dump.cols; *ent = g_dump.ent; *n_ent = (long)(g_dump.n_ent / 3);
+    return (long)(g_dump.n_cols / 6);
+}

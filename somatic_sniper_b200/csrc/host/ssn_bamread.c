@@ -1,0 +1,312 @@
+#include "ssn_bamread.h"
+
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "ssn_bgzf.h"
+
+#define QUEUE_MAX_BYTES ((size_t)256 << 20)   /* finished windows waiting for the packer (back-pressure) */
+#define MAX_OPEN 64                           /* windows one read may span at once (beyond: longer reads are clipped to the list) */
+
+struct ssn_bamreader {
+    ssn_bgzf *z;
+    ssn_bam_header hdr;
+    int flag_mask, mapq_thresh;
+    /* byte stream over inflated chunks */
+    const uint8_t *chunk;
+    size_t chunk_len, chunk_pos;
+    uint8_t *carry;
+    size_t carry_cap;
+    int stream_end;
+    /* reader thread + queue of finished windows */
+    pthread_t th;
+    int th_started;
+    pthread_mutex_t mu;
+    pthread_cond_t not_empty, not_full;
+    ssn_window *q_head, *q_tail;
+    size_t q_bytes;
+    int finished, stop;
+    uint64_t n_records;
+    /* open windows of the current target, ascending widx */
+    ssn_window *open[MAX_OPEN];
+    int n_open;
+};
+
+/* ---- byte stream -------------------------------------------------------------------------------- */
+
+static int stream_fill(ssn_bamreader *r)
+{
+    if (r->stream_end) return 0;
+    if (!ssn_bgzf_next(r->z, &r->chunk, &r->chunk_len)) { r->stream_end = 1; r->chunk_len = r->chunk_pos = 0; return 0; }
+    r->chunk_pos = 0;
+    return 1;
+}
+
+/* Returns a pointer to the next n bytes (inside the chunk, or assembled in the carry buffer), NULL at end of stream. */
+static const uint8_t *stream_take(ssn_bamreader *r, size_t n)
+{
+    size_t have;
+    if (r->chunk_len - r->chunk_pos >= n) {
+        const uint8_t *p = r->chunk + r->chunk_pos;
+        r->chunk_pos += n;
+        return p;
+    }
+    if (r->carry_cap < n) {
+        r->carry_cap = n + (n >> 1) + 64;
+        r->carry = (uint8_t*)realloc(r->carry, r->carry_cap);
+        if (!r->carry) return 0;
+    }
+    have = 0;
+    while (have < n) {
+        size_t avail = r->chunk_len - r->chunk_pos, take;
+        if (avail == 0) {
+            if (!stream_fill(r)) return 0;          /* truncated: the reference treats any short read as end-of-file */
+            continue;
+        }
+        take = avail < n - have ? avail : n - have;
+        memcpy(r->carry + have, r->chunk + r->chunk_pos, take);
+        r->chunk_pos += take; have += take;
+    }
+    return r->carry;
+}
+
+static uint32_t le32(const uint8_t *p) { return p[0] | (uint32_t)p[1] << 8 | (uint32_t)p[2] << 16 | (uint32_t)p[3] << 24; }
+
+static int read_header(ssn_bamreader *r, char *err, size_t errlen)
+{
+    const uint8_t *p = stream_take(r, 4);
+    int32_t i;
+    if (!p || memcmp(p, "BAM\001", 4) != 0) { snprintf(err, errlen, "wrong BAM header"); return -1; }
+    if (!(p = stream_take(r, 4))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+    r->hdr.l_text = (int32_t)le32(p);
+    if (r->hdr.l_text < 0) { snprintf(err, errlen, "bad BAM header"); return -1; }
+    r->hdr.text = (char*)calloc((size_t)r->hdr.l_text + 1, 1);
+    if (r->hdr.l_text) {
+        if (!(p = stream_take(r, (size_t)r->hdr.l_text))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+        memcpy(r->hdr.text, p, (size_t)r->hdr.l_text);
+    }
+    if (!(p = stream_take(r, 4))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+    r->hdr.n_targets = (int32_t)le32(p);
+    if (r->hdr.n_targets < 0) { snprintf(err, errlen, "bad BAM header"); return -1; }
+    r->hdr.target_name = (char**)calloc((size_t)r->hdr.n_targets + 1, sizeof(char*));
+    r->hdr.target_len = (uint32_t*)calloc((size_t)r->hdr.n_targets + 1, 4);
+    for (i = 0; i < r->hdr.n_targets; ++i) {
+        int32_t nl;
+        if (!(p = stream_take(r, 4))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+        nl = (int32_t)le32(p);
+        if (nl < 0) { snprintf(err, errlen, "bad BAM header"); return -1; }
+        r->hdr.target_name[i] = (char*)calloc((size_t)nl + 1, 1);
+        if (nl) {
+            if (!(p = stream_take(r, (size_t)nl))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+            memcpy(r->hdr.target_name[i], p, (size_t)nl);
+        }
+        if (!(p = stream_take(r, 4))) { snprintf(err, errlen, "truncated BAM header"); return -1; }
+        r->hdr.target_len[i] = le32(p);
+    }
+    return 0;
+}
+
+/* ---- windows --------------------------------------------------------------------------------------- */
+
+void ssn_window_free(ssn_window *w)
+{
+    if (!w) return;
+    free(w->buf);
+    free(w);
+}
+
+static void queue_push(ssn_bamreader *r, ssn_window *w)
+{
+    pthread_mutex_lock(&r->mu);
+    while (!r->stop && r->q_bytes > QUEUE_MAX_BYTES && r->q_head) pthread_cond_wait(&r->not_full, &r->mu);
+    w->next = 0;
+    if (r->q_tail) r->q_tail->next = w; else r->q_head = w;
+    r->q_tail = w;
+    r->q_bytes += w->len;
+    pthread_cond_signal(&r->not_empty);
+    pthread_mutex_unlock(&r->mu);
+}
+
+/* hands over every open window that ends at or before position `upto` of target `tid` (all of them when tid differs) */
+static void flush_open(ssn_bamreader *r, int32_t tid, uint32_t first_live_widx, int all)
+{
+    int i, k = 0;
+    for (i = 0; i < r->n_open; ++i) {
+        ssn_window *w = r->open[i];
+        if (all || w->tid != tid || w->widx < first_live_widx) queue_push(r, w);
+        else r->open[k++] = w;
+    }
+    r->n_open = k;
+}
+
+static ssn_window *open_window(ssn_bamreader *r, int32_t tid, uint32_t widx)
+{
+    int i;
+    ssn_window *w;
+    for (i = 0; i < r->n_open; ++i)
+        if (r->open[i]->widx == widx) return r->open[i];
+    if (r->n_open == MAX_OPEN) return 0;
+    w = (ssn_window*)calloc(1, sizeof(*w));
+    if (!w) return 0;
+    w->tid = tid; w->widx = widx;
+    /* keep ascending widx order (reads arrive sorted by start, so new windows normally go last) */
+    i = r->n_open++;
+    while (i > 0 && r->open[i - 1]->widx > widx) { r->open[i] = r->open[i - 1]; --i; }
+    r->open[i] = w;
+    return w;
+}
+
+static void window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar, const uint8_t *seq, const uint8_t *qual)
+{
+    const size_t nc = (size_t)h->n_cigar * 4, ns = ((size_t)h->l_qseq + 1) >> 1, nq = h->l_qseq;
+    uint8_t *d;
+    if (w->len + h->bytes > w->cap) {
+        size_t cap = w->cap ? w->cap * 2 : ((size_t)1 << 16);
+        while (cap < w->len + h->bytes) cap *= 2;
+        w->buf = (uint8_t*)realloc(w->buf, cap);
+        w->cap = cap;
+    }
+    d = w->buf + w->len;
+    memcpy(d, h, sizeof(*h)); d += sizeof(*h);
+    memcpy(d, cigar, nc); d += nc;
+    memcpy(d, seq, ns); d += ns;
+    memcpy(d, qual, nq);
+    w->len += h->bytes;
+    w->n_reads += 1;
+    w->n_bases += h->l_qseq;
+}
+
+/* ---- reader thread ----------------------------------------------------------------------------------- */
+
+static void *reader_main(void *v)
+{
+    ssn_bamreader *r = (ssn_bamreader*)v;
+    int32_t max_tid = -1;
+    uint32_t prev_beg = 0;          /* cursor position at the next fetch (0 before the first passing read) */
+    for (;;) {
+        const uint8_t *p;
+        int32_t block_len, tid, pos;
+        uint32_t x2, x3, l_qseq, mapq, l_qname, flag, n_cigar, k, end;
+        const uint8_t *cigar, *seq, *qual;
+        ssn_read h;
+        uint32_t w0, w1, wi;
+        if (r->stop) break;
+        if (!(p = stream_take(r, 4))) break;
+        block_len = (int32_t)le32(p);
+        if (block_len < 32) break;
+        if (!(p = stream_take(r, (size_t)block_len))) break;
+        r->n_records += 1;
+        tid = (int32_t)le32(p); pos = (int32_t)le32(p + 4);
+        x2 = le32(p + 8); x3 = le32(p + 12); l_qseq = le32(p + 16);
+        mapq = (x2 >> 8) & 0xff; l_qname = x2 & 0xff; flag = x3 >> 16; n_cigar = x3 & 0xffff;
+        if ((flag & (uint32_t)r->flag_mask) || (int)mapq < r->mapq_thresh) continue;       /* sniper_pileup.c:208 */
+        if ((size_t)32 + l_qname + (size_t)n_cigar * 4 + ((size_t)l_qseq + 1) / 2 + l_qseq > (size_t)block_len) break;
+        cigar = p + 32 + l_qname;
+        seq = cigar + (size_t)n_cigar * 4;
+        qual = seq + ((size_t)l_qseq + 1) / 2;
+        end = (uint32_t)pos;                                                                 /* bam_calend, bam.c:37-47 */
+        for (k = 0; k < n_cigar; ++k) {
+            const uint32_t c = le32(cigar + 4 * k), op = c & 0xf;
+            if (op == 0 || op == 2 || op == 3) end += c >> 4;
+        }
+        if (tid < max_tid) {                                                                 /* sniper_pileup.c:211-214 */
+            fprintf(stderr, "[bam_pileup_core] the input is not sorted. Abort!\n");
+            abort();
+        }
+        if (tid == max_tid && (uint32_t)pos < prev_beg) {
+            /* positions running backwards inside a target: the reference does not notice (its test at :211 is
+             * shadowed by tid >= max_tid) and piles such reads from the cursor onwards only; this reader needs
+             * sorted starts, so it stops here like on any other unsorted input */
+            fprintf(stderr, "[bam_pileup_core] the input is not sorted. Abort!\n");
+            abort();
+        }
+        {
+            const int keep = end > prev_beg;                                                 /* sniper_pileup.c:216 */
+            max_tid = tid; prev_beg = (uint32_t)pos;
+            if (!keep || tid < 0 || pos < 0 || end <= (uint32_t)pos) continue;
+        }
+        h.beg = pos; h.end = (int32_t)end; h.l_qseq = l_qseq; h.n_cigar = (uint16_t)n_cigar;
+        h.mapq = (uint8_t)mapq; h.strand = (flag & 16) ? 1 : 0;
+        h.bytes = (uint32_t)((sizeof(h) + (size_t)n_cigar * 4 + ((size_t)l_qseq + 1) / 2 + l_qseq + 3) & ~(size_t)3);
+        w0 = (uint32_t)pos >> SSN_WINDOW_SHIFT; w1 = (end - 1) >> SSN_WINDOW_SHIFT;
+        flush_open(r, tid, w0, 0);
+        for (wi = w0; wi <= w1; ++wi) {
+            ssn_window *w = open_window(r, tid, wi);
+            if (!w) {
+                fprintf(stderr, "[ssn_bamread] a read spans more than %d windows of %u positions; the rest of it is ignored\n", MAX_OPEN, SSN_WINDOW);
+                break;
+            }
+            window_append(w, &h, cigar, seq, qual);
+        }
+    }
+    flush_open(r, 0, 0, 1);
+    pthread_mutex_lock(&r->mu);
+    r->finished = 1;
+    pthread_cond_broadcast(&r->not_empty);
+    pthread_mutex_unlock(&r->mu);
+    return 0;
+}
+
+/* ---- API ------------------------------------------------------------------------------------------------ */
+
+ssn_bamreader *ssn_bamreader_open(const char *path, int flag_mask, int mapq_thresh, ssn_pool *pool, char *err, size_t errlen)
+{
+    ssn_bamreader *r = (ssn_bamreader*)calloc(1, sizeof(*r));
+    if (!r) { snprintf(err, errlen, "out of memory"); return 0; }
+    r->z = ssn_bgzf_open(path, pool);
+    if (!r->z) { snprintf(err, errlen, "cannot open %s", path); free(r); return 0; }
+    r->flag_mask = flag_mask < 0 ? SSN_BAM_DEF_MASK : (4 | flag_mask);       /* bam_plbuf_set_mask, sniper_pileup.c:146-150 */
+    r->mapq_thresh = mapq_thresh < 0 ? 0 : mapq_thresh;                      /* bam_plbuf_set_mapq_thresh, :139-143 */
+    pthread_mutex_init(&r->mu, 0);
+    pthread_cond_init(&r->not_empty, 0);
+    pthread_cond_init(&r->not_full, 0);
+    if (read_header(r, err, errlen) != 0) { ssn_bamreader_close(r); return 0; }
+    if (pthread_create(&r->th, 0, reader_main, r) != 0) { snprintf(err, errlen, "cannot start the reader thread"); ssn_bamreader_close(r); return 0; }
+    r->th_started = 1;
+    return r;
+}
+
+const ssn_bam_header *ssn_bamreader_header(const ssn_bamreader *r) { return &r->hdr; }
+uint64_t ssn_bamreader_records(const ssn_bamreader *r) { return r->n_records; }
+
+ssn_window *ssn_bamreader_pop(ssn_bamreader *r)
+{
+    ssn_window *w;
+    pthread_mutex_lock(&r->mu);
+    while (!r->q_head && !r->finished) pthread_cond_wait(&r->not_empty, &r->mu);
+    w = r->q_head;
+    if (w) {
+        r->q_head = w->next;
+        if (!r->q_head) r->q_tail = 0;
+        r->q_bytes -= w->len;
+        w->next = 0;
+        pthread_cond_signal(&r->not_full);
+    }
+    pthread_mutex_unlock(&r->mu);
+    return w;
+}
+
+void ssn_bamreader_close(ssn_bamreader *r)
+{
+    int i;
+    if (!r) return;
+    if (r->th_started) {
+        pthread_mutex_lock(&r->mu);
+        r->stop = 1;
+        pthread_cond_broadcast(&r->not_full);
+        pthread_mutex_unlock(&r->mu);
+        pthread_join(r->th, 0);
+    }
+    while (r->q_head) { ssn_window *w = r->q_head; r->q_head = w->next; ssn_window_free(w); }
+    for (i = 0; i < r->n_open; ++i) ssn_window_free(r->open[i]);
+    if (r->hdr.target_name) for (i = 0; i < r->hdr.n_targets; ++i) free(r->hdr.target_name[i]);
+    free(r->hdr.target_name); free(r->hdr.target_len); free(r->hdr.text);
+    free(r->carry);
+    ssn_bgzf_close(r->z);
+    pthread_mutex_destroy(&r->mu);
+    pthread_cond_destroy(&r->not_empty);
+    pthread_cond_destroy(&r->not_full);
+    free(r);
+}

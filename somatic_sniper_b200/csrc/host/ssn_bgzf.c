@@ -1,0 +1,165 @@
+#include "ssn_bgzf.h"
+
+#include <errno.h>
+#include <fcntl.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+#include <zlib.h>
+
+#define RAW_CAP (8u << 20)      /* compressed bytes held at once */
+#define MAX_BLOCKS 512          /* blocks inflated per call */
+
+typedef struct {
+    const uint8_t *cdata;
+    uint32_t clen, ulen;
+    size_t uoff;
+    int bad;
+} blk;
+
+struct ssn_bgzf {
+    int fd, own_fd, eof_file, done;
+    ssn_pool *pool;
+    uint8_t *raw;
+    size_t raw_len, raw_pos;
+    uint8_t *out;
+    size_t out_cap;
+    blk blocks[MAX_BLOCKS];
+    uint64_t consumed;
+};
+
+ssn_bgzf *ssn_bgzf_open(const char *path, ssn_pool *pool)
+{
+    ssn_bgzf *z = (ssn_bgzf*)calloc(1, sizeof(*z));
+    if (!z) return 0;
+    if (strcmp(path, "-") == 0) { z->fd = 0; z->own_fd = 0; }
+    else {
+        z->fd = open(path, O_RDONLY);
+        z->own_fd = 1;
+        if (z->fd < 0) { free(z); return 0; }
+#ifdef POSIX_FADV_SEQUENTIAL
+        posix_fadvise(z->fd, 0, 0, POSIX_FADV_SEQUENTIAL);
+#endif
+    }
+    z->pool = pool;
+    z->raw = (uint8_t*)malloc(RAW_CAP);
+    z->out_cap = (size_t)MAX_BLOCKS * 65536;
+    z->out = (uint8_t*)malloc(z->out_cap);
+    if (!z->raw || !z->out) { ssn_bgzf_close(z); return 0; }
+    return z;
+}
+
+void ssn_bgzf_close(ssn_bgzf *z)
+{
+    if (!z) return;
+    if (z->own_fd && z->fd >= 0) close(z->fd);
+    free(z->raw); free(z->out); free(z);
+}
+
+uint64_t ssn_bgzf_compressed_bytes(const ssn_bgzf *z) { return z->consumed; }
+
+static void refill(ssn_bgzf *z)
+{
+    if (z->raw_pos > 0) {
+        memmove(z->raw, z->raw + z->raw_pos, z->raw_len - z->raw_pos);
+        z->raw_len -= z->raw_pos;
+        z->raw_pos = 0;
+    }
+    while (!z->eof_file && z->raw_len < RAW_CAP) {
+        ssize_t r = read(z->fd, z->raw + z->raw_len, RAW_CAP - z->raw_len);
+        if (r < 0) { if (errno == EINTR) continue; z->eof_file = 1; break; }
+        if (r == 0) { z->eof_file = 1; break; }
+        z->raw_len += (size_t)r;
+    }
+}
+
+/* parses one block header at p (avail bytes); 0 = need more bytes, <0 = invalid, else total block length */
+static int parse_block(const uint8_t *p, size_t avail, blk *b)
+{
+    uint32_t xlen, total = 0, x;
+    if (avail < 18) return 0;
+    if (p[0] != 31 || p[1] != 139 || p[2] != 8 || !(p[3] & 4)) return -1;
+    xlen = p[10] | (uint32_t)p[11] << 8;
+    if (avail < 12 + xlen) return 0;
+    for (x = 0; x + 4 <= xlen;) {
+        const uint8_t *s = p + 12 + x;
+        const uint32_t slen = s[2] | (uint32_t)s[3] << 8;
+        if (s[0] == 'B' && s[1] == 'C' && slen == 2 && x + 6 <= xlen) total = (s[4] | (uint32_t)s[5] << 8) + 1;
+        x += 4 + slen;
+    }
+    if (total == 0 || total < 12 + xlen + 8) return -1;
+    if (avail < total) return 0;
+    b->cdata = p + 12 + xlen;
+    b->clen = total - 12 - xlen - 8;
+    b->ulen = p[total - 4] | (uint32_t)p[total - 3] << 8 | (uint32_t)p[total - 2] << 16 | (uint32_t)p[total - 1] << 24;
+    b->bad = 0;
+    return (int)total;
+}
+
+static __thread z_stream t_zs;
+static __thread int t_zs_ready = 0;
+
+typedef struct { ssn_bgzf *z; } inflate_arg;
+
+static void inflate_one(void *arg, int i)
+{
+    ssn_bgzf *z = ((inflate_arg*)arg)->z;
+    blk *b = &z->blocks[i];
+    int st;
+    if (!t_zs_ready) {
+        memset(&t_zs, 0, sizeof(t_zs));
+        if (inflateInit2(&t_zs, -15) != Z_OK) { b->bad = 1; return; }
+        t_zs_ready = 1;
+    } else inflateReset(&t_zs);
+    t_zs.next_in = (Bytef*)b->cdata; t_zs.avail_in = b->clen;
+    t_zs.next_out = z->out + b->uoff; t_zs.avail_out = b->ulen;
+    st = inflate(&t_zs, Z_FINISH);
+    if (st != Z_STREAM_END || t_zs.avail_out != 0) b->bad = 1;
+}
+
+int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
+{
+    int n = 0, i, stop = 0;
+    size_t uoff = 0;
+    inflate_arg a;
+    *data = 0; *len = 0;
+    if (z->done) return 0;
+    if (z->raw_len - z->raw_pos < (RAW_CAP >> 1)) refill(z);
+    while (n < MAX_BLOCKS) {
+        blk *b = &z->blocks[n];
+        int r = parse_block(z->raw + z->raw_pos, z->raw_len - z->raw_pos, b);
+        if (r == 0) {
+            if (n > 0) break;
+            if (z->eof_file) {
+                if (z->raw_len != z->raw_pos) fprintf(stderr, "[ssn_bgzf] truncated block at the end of the file\n");
+                stop = 1; break;
+            }
+            refill(z);
+            if (z->eof_file && z->raw_len - z->raw_pos < 18) { stop = 1; if (z->raw_len != z->raw_pos) fprintf(stderr, "[ssn_bgzf] truncated block at the end of the file\n"); break; }
+            continue;
+        }
+        if (r < 0) { fprintf(stderr, "[ssn_bgzf] invalid block header\n"); stop = 1; break; }
+        z->raw_pos += (size_t)r;
+        z->consumed += (uint64_t)r;
+        if (b->ulen == 0) { stop = 1; break; }          /* empty block: the reference's reader stops here */
+        if (b->ulen > 65536) { fprintf(stderr, "[ssn_bgzf] block larger than 64 KiB\n"); stop = 1; break; }
+        b->uoff = uoff; uoff += b->ulen;
+        ++n;
+    }
+    if (stop) z->done = 1;
+    if (n == 0) return 0;
+    a.z = z;
+    ssn_pool_for(z->pool, n, inflate_one, &a);
+    for (i = 0; i < n; ++i) {
+        if (z->blocks[i].bad) {
+            fprintf(stderr, "[ssn_bgzf] inflate failed\n");
+            z->done = 1;
+            uoff = z->blocks[i].uoff;                    /* keep what came before the bad block */
+            break;
+        }
+    }
+    if (uoff == 0) return 0;
+    *data = z->out; *len = uoff;
+    return 1;
+}

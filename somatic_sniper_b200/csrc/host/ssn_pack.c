@@ -1,0 +1,403 @@
+/*
+ * ssn_pack.c — joins the tumor and normal window streams on (tid, window) and packs the pileup columns of
+ * both samples into SoA batches (include/ssn_host.h).  Two parallel phases over the windows of a batch:
+ *   count  per-position read-base counts of each sample (difference array over the CIGAR match runs)
+ *   fill   per-column offsets, then every read base is written at its column's cursor
+ * The pileup contents follow get_next_pos/resolve_cigar (src/lib/sniper/sniper_pileup.c:57-104,186-205): a
+ * kept read contributes a base at every position covered by a CIGAR M run; positions inside D yield the
+ * is_del entries every consumer skips (sniper_maqcns.c:147, dqstats.c:20) and positions inside N yield
+ * nothing (:98); I and S advance the query only; H, P and the operators samtools-0.1.6 does not know
+ * (=, X) advance nothing (QUIRK B6).
+ */
+#include <pthread.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include "ssn_bamread.h"
+#include "ssn_fasta.h"
+#include "ssn_host.h"
+#include "ssn_nt16.h"
+#include "ssn_pool.h"
+
+#define GROUP_MAX 16           /* windows pulled per batch at most */
+
+static __thread char h_err[512] = "";
+const char *ssn_host_last_error(void) { return h_err; }
+static void set_err(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(h_err, sizeof(h_err), fmt, ap);
+    va_end(ap);
+}
+
+static double now_s(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+/* a joined window: both samples' reads plus the per-position counts */
+typedef struct pair {
+    ssn_window *w[2];             /* 0 tumor, 1 normal */
+    uint32_t *cnt[2];             /* [SSN_WINDOW] read bases per position */
+    uint32_t next_i;              /* first position index not yet emitted */
+    const char *ref; int ref_len; /* target sequence (owned by the packer's cache) */
+} pair;
+
+typedef struct { int32_t tid; char *seq; int len; } ref_slot;
+
+typedef struct {                  /* one fill task */
+    pair *p;
+    uint32_t i0, i1;              /* position indices inside the window */
+    uint32_t col_base;
+    uint64_t ent_base;
+} segment;
+
+struct ssn_packer {
+    ssn_pool *pool;
+    ssn_bamreader *rd[2];
+    ssn_window *head[2];          /* next window of each stream (look-ahead of the join) */
+    int ended;
+    ssn_fasta *fa;
+    ref_slot refs[4];
+    pair *pending[GROUP_MAX + 1];
+    int n_pending;
+    ssn_packer_stats st;
+    /* the batch being filled */
+    const ssn_batch_view *view;
+    const ssn_colmap *map;
+    segment seg[GROUP_MAX + 1];
+};
+
+/* ---- CIGAR walk -------------------------------------------------------------------------------------------- */
+
+static inline const uint32_t *read_cigar(const ssn_read *h) { return (const uint32_t*)((const uint8_t*)h + sizeof(*h)); }
+
+/* adds +1/-1 marks for every M run of the read clipped to [lo, hi) */
+static void count_read(const ssn_read *h, uint32_t lo, uint32_t hi, int32_t *diff)
+{
+    const uint32_t *cg = read_cigar(h);
+    uint32_t x = (uint32_t)h->beg, k;
+    for (k = 0; k < h->n_cigar && x < hi; ++k) {
+        const uint32_t op = cg[k] & 0xf, l = cg[k] >> 4;
+        if (op == 0) {
+            const uint32_t a = x > lo ? x : lo, b = x + l < hi ? x + l : hi;
+            if (a < b) { diff[a - lo] += 1; diff[b - lo] -= 1; }
+            x += l;
+        } else if (op == 2 || op == 3) x += l;
+    }
+}
+
+static void count_task(void *arg, int idx)
+{
+    pair *p = ((pair**)arg)[idx];
+    int s;
+    for (s = 0; s < 2; ++s) {
+        const ssn_window *w = p->w[s];
+        const uint32_t lo = w->widx << SSN_WINDOW_SHIFT, hi = lo + SSN_WINDOW;
+        int32_t *diff = (int32_t*)calloc(SSN_WINDOW + 1, sizeof(int32_t));
+        uint32_t *cnt = (uint32_t*)malloc(sizeof(uint32_t) * SSN_WINDOW);
+        size_t o = 0;
+        uint32_t i;
+        int32_t run = 0;
+        while (o < w->len) {
+            const ssn_read *h = (const ssn_read*)(w->buf + o);
+            count_read(h, lo, hi, diff);
+            o += h->bytes;
+        }
+        for (i = 0; i < SSN_WINDOW; ++i) { run += diff[i]; cnt[i] = (uint32_t)run; }
+        free(diff);
+        p->cnt[s] = cnt;
+    }
+    /* a column exists where both samples have a read base and the reference base is callable */
+    {
+        const uint32_t lo = p->w[0]->widx << SSN_WINDOW_SHIFT;
+        uint32_t i;
+        for (i = 0; i < SSN_WINDOW; ++i) {
+            const uint32_t pos = lo + i;
+            const int rb = (p->ref && (int)pos < p->ref_len) ? (unsigned char)p->ref[pos] : 'N';
+            if (p->cnt[0][i] == 0 || p->cnt[1][i] == 0 || ssn_nt16_table(rb) == 15) { p->cnt[0][i] = 0; p->cnt[1][i] = 0; }
+        }
+    }
+}
+
+/* writes the read's bases that fall on live columns of [lo + i0, lo + i1) at their cursors */
+static void fill_read(const ssn_read *h, uint32_t lo, uint32_t a_lo, uint32_t a_hi, uint32_t *cur,
+                      uint8_t *bs, uint8_t *bq, uint8_t *mq)
+{
+    const uint32_t *cg = read_cigar(h);
+    const uint8_t *seq = (const uint8_t*)(cg + h->n_cigar), *qual = seq + ((h->l_qseq + 1) >> 1);
+    const uint8_t strand = (uint8_t)(h->strand << 4), mapq = h->mapq;
+    uint32_t x = (uint32_t)h->beg, y = 0, k;
+    for (k = 0; k < h->n_cigar && x < a_hi; ++k) {
+        const uint32_t op = cg[k] & 0xf, l = cg[k] >> 4;
+        if (op == 0) {
+            const uint32_t a = x > a_lo ? x : a_lo, b = x + l < a_hi ? x + l : a_hi;
+            uint32_t pos;
+            for (pos = a; pos < b; ++pos) {
+                const uint32_t c = cur[pos - lo];
+                if (c != 0xffffffffu) {
+                    const uint32_t q = y + (pos - x);
+                    if (q < h->l_qseq) {
+                        bs[c] = (uint8_t)(((seq[q >> 1] >> ((~q & 1) << 2)) & 0xf) | strand);   /* bam1_seqi */
+                        bq[c] = qual[q];
+                        mq[c] = mapq;
+                    } else { bs[c] = (uint8_t)(15 | strand); bq[c] = 0; mq[c] = mapq; }      /* CIGAR longer than the read */
+                    cur[pos - lo] = c + 1;
+                }
+            }
+            x += l; y += l;
+        } else if (op == 2 || op == 3) x += l;
+        else if (op == 1 || op == 4) y += l;
+    }
+}
+
+static void fill_task(void *arg, int idx)
+{
+    ssn_packer *pk = (ssn_packer*)arg;
+    const segment *sg = &pk->seg[idx];
+    pair *p = sg->p;
+    const ssn_batch_view *v = pk->view;
+    const ssn_colmap *m = pk->map;
+    const uint32_t lo = p->w[0]->widx << SSN_WINDOW_SHIFT;
+    uint32_t col = sg->col_base, i;
+    uint64_t e = sg->ent_base;
+    int s;
+    /* offsets and cursors; the counts of [i0, i1) are consumed */
+    for (i = sg->i0; i < sg->i1; ++i) {
+        const uint32_t ct = p->cnt[0][i], cn = p->cnt[1][i];
+        if (ct == 0) { p->cnt[0][i] = 0xffffffffu; p->cnt[1][i] = 0xffffffffu; continue; }
+        {
+            const uint32_t pos = lo + i;
+            const int rb = (unsigned char)p->ref[pos];
+            v->off[2 * (size_t)col] = (uint32_t)e;
+            v->off[2 * (size_t)col + 1] = (uint32_t)(e + ct);
+            v->ref_nt16[col] = (uint8_t)ssn_nt16_table(rb);
+            m->tid[col] = p->w[0]->tid; m->pos[col] = pos; m->ref_char[col] = (uint8_t)rb;
+            p->cnt[0][i] = (uint32_t)e; p->cnt[1][i] = (uint32_t)(e + ct);
+            e += (uint64_t)ct + cn;
+            ++col;
+        }
+    }
+    for (s = 0; s < 2; ++s) {
+        const ssn_window *w = p->w[s];
+        size_t o = 0;
+        while (o < w->len) {
+            const ssn_read *h = (const ssn_read*)(w->buf + o);
+            if ((uint32_t)h->end > lo + sg->i0 && (uint32_t)h->beg < lo + sg->i1)
+                fill_read(h, lo, lo + sg->i0, lo + sg->i1, p->cnt[s], v->bs, v->bq, v->mq);
+            o += h->bytes;
+        }
+    }
+}
+
+/* ---- join ---------------------------------------------------------------------------------------------------- */
+
+static void pair_free(pair *p)
+{
+    if (!p) return;
+    ssn_window_free(p->w[0]); ssn_window_free(p->w[1]);
+    free(p->cnt[0]); free(p->cnt[1]);
+    free(p);
+}
+
+static int win_cmp(const ssn_window *a, const ssn_window *b)
+{
+    if (a->tid != b->tid) return a->tid < b->tid ? -1 : 1;
+    if (a->widx != b->widx) return a->widx < b->widx ? -1 : 1;
+    return 0;
+}
+
+/* next window present in both streams, NULL when either stream is exhausted (sniper_pileup.c:245) */
+static pair *next_pair(ssn_packer *pk)
+{
+    pair *p;
+    if (pk->ended) return 0;
+    for (;;) {
+        int s, c;
+        for (s = 0; s < 2; ++s)
+            if (!pk->head[s]) {
+                pk->head[s] = ssn_bamreader_pop(pk->rd[s]);
+                if (!pk->head[s]) { pk->ended = 1; return 0; }
+            }
+        c = win_cmp(pk->head[0], pk->head[1]);
+        if (c == 0) break;
+        s = c < 0 ? 0 : 1;                       /* the stream that is behind has no partner for this window */
+        ssn_window_free(pk->head[s]);
+        pk->head[s] = 0;
+    }
+    p = (pair*)calloc(1, sizeof(*p));
+    p->w[0] = pk->head[0]; p->w[1] = pk->head[1];
+    pk->head[0] = pk->head[1] = 0;
+    return p;
+}
+
+/* target sequence through a tiny cache (tids arrive in ascending order) */
+static void attach_ref(ssn_packer *pk, pair *p)
+{
+    const int32_t tid = p->w[0]->tid;
+    const int n = (int)(sizeof(pk->refs) / sizeof(pk->refs[0]));
+    int i, victim = 0;
+    for (i = 0; i < n; ++i)
+        if (pk->refs[i].seq && pk->refs[i].tid == tid) { p->ref = pk->refs[i].seq; p->ref_len = pk->refs[i].len; return; }
+    for (i = 0; i < n; ++i) {
+        if (!pk->refs[i].seq && pk->refs[i].tid == -1) { victim = i; break; }
+        if (pk->refs[i].tid < pk->refs[victim].tid) victim = i;
+    }
+    /* the victim's tid is older than every window still pending (pending tids are >= the batch's first) */
+    free(pk->refs[victim].seq);
+    pk->refs[victim].seq = 0; pk->refs[victim].len = 0; pk->refs[victim].tid = tid;
+    {
+        const ssn_bam_header *h = ssn_bamreader_header(pk->rd[0]);      /* names come from the tumor header, QUIRK B9 */
+        if (pk->fa && tid >= 0 && tid < h->n_targets)
+            pk->refs[victim].seq = ssn_fasta_fetch(pk->fa, h->target_name[tid], &pk->refs[victim].len);
+        if (!pk->refs[victim].seq) { pk->refs[victim].seq = (char*)calloc(1, 1); pk->refs[victim].len = 0; }
+    }
+    p->ref = pk->refs[victim].seq; p->ref_len = pk->refs[victim].len;
+}
+
+/* ---- API -------------------------------------------------------------------------------------------------------- */
+
+ssn_status ssn_packer_open(const char *tumor_bam, const char *normal_bam, const char *fasta, int min_mapq,
+                           int n_threads, ssn_packer **out)
+{
+    ssn_packer *pk;
+    char err[256];
+    int i;
+    if (!tumor_bam || !normal_bam || !out) { set_err("ssn_packer_open: null argument"); return SSN_ERR_ARG; }
+    pk = (ssn_packer*)calloc(1, sizeof(*pk));
+    if (!pk) { set_err("out of memory"); return SSN_ERR_NOMEM; }
+    for (i = 0; i < (int)(sizeof(pk->refs) / sizeof(pk->refs[0])); ++i) pk->refs[i].tid = -1;
+    pk->pool = ssn_pool_create(n_threads);
+    if (fasta) {
+        pk->fa = ssn_fasta_load(fasta);
+        /* like the reference (main.c:106-108, somatic_sniper.c:112-117) a FASTA that cannot be loaded is not fatal:
+         * every reference base then reads as 'N' and no column is ever emitted */
+    }
+    pk->rd[0] = ssn_bamreader_open(tumor_bam, -1, min_mapq, pk->pool, err, sizeof(err));
+    if (!pk->rd[0]) { set_err("tumor BAM: %s", err); ssn_packer_close(pk); return SSN_ERR_ARG; }
+    pk->rd[1] = ssn_bamreader_open(normal_bam, -1, min_mapq, pk->pool, err, sizeof(err));
+    if (!pk->rd[1]) { set_err("normal BAM: %s", err); ssn_packer_close(pk); return SSN_ERR_ARG; }
+    *out = pk;
+    return SSN_OK;
+}
+
+void ssn_packer_close(ssn_packer *pk)
+{
+    int i;
+    if (!pk) return;
+    for (i = 0; i < pk->n_pending; ++i) pair_free(pk->pending[i]);
+    ssn_window_free(pk->head[0]); ssn_window_free(pk->head[1]);
+    if (pk->rd[0]) ssn_bamreader_close(pk->rd[0]);
+    if (pk->rd[1]) ssn_bamreader_close(pk->rd[1]);
+    for (i = 0; i < (int)(sizeof(pk->refs) / sizeof(pk->refs[0])); ++i) free(pk->refs[i].seq);
+    ssn_fasta_destroy(pk->fa);
+    ssn_pool_destroy(pk->pool);
+    free(pk);
+}
+
+int32_t ssn_packer_n_targets(const ssn_packer *pk, int which) { return ssn_bamreader_header(pk->rd[which ? 1 : 0])->n_targets; }
+
+const char *ssn_packer_target_name(const ssn_packer *pk, int which, int32_t tid)
+{
+    const ssn_bam_header *h = ssn_bamreader_header(pk->rd[which ? 1 : 0]);
+    return (tid >= 0 && tid < h->n_targets) ? h->target_name[tid] : 0;
+}
+
+void ssn_packer_get_stats(const ssn_packer *pk, ssn_packer_stats *out)
+{
+    *out = pk->st;
+    out->records[0] = ssn_bamreader_records(pk->rd[0]);
+    out->records[1] = ssn_bamreader_records(pk->rd[1]);
+}
+
+ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn_colmap *map,
+                           uint32_t *n_columns, uint64_t *n_entries)
+{
+    uint32_t ncol = 0;
+    uint64_t nent = 0;
+    int nseg = 0, i, fresh0, full = 0;
+    double t0, t1;
+    if (!pk || !view || !map || !n_columns || !n_entries) { set_err("ssn_packer_next: null argument"); return SSN_ERR_ARG; }
+    if (view->max_columns == 0 || view->max_entries == 0 || view->max_entries >= 0xffffffffull) { set_err("ssn_packer_next: bad batch capacity"); return SSN_ERR_ARG; }
+    *n_columns = 0; *n_entries = 0;
+    pk->view = view; pk->map = map;
+
+    /* 1. pull joined windows while their upper bounds suggest they still fit */
+    t0 = now_s();
+    fresh0 = pk->n_pending;
+    {
+        uint64_t bound_ent = 0, bound_col = 0;
+        for (i = 0; i < pk->n_pending; ++i) {
+            bound_ent += pk->pending[i]->w[0]->n_bases + pk->pending[i]->w[1]->n_bases;
+            bound_col += SSN_WINDOW - pk->pending[i]->next_i;
+        }
+        while (pk->n_pending < GROUP_MAX && bound_ent < view->max_entries && bound_col < view->max_columns) {
+            pair *p = next_pair(pk);
+            if (!p) break;
+            attach_ref(pk, p);
+            pk->pending[pk->n_pending++] = p;
+            bound_ent += p->w[0]->n_bases + p->w[1]->n_bases;
+            bound_col += SSN_WINDOW;
+        }
+    }
+    t1 = now_s(); pk->st.t_wait += t1 - t0;
+    if (pk->n_pending == 0) return SSN_OK;
+
+    /* 2. count the new windows */
+    if (pk->n_pending > fresh0) ssn_pool_for(pk->pool, pk->n_pending - fresh0, count_task, pk->pending + fresh0);
+    t0 = now_s(); pk->st.t_count += t0 - t1;
+
+    /* 3. cut the batch: whole windows while they fit, then the longest prefix of the next one */
+    for (i = 0; i < pk->n_pending && !full; ++i) {
+        pair *p = pk->pending[i];
+        segment *sg = &pk->seg[nseg];
+        uint32_t j, c = 0;
+        uint64_t e = 0;
+        for (j = p->next_i; j < SSN_WINDOW; ++j) {
+            const uint32_t ct = p->cnt[0][j];
+            if (ct == 0) continue;
+            {
+                const uint64_t add = (uint64_t)ct + p->cnt[1][j];
+                if (ncol + c + 1 > view->max_columns || nent + e + add > view->max_entries) { full = 1; break; }
+                c += 1; e += add;
+            }
+        }
+        if (full && c == 0 && ncol == 0) {
+            set_err("column %d:%u holds %llu read bases; the batch capacity is %llu", p->w[0]->tid,
+                    (p->w[0]->widx << SSN_WINDOW_SHIFT) + j, (unsigned long long)((uint64_t)p->cnt[0][j] + p->cnt[1][j]),
+                    (unsigned long long)view->max_entries);
+            return SSN_ERR_OVERFLOW;
+        }
+        if (j > p->next_i) {
+            sg->p = p; sg->i0 = p->next_i; sg->i1 = j; sg->col_base = ncol; sg->ent_base = nent;
+            ++nseg;
+            ncol += c; nent += e;
+            p->next_i = j;
+        }
+    }
+
+    /* 4. fill */
+    ssn_pool_for(pk->pool, nseg, fill_task, pk);
+    view->off[2 * (size_t)ncol] = (uint32_t)nent;
+    t1 = now_s(); pk->st.t_fill += t1 - t0;
+
+    /* 5. retire the windows that are used up */
+    {
+        int k = 0;
+        for (i = 0; i < pk->n_pending; ++i) {
+            if (pk->pending[i]->next_i >= SSN_WINDOW) pair_free(pk->pending[i]);
+            else pk->pending[k++] = pk->pending[i];
+        }
+        pk->n_pending = k;
+    }
+    pk->st.columns += ncol; pk->st.entries += nent; pk->st.batches += 1;
+    *n_columns = ncol; *n_entries = nent;
+    if (ncol == 0) return ssn_packer_next(pk, view, map, n_columns, n_entries);   /* windows without a common column */
+    return SSN_OK;
+}

@@ -1,0 +1,105 @@
+"""ctypes mirror of include/ssn_host.h (libssn_host.so: the BAM -> SoA column packer and the line writers).
+Holds no logic of its own; tests and tools drive the native code through it."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import api
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+CLI = os.path.join(_HERE, "bin", "bam-somaticsniper")
+
+
+class ColMap(C.Structure):
+    _fields_ = [("tid", C.POINTER(C.c_int32)), ("pos", C.POINTER(C.c_uint32)), ("ref_char", C.POINTER(C.c_uint8))]
+
+
+class PackerStats(C.Structure):
+    _fields_ = [("records", C.c_uint64 * 2), ("columns", C.c_uint64), ("entries", C.c_uint64), ("batches", C.c_uint64),
+                ("t_wait", C.c_double), ("t_count", C.c_double), ("t_fill", C.c_double)]
+
+
+HOST_SYMBOLS = ["ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
+                "ssn_packer_get_stats", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
+                "ssn_writer_destroy", "ssn_writer_n_formats", "ssn_writer_format_name"]
+
+
+def load_library():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = os.path.join(_HERE, "lib", "libssn_host.so")
+    if not os.path.exists(path):
+        raise RuntimeError("libssn_host.so is not built (run python __graft_entry__.py)")
+    lib = C.CDLL(path)
+    lib.ssn_packer_open.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    lib.ssn_packer_open.restype = C.c_int
+    lib.ssn_packer_close.argtypes = [C.c_void_p]
+    lib.ssn_packer_close.restype = None
+    lib.ssn_packer_n_targets.argtypes = [C.c_void_p, C.c_int]
+    lib.ssn_packer_n_targets.restype = C.c_int32
+    lib.ssn_packer_target_name.argtypes = [C.c_void_p, C.c_int, C.c_int32]
+    lib.ssn_packer_target_name.restype = C.c_char_p
+    lib.ssn_packer_next.argtypes = [C.c_void_p, C.POINTER(api.BatchView), C.POINTER(ColMap), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+    lib.ssn_packer_next.restype = C.c_int
+    lib.ssn_packer_get_stats.argtypes = [C.c_void_p, C.POINTER(PackerStats)]
+    lib.ssn_packer_get_stats.restype = None
+    lib.ssn_host_last_error.restype = C.c_char_p
+    lib.ssn_writer_n_formats.restype = C.c_int
+    lib.ssn_writer_format_name.argtypes = [C.c_int]
+    lib.ssn_writer_format_name.restype = C.c_char_p
+    _LIB = lib
+    return lib
+
+
+class Packer:
+    """Iterates the SoA batches of a tumor/normal BAM pair (host arrays owned by numpy; no GPU involved)."""
+
+    def __init__(self, tumor, normal, fasta, min_mapq=0, threads=2, max_columns=1 << 16, max_entries=1 << 23):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        st = self.lib.ssn_packer_open(os.fsencode(tumor), os.fsencode(normal), os.fsencode(fasta) if fasta else None,
+                                      int(min_mapq), int(threads), C.byref(self.h))
+        if st != 0:
+            raise RuntimeError("ssn_packer_open: %s" % self.lib.ssn_host_last_error().decode())
+        self.max_columns, self.max_entries = max_columns, max_entries
+
+    def close(self):
+        if self.h:
+            self.lib.ssn_packer_close(self.h)
+            self.h = C.c_void_p()
+
+    def target_names(self, which=0):
+        n = self.lib.ssn_packer_n_targets(self.h, which)
+        return [self.lib.ssn_packer_target_name(self.h, which, i).decode() for i in range(n)]
+
+    def stats(self):
+        s = PackerStats()
+        self.lib.ssn_packer_get_stats(self.h, C.byref(s))
+        return s
+
+    def __iter__(self):
+        mc, me = self.max_columns, self.max_entries
+        while True:
+            off = np.zeros(2 * mc + 1, np.uint32)
+            bs = np.zeros(me + 64, np.uint8); bq = np.zeros(me + 64, np.uint8); mq = np.zeros(me + 64, np.uint8)
+            ref16 = np.zeros(mc + 64, np.uint8)
+            tid = np.zeros(mc, np.int32); pos = np.zeros(mc, np.uint32); refc = np.zeros(mc, np.uint8)
+            view = api.BatchView()
+            view.off = off.ctypes.data_as(C.POINTER(C.c_uint32))
+            view.bs = bs.ctypes.data_as(C.POINTER(C.c_uint8)); view.bq = bq.ctypes.data_as(C.POINTER(C.c_uint8))
+            view.mq = mq.ctypes.data_as(C.POINTER(C.c_uint8)); view.ref_nt16 = ref16.ctypes.data_as(C.POINTER(C.c_uint8))
+            view.max_columns = mc; view.max_entries = me
+            cm = ColMap(tid.ctypes.data_as(C.POINTER(C.c_int32)), pos.ctypes.data_as(C.POINTER(C.c_uint32)),
+                        refc.ctypes.data_as(C.POINTER(C.c_uint8)))
+            ncol, nent = C.c_uint32(0), C.c_uint64(0)
+            st = self.lib.ssn_packer_next(self.h, C.byref(view), C.byref(cm), C.byref(ncol), C.byref(nent))
+            if st != 0:
+                raise RuntimeError("ssn_packer_next: %s" % self.lib.ssn_host_last_error().decode())
+            n, e = ncol.value, nent.value
+            if n == 0:
+                return
+            yield dict(off=off[:2 * n + 1].copy(), bs=bs[:e].copy(), bq=bq[:e].copy(), mq=mq[:e].copy(), ref_nt16=ref16[:n].copy(),
+                       ref_char=refc[:n].copy(), tid=tid[:n].copy(), pos=pos[:n].copy(), ncol=n, n_entries=e)
