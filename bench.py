@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=1_000_000, help="columns of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--backend", default="nccl", help=argparse.SUPPRESS)
     return ap.parse_args()
 
 
@@ -124,30 +125,38 @@ def slice_columns(cols, c0, c1):
                 mq=cols["mq"][e0:e1], ref_char=cols["ref_char"][c0:c1], ncol=c1 - c0, n_entries=e1 - e0)
 
 
-def dist_setup(n):
-    """torch.distributed is plumbing only: barrier + max over ranks."""
+def dist_setup(n, backend="nccl"):
+    """torch.distributed is plumbing only: barrier + max/sum over ranks.  Region shards need no data-path collective."""
     if n <= 1:
         return None, 0, 0
     import torch
     import torch.distributed as dist
     rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if backend == "nccl":
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:                                   # gloo: the CPU tests of the N>1 bookkeeping
+        dist.init_process_group(backend)
     return dist, rank, local
+
+
+def _dist_device(dist):
+    return "cuda" if dist.get_backend() == "nccl" else "cpu"
 
 
 def dist_barrier(dist):
     if dist is not None:
         import torch
         dist.barrier()
-        torch.cuda.synchronize()
+        if _dist_device(dist) == "cuda":
+            torch.cuda.synchronize()
 
 
 def dist_max(dist, x):
     if dist is None:
         return x
     import torch
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    t = torch.tensor([x], dtype=torch.float64, device=_dist_device(dist))
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
@@ -156,9 +165,21 @@ def dist_sum(dist, x):
     if dist is None:
         return x
     import torch
-    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    t = torch.tensor([x], dtype=torch.float64, device=_dist_device(dist))
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return float(t.item())
+
+
+def shard_seed(rank):
+    """Rank r scores its own region shard: an independent 1 Mb region drawn with seed 1234 + r (weak scaling)."""
+    return 1234 + rank
+
+
+def whole_job_rate(dist, columns_this_rank, steps, ms_this_rank):
+    """columns/s of the whole job: units of all ranks / the slowest rank's device time."""
+    ms_max = dist_max(dist, ms_this_rank)
+    total = dist_sum(dist, float(columns_this_rank))
+    return total * steps / (ms_max * 1e-3), ms_max, total
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -237,9 +258,9 @@ def run_reference(args):
 
 def run_b200(args):
     from somatic_sniper_b200 import api, synth
-    dist, rank, local = dist_setup(args.gpus)
+    dist, rank, local = dist_setup(args.gpus, args.backend)
     ncol = args.columns
-    cols = synth.make_columns(ncol, depth_t=args.depth_t, depth_n=args.depth_n, seed=1234 + rank)
+    cols = synth.make_columns(ncol, depth_t=args.depth_t, depth_n=args.depth_n, seed=shard_seed(rank))
     nent = int(cols["n_entries"])
     alg_bytes = synth.algorithmic_bytes(cols)
     bounds = np.linspace(0, ncol, CHUNKS + 1).astype(int)
@@ -271,9 +292,7 @@ def run_b200(args):
     n_sites = len(sites_ref)
     sc.release(b)
     sc.close()
-    ms_max = dist_max(dist, ms)
-    total_cols = dist_sum(dist, float(ncol))
-    value = total_cols * args.steps / (ms_max * 1e-3)
+    value, ms_max, total_cols = whole_job_rate(dist, ncol, args.steps, ms)
     peak, peak_src = measured_peak()
     k_avg_ms = kms / max(kn, 1)
     achieved = alg_bytes / (k_avg_ms * 1e-3) / 1e9
