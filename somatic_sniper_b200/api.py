@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libssn.so")
+LIB_PATH = os.environ.get("SSN_LIB_PATH") or os.path.join(HERE, "lib", "libssn.so")   # override: kernel experiments only
 COLUMN_DUMP_WORDS = 29
 SUBMIT_COLUMN_DUMP = 1
 

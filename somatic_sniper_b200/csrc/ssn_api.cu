@@ -122,7 +122,7 @@ extern "C" int ssn_nt16_of_char(int ch)
 static size_t smem_bytes_for(uint32_t words_per_warp)
 {
     /* dynamic part only; the model tables and key LUTs are static shared memory (CtaTables) */
-    return (size_t)kWarpsPerCta * (kAuxWords + words_per_warp) * 4;
+    return (size_t)kWarpsPerCta * (kSlotWords + words_per_warp) * 4 + 64;   /* + slack for the staged words read past a tile's end */
 }
 
 static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, uint64_t max_entries)

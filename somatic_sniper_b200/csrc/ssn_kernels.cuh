@@ -28,16 +28,16 @@
  * chain for every base exactly.  The class bits come from a shared-memory LUT indexed by
  * (sample, reference nt16, bs), sub from a 256-entry LUT: a handful of integer instructions per read-base.
  *
- * FAST TILES (every column of the tile holds <= 2*NW read-bases per the checks in tile_fits, NW in
- * {16,32,64}; all of WGS 30x/60x): FRONT writes the keys transposed into a per-warp
- * [NW words][32 columns] shared-memory array (XOR-swizzled: conflict-free for the column-wise writes
- * and the lane-wise reads); then each LANE loads its column's NW packed words into registers and
- * sorts them with a generated odd-even merge-sort network (ssn_sortnet.cuh: VIMNMX.U16x2 only, no
- * shuffles — 4x fewer issue slots per comparator than a warp-cooperative bitonic sort), stores them
- * back in walk order and runs the chain.  The tumor keys live in slots [0,nT), the normal keys in
- * slots from roundup2(nT).
- * DEEP TILES (panel depths) take the generic path: warp-cooperative bitonic sort of 1024-key runs in
- * registers (SHFL + VIMNMX) and a per-lane k-way merge during the walk.
+ * FAST TILES (every column of the tile holds <= ~128 read-bases, every staged base quality is in [1,63]; all of
+ * WGS 30x/60x): everything is lane-per-column.  Each lane reads its own column's staged bytes four read-bases at a
+ * time (aligned 32-bit shared loads + funnel shift), builds the keys two at a time with packed 16-bit arithmetic
+ * (PRMT / VIMNMX.U16x2 / one shared 16x16 LUT lookup per read-base for the class bits) straight into the NW
+ * registers the sorting network works on (padding behind the column's last read-base), sorts them with a generated odd-even merge-sort network
+ * (ssn_sortnet.cuh: VIMNMX.U16x2 only, no shuffles), stores them over the dead staging area in walk order and
+ * runs the chain.  With base qualities in [1,63] every read-base contributes, sub is 1 and the :165 promotion is
+ * q_eff = max(q, 4), which keeps the walk branch-free apart from the group change.
+ * OTHER TILES (panel depths, base quality 0 or >= 64 somewhere in the tile) take the generic path: warp-cooperative
+ * bitonic sort of 1024-key runs in registers (SHFL + VIMNMX) and a per-lane k-way merge during the walk.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -50,26 +50,42 @@
 #define SSN_ROUND_MAGIC 1 /* 1: (s+M)-M rounding in the FP64 pipe; 0: F2F.F32.F64 + F2F.F64.F32 */
 #endif
 
+#ifndef SSN_PHASE_LOCK
+#define SSN_PHASE_LOCK 0   /* 1: the warps of a CTA take 16 consecutive tiles and step through the phases together (i-cache locality) */
+#endif
+#if SSN_PHASE_LOCK
+#define SSN_PL_BAR() asm volatile("bar.sync 0;" ::: "memory")
+#else
+#define SSN_PL_BAR() do { } while (0)
+#endif
+
 namespace ssn {
 
-constexpr int kWarpsPerCta = 12;        /* one CTA per SM: 12 x (keys 8 KB + raw/slots 9.4 KB) + tables = 223 KB */
+#ifndef SSN_WARPS_PER_CTA
+#define SSN_WARPS_PER_CTA 16
+#endif
+constexpr int kWarpsPerCta = SSN_WARPS_PER_CTA;   /* one CTA per SM: 16 x (keys 8 KB + slots 3 KB; the raw staging aliases both) + tables */
 constexpr int kRunLen = 1024;          /* keys per sorted run of the generic path (R = 16 packed registers) */
 constexpr int kMaxRuns = 64;           /* => at most 65536 read-bases per column (tumor + normal) */
 constexpr int kSlotWords = 24 * 32;    /* per warp: 8 (sample,base) slots x {esum,fsum,count} x 32 lanes */
 constexpr int kFastWords = 64;         /* largest NW of the fast path: 128 key slots per column */
 constexpr int kRawBytes = 3200;        /* per array: staged read-bases of one fast tile (16-byte aligned window) */
-constexpr int kAuxWords = 3 * kRawBytes / 4;   /* raw staging; the chain slots alias its head once FRONT is done */
-static_assert(kAuxWords >= kSlotWords, "slots must fit in the raw staging area");
+constexpr int kAuxWords = 3 * kRawBytes / 4;   /* raw staging of a fast tile: aliases the key store and the head of the slots */
+static_assert(kAuxWords <= kFastWords * 32 + kSlotWords, "the raw staging must fit in key store + slots");
+constexpr uint32_t kPadPair = 0xffff0000u;     /* an empty register of the sorting network: key 0 | ~key 0 << 16 */
 constexpr unsigned kFull = 0xffffffffu;
 
 /* static shared memory of a CTA: model tables + key LUTs */
-struct CtaTables {
+struct __align__(1024) CtaTables {
+    uint32_t lut3[16 * 16];      /* [ref nt16][read nt16] -> b4<<13 | valid<<4 | sub 1; 1 KB aligned: address = row | nt*4 */
     double2 fk2[256];            /* {fk[w], fk[w]/32}: the walk multiplies by q*32 taken straight from the key */
     unsigned long long mbar[kWarpsPerCta];   /* one mbarrier per warp for its bulk copies */
     int32_t qadd[1024 + 64];
     int32_t prior[160];
     uint16_t cls[2 * 16 * 32];   /* [sample][ref nt16][bs & 31] -> sample<<15 | b4<<13 | valid<<4 | strand<<3 */
     uint8_t sub[256];            /* [baseQ] -> sub */
+    uint2 tail[5];               /* [live read-bases in a 4-chunk, clamped to 0..4] -> keep-masks of its two registers */
+    uint32_t tile_base;
 };
 
 struct DevModel {
@@ -106,6 +122,18 @@ __device__ __forceinline__ void build_key_luts(CtaTables &T, int tid, int nthrea
     }
     for (int i = tid; i < 256; i += nthreads)
         T.sub[i] = (uint8_t)(1 + (i < 64 ? 0 : 2 * (i >> 6) - ((i & 63) == 0 ? 1 : 0)));
+    for (int i = tid; i < 256; i += nthreads) {
+        const uint32_t ref16 = (uint32_t)i >> 4;
+        uint32_t nt = (uint32_t)i & 15u;
+        nt = nt ? nt : ref16;
+        const uint32_t valid = (nt != 0u && (nt & (nt - 1u)) == 0u) ? 1u : 0u;
+        const uint32_t b4 = valid ? ((nt >> 1) - (nt >> 3)) : 0u;
+        T.lut3[i] = b4 << 13 | valid << 4 | 1u;
+    }
+    if (tid < 5) {
+        const uint32_t k[5][2] = {{0u, 0u}, {0xffffu, 0u}, {0xffffffffu, 0u}, {0xffffffffu, 0xffffu}, {0xffffffffu, 0xffffffffu}};
+        T.tail[tid] = make_uint2(k[tid][0], k[tid][1]);
+    }
 }
 
 /* cls_col = T.cls + (sample*16 + ref16)*32 */
@@ -310,54 +338,83 @@ __device__ __forceinline__ void stage_wait(uint32_t mbar_s, uint32_t parity)
                  "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" :: "r"(mbar_s), "r"(parity) : "memory");
 }
 
-/* FRONT of a fast tile: keys of all 32 columns -> keys[w*32 + (col ^ (w & 31))] (packed, hi half complemented).
- * raw = staged bytes; column j's read-bases start at raw offset shfl(r0, j), tumor first. */
-template <int NW>
-__device__ __forceinline__ void fast_front(const CtaTables &T, const unsigned char *__restrict__ raw, uint32_t *__restrict__ keys,
-                                           int lane, uint32_t r0, uint32_t nT, uint32_t n, uint32_t ref16, int cap_mapq,
-                                           uint32_t &my_rms_t, uint32_t &my_rms_n)
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t a) { uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
+__device__ __forceinline__ uint4 lds_u32x4(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+__device__ __forceinline__ double2 lds_f64x2(uint32_t a) { double2 v; asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a)); return v; }
+
+/* Is every staged base quality of the tile in [1,63]?  (Then every read-base contributes, sub == 1 and the :165
+ * promotion is max(q,4).)  Warp-cooperative scan of the staged bq bytes; slack bytes of neighbouring tiles only make
+ * the answer conservative. */
+__device__ __forceinline__ bool tile_is_clean(uint32_t raw_s, uint32_t bytes, int lane)
 {
-#pragma unroll
-    for (int w = 0; w < NW; ++w) keys[w * 32 + lane] = 0xffff0000u;   /* padding: key 0 in both halves */
-    __syncwarp();
-    const uint32_t xmask = (lane & 1) ? 0xffffu : 0u;
-    unsigned char *kb = reinterpret_cast<unsigned char*>(keys) + (lane & 1) * 2;
-    const uint32_t cap = (uint32_t)cap_mapq;
-#pragma unroll 1
-    for (int j = 0; j < 32; ++j) {
-        const uint32_t nj = __shfl_sync(kFull, n, j);
-        if (nj == 0u) continue;
-        const uint32_t nTj = __shfl_sync(kFull, nT, j), refj = __shfl_sync(kFull, ref16, j);
-        const unsigned char *src = raw + __shfl_sync(kFull, r0, j);
-        const uint16_t *cls_t = T.cls + (16 + refj) * 32, *cls_n = T.cls + refj * 32;
-        uint32_t rt = 0, rn = 0;
-#pragma unroll 1
-        for (uint32_t i = lane; i < nj; i += 32) {
-            const uint32_t bs = src[i], bq = src[kRawBytes + i], mq = src[2 * kRawBytes + i];
-            const bool is_t = i < nTj;
-            const uint32_t key = make_key(is_t ? cls_t : cls_n, T.sub, bs, bq, mq);
-            const uint32_t m = min(mq & 0x7fu, cap);                          /* sniper_maqcns.c:173-174 */
-            if (is_t) rt += m * m; else rn += m * m;
-            const uint32_t w = i >> 1;
-            *reinterpret_cast<uint16_t*>(kb + w * 128 + (((uint32_t)j ^ w) & 31u) * 4) = (uint16_t)(key ^ xmask);
-        }
-        rt = __reduce_add_sync(kFull, rt);
-        rn = __reduce_add_sync(kFull, rn);
-        if (lane == j) { my_rms_t = rt; my_rms_n = rn; }
+    uint32_t bad = 0;
+    for (uint32_t i = (uint32_t)lane * 16u; i < bytes; i += 512u) {
+        const uint4 w = lds_u32x4(raw_s + (uint32_t)kRawBytes + i);
+        bad |= (w.x & 0xc0c0c0c0u) | ((w.x - 0x01010101u) & ~w.x & 0x80808080u);
+        bad |= (w.y & 0xc0c0c0c0u) | ((w.y - 0x01010101u) & ~w.y & 0x80808080u);
+        bad |= (w.z & 0xc0c0c0c0u) | ((w.z - 0x01010101u) & ~w.z & 0x80808080u);
+        bad |= (w.w & 0xc0c0c0c0u) | ((w.w - 0x01010101u) & ~w.w & 0x80808080u);
     }
-    __syncwarp();
+    return !__any_sync(kFull, bad != 0u);
 }
 
-/* BACK of a fast tile, first half: sort this lane's column and lay the keys out for the walk */
-template <int NW>
-__device__ __forceinline__ void fast_sort(uint32_t *keys, int lane)
+/* Keys of two consecutive read-bases (bytes SEL of the chunk words) -> one register of the sorting network:
+ * lo = key of the first, hi = complemented key of the second; registers past the column's end become padding.
+ * keep / tum = 0xffff per half that is a live read-base / a tumor read-base. */
+template <int HALF>
+__device__ __forceinline__ uint32_t t3_pair(uint32_t BS, uint32_t ST, uint32_t BQ, uint32_t MQ, uint32_t keep, uint32_t tum, uint32_t lutK,
+                                            uint32_t cap2, uint32_t &rms_all, uint32_t &rms_t)
 {
-    uint32_t v[NW];
+    constexpr uint32_t sel = HALF ? 0x4342u : 0x4140u;
+    const uint32_t bq = __byte_perm(BQ, 0u, sel), mq = __byte_perm(MQ, 0u, sel);
+    const uint32_t q = __vminu2(bq, mq);                                                   /* sniper_maqcns.c:151 */
+    const uint32_t x0 = HALF ? (BS >> 14) : (BS << 2), x1 = HALF ? (BS >> 22) : (BS >> 6);
+    const uint32_t l0 = lds_u32((x0 & 0x3cu) | lutK), l1 = lds_u32((x1 & 0x3cu) | lutK);
+    const uint32_t t = __byte_perm(l0, l1, 0x5410u) + (q << 5) + __byte_perm(ST, 0u, sel) + (tum & 0x80008000u);
+    const uint32_t mm = __vminu2(mq & 0x007f007fu & keep, cap2);                           /* :173-174 */
+    const uint32_t mb = __byte_perm(mm, 0u, 0x4420u);
+    rms_all = __dp2a_lo(mm, mb, rms_all);
+    rms_t = __dp2a_lo(mm & tum, mb, rms_t);
+    return ((t ^ kPadPair) & keep) | (kPadPair & ~keep);
+}
+
+/* FRONT of a fast tile, lane-per-column: the column's read-bases (tumor first, normal right behind them in the
+ * staged bytes) become the keys of registers [0, ceil(n/2)), the rest is padding.  C = tile-uniform chunk count
+ * (4 read-bases = 2 registers per chunk).  raw_s = shared address of the staged tile. */
+template <int NW>
+__device__ __forceinline__ void t3_build(uint32_t (&v)[NW], uint32_t raw_s, uint32_t r0, uint32_t nT, uint32_t n, int C,
+                                         uint32_t lutK, uint32_t tail_s, int cap_mapq, uint32_t &rms_t, uint32_t &rms_n)
+{
+    const uint32_t cap2 = (uint32_t)cap_mapq * 0x00010001u;
+    const uint32_t a = raw_s + (r0 & ~3u), sh = (r0 & 3u) * 8u;
+    uint32_t ws = lds_u32(a), wq = lds_u32(a + kRawBytes), wm = lds_u32(a + 2 * kRawBytes);
+    uint32_t rall = 0, rt = 0;
 #pragma unroll
-    for (int w = 0; w < NW; ++w) v[w] = keys[w * 32 + ((lane ^ w) & 31)];
-    __syncwarp();                                   /* all lanes have read before anyone overwrites */
+    for (int c = 0; c < NW / 2; ++c) {
+        if (c < C) {
+            const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
+            const uint32_t BS = __funnelshift_r(ws, ns, sh), BQ = __funnelshift_r(wq, nq, sh), MQ = __funnelshift_r(wm, nm, sh);
+            const uint2 keep = lds_u32x2(tail_s + 8u * (uint32_t)min(max((int)n - 4 * c, 0), 4));
+            const uint2 tum = lds_u32x2(tail_s + 8u * (uint32_t)min(max((int)nT - 4 * c, 0), 4));
+            const uint32_t ST = (BS & 0x10101010u) >> 1;                                  /* strand -> key bit 3 */
+            v[2 * c] = t3_pair<0>(BS, ST, BQ, MQ, keep.x, tum.x, lutK, cap2, rall, rt);
+            v[2 * c + 1] = t3_pair<1>(BS, ST, BQ, MQ, keep.y, tum.y, lutK, cap2, rall, rt);
+            ws = ns; wq = nq; wm = nm;
+        } else {
+            v[2 * c] = kPadPair; v[2 * c + 1] = kPadPair;
+        }
+    }
+    rms_t = rt; rms_n = rall - rt;
+}
+
+/* sort this lane's column and lay the keys out for the walk (over the dead staging area) */
+template <int NW>
+__device__ __forceinline__ void t3_sort_store(uint32_t (&v)[NW], uint32_t *keys, int lane)
+{
     SortNet<NW>::lists(v);
     SortNet<NW>::merge(v);
+    __syncwarp();                                   /* every lane is done reading the staged bytes */
     /* ascending sequence lo[0..NW) ++ hi[0..NW), two keys per word, word k of lane l at keys[k*32 + l] */
 #pragma unroll
     for (int k = 0; k < NW / 2; ++k) {
@@ -366,60 +423,59 @@ __device__ __forceinline__ void fast_sort(uint32_t *keys, int lane)
     }
 }
 
-/* The walk of a fast tile.  Group changes (and the end: key 0) are detected by one compare against the
- * current group's floor; q*32 is taken from the key unshifted and multiplied by fk/32 (exact scaling). */
+/* The walk of a fast tile (every key contributes, sub == 1).  Group changes (and the end: key 0) are detected by
+ * one compare against the current group's floor; q*32 is taken from the key unshifted and multiplied by fk/32 (exact
+ * scaling); the two strands' dependency ranks share one register (rank < 256: a fast column has <= 128 keys). */
 struct Walk {
     double e, f;
-    uint32_t w0, w1, c, floor;
-    int sb;
+    uint32_t ww, floor;
+    int sb, start;
 };
 
-__device__ __forceinline__ void walk_flush(const Walk &ch, uint32_t *slots, int lane)
+__device__ __forceinline__ void walk_flush(const Walk &ch, int pos, uint32_t *slots, int lane)
 {
     if (ch.sb >= 0) {
         uint32_t *s = slots + ch.sb * 96 + lane;
         s[0] = __float_as_uint(__double2float_rn(ch.e));
         s[32] = __float_as_uint(__double2float_rn(ch.f));
-        s[64] = ch.c;
+        s[64] = (uint32_t)(ch.start - pos);
     }
 }
 
-/* returns false when the column's keys are exhausted */
-__device__ __forceinline__ bool walk_step(Walk &ch, uint32_t key, const double2 *fk2, uint32_t *slots, int lane)
+/* pos = position of the key in the descending walk (counts down); returns false when the column's keys are exhausted */
+__device__ __forceinline__ bool walk_step(Walk &ch, uint32_t key, int pos, uint32_t fk2_s, uint32_t *slots, int lane)
 {
     if (key < ch.floor) {
-        walk_flush(ch, slots, lane);
+        walk_flush(ch, pos, slots, lane);
         ch.sb = -1;
         if (key == 0u) return false;
         ch.sb = (int)(key >> 13); ch.floor = max(key & 0xe000u, 1u);   /* group 0's real keys are >= 1 */
-        ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0;
+        ch.e = 0.0; ch.f = 0.0; ch.ww = 0; ch.start = pos;
     }
-    uint32_t q32 = key & 0x1fe0u;
-    if (q32 < 128u) q32 = (q32 != 0u && !(key & 1u)) ? q32 : 128u;   /* sniper_maqcns.c:165; sub even <=> baseQ in {64,128,192} */
-    const bool rev = (key & 8u) != 0u;
-    const uint32_t w = rev ? ch.w1 : ch.w0;
-    const double2 fk = fk2[w];
+    const uint32_t q32 = max(key & 0x1fe0u, 128u);                     /* sniper_maqcns.c:165 with baseQ in [1,63]: q_eff = max(q,4) */
+    const uint32_t sh = key & 8u;                                      /* strand bit doubles as the rank's shift */
+    const uint32_t w = (ch.ww >> sh) & 0xffu;
+    ch.ww += 1u << sh;                                                 /* :170 (no saturation needed below 256) */
+    const double2 fk = lds_f64x2(fk2_s + w * 16u);
     const double qd = __hiloint2double(0x43300000, (int)q32) - 4503599627370496.0;   /* exact int -> double */
-    ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fk.y, qd)));     /* esum += fk[w]*q  (:168) */
-    ch.f = round_to_f32f(__dadd_rn(ch.f, fk.x));                   /* fsum += fk[w]    (:169) */
-    const uint32_t wn = min(w + 1u, 255u);                         /* :170 */
-    if (rev) ch.w1 = wn; else ch.w0 = wn;
-    ++ch.c;
+    ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fk.y, qd)));        /* esum += fk[w]*q  (:168) */
+    ch.f = round_to_f32f(__dadd_rn(ch.f, fk.x));                      /* fsum += fk[w]    (:169) */
     return true;
 }
 
 template <int NW>
-__device__ __forceinline__ void fast_walk(const uint32_t *keys, const double2 *fk2, uint32_t *slots, int lane)
+__device__ __forceinline__ void fast_walk(const uint32_t *keys, uint32_t fk2_s, uint32_t *slots, int lane)
 {
     Walk ch;
-    ch.e = 0.0; ch.f = 0.0; ch.w0 = 0; ch.w1 = 0; ch.c = 0; ch.floor = 0x10000u; ch.sb = -1;
+    ch.e = 0.0; ch.f = 0.0; ch.ww = 0; ch.floor = 0x10000u; ch.sb = -1; ch.start = 0;
+    int pos = 2 * NW - 1;
 #pragma unroll 1
-    for (int k = NW - 1; k >= 0; --k) {
+    for (int k = NW - 1; k >= 0; --k, pos -= 2) {
         const uint32_t wd = keys[k * 32 + lane];
-        if (!walk_step(ch, wd >> 16, fk2, slots, lane)) break;
-        if (!walk_step(ch, wd & 0xffffu, fk2, slots, lane)) break;
+        if (!walk_step(ch, wd >> 16, pos, fk2_s, slots, lane)) break;
+        if (!walk_step(ch, wd & 0xffffu, pos - 1, fk2_s, slots, lane)) break;
     }
-    walk_flush(ch, slots, lane);
+    walk_flush(ch, -1, slots, lane);
 }
 
 /* -------------------------------------------------------------------------------------------- */
@@ -746,6 +802,21 @@ __device__ __noinline__ void generic_tile(const DevModel &M, const DevBatch &B, 
     chain_flush(ch, slots, lane);
 }
 
+template <int NW>
+__device__ __noinline__ void fast_tile(uint32_t raw_s, uint32_t r0, uint32_t nT, uint32_t n, int C, uint32_t lutK, uint32_t tail_s,
+                                       int cap_mapq, uint32_t *keys_s, uint32_t *slots, uint32_t fk2_s, int lane,
+                                       uint32_t &my_rms_t, uint32_t &my_rms_n)
+{
+    uint32_t v[NW];
+    t3_build<NW>(v, raw_s, r0, nT, n, C, lutK, tail_s, cap_mapq, my_rms_t, my_rms_n);
+    SSN_PL_BAR();
+    t3_sort_store<NW>(v, keys_s, lane);
+    for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;      /* the staging area is dead: its tail becomes the slots */
+    __syncwarp();
+    SSN_PL_BAR();
+    fast_walk<NW>(keys_s, fk2_s, slots, lane);
+}
+
 template <bool DUMP>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 1)
 ssn_score_kernel(const DevModel M, const DevBatch B)
@@ -766,11 +837,12 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    /* per warp: [keys: smem_words_per_warp] [aux: kAuxWords = raw staging of a fast tile, then the chain slots] */
-    uint32_t *keys_s = reinterpret_cast<uint32_t*>(smem_raw) + (size_t)warp * (kAuxWords + B.smem_words_per_warp);
+    /* per warp: [key store: smem_words_per_warp words][chain slots: kSlotWords]; the raw staging of a fast tile
+     * (kAuxWords) aliases the region from its start and is dead before keys and slots are written */
+    uint32_t *keys_s = reinterpret_cast<uint32_t*>(smem_raw) + (size_t)warp * (kSlotWords + B.smem_words_per_warp);
     uint32_t *slots = keys_s + B.smem_words_per_warp;
-    const unsigned char *raw = reinterpret_cast<const unsigned char*>(slots);
-    const uint32_t raw_s = smem_u32(slots);
+    const uint32_t raw_s = smem_u32(keys_s);
+    const uint32_t fk2_s = smem_u32(T.fk2), lut_s = smem_u32(T.lut3), tail_s = smem_u32(T.tail);
     const uint32_t gwarp = blockIdx.x * kWarpsPerCta + warp;
     uint32_t *keys_g = B.scratch ? B.scratch + (size_t)gwarp * B.scratch_words_per_warp : nullptr;
     const uint32_t ntiles = (B.ncol + 31u) >> 5;
@@ -778,9 +850,17 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
 
     for (;;) {
         uint32_t tile = 0;
+#if SSN_PHASE_LOCK
+        __syncthreads();
+        if (threadIdx.x == 0) T.tile_base = atomicAdd(B.site_count + 1, (uint32_t)kWarpsPerCta);
+        __syncthreads();
+        if (T.tile_base >= ntiles) break;
+        tile = T.tile_base + (uint32_t)warp;
+#else
         if (lane == 0) tile = atomicAdd(B.site_count + 1, 1u);
         tile = __shfl_sync(kFull, tile, 0);
         if (tile >= ntiles) break;
+#endif
         const uint32_t col = tile * 32u + lane;
         const bool live = col < B.ncol;
         uint32_t o0 = 0, o1 = 0, o2 = 0, ref16 = 15;
@@ -796,25 +876,31 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         const bool fast = need <= 2u * kFastWords && bytes <= (uint32_t)kRawBytes && B.smem_words_per_warp >= kFastWords * 32u;
 
         uint32_t my_rms_t = 0, my_rms_n = 0;
+        bool done = false;
         __syncwarp();                                   /* the previous tile is done with slots / keys */
         if (need != 0u && fast) {
             if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
+            const int C = (int)((need + 3u) >> 2);       /* tile-uniform chunk count (4 read-bases = 2 registers per chunk) */
             stage_wait(mbar_s, phase);
             phase ^= 1u;
-            const uint32_t r0 = o0 - a0;
-            if (need <= 32u) fast_front<16>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
-            else if (need <= 64u) fast_front<32>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
-            else fast_front<64>(T, raw, keys_s, lane, r0, nT, n, ref16, M.cap_mapq, my_rms_t, my_rms_n);
-            for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;      /* raw staging is dead: it becomes the slots */
+            if (tile_is_clean(raw_s, bytes, lane)) {
+                const uint32_t r0 = live ? o0 - a0 : 0u;
+                const uint32_t lutK = lut_s + ref16 * 64u;
+                if (C <= 8) fast_tile<16>(raw_s, r0, nT, n, C, lutK, tail_s, M.cap_mapq, keys_s, slots, fk2_s, lane, my_rms_t, my_rms_n);
+                else if (C <= 16) fast_tile<32>(raw_s, r0, nT, n, C, lutK, tail_s, M.cap_mapq, keys_s, slots, fk2_s, lane, my_rms_t, my_rms_n);
+                else fast_tile<64>(raw_s, r0, nT, n, C, lutK, tail_s, M.cap_mapq, keys_s, slots, fk2_s, lane, my_rms_t, my_rms_n);
+                done = true;
+            }
+        }
+        if (!done) {
             __syncwarp();
-            if (need <= 32u) { fast_sort<16>(keys_s, lane); fast_walk<16>(keys_s, T.fk2, slots, lane); }
-            else if (need <= 64u) { fast_sort<32>(keys_s, lane); fast_walk<32>(keys_s, T.fk2, slots, lane); }
-            else { fast_sort<64>(keys_s, lane); fast_walk<64>(keys_s, T.fk2, slots, lane); }
-        } else {
             for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
             __syncwarp();
+            SSN_PL_BAR();
             if (need != 0u) generic_tile(M, B, T, slots, keys_s, keys_g, lane, o0, nT, n, ref16, my_rms_t, my_rms_n);
+            SSN_PL_BAR();
         }
+        SSN_PL_BAR();
         __syncwarp();
 
         Glf gt, gn;
@@ -822,6 +908,7 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         gn = gt;
         if (nT) sample_glf(M, slots, lane, 1, nT, my_rms_t, gt);
         if (nN) sample_glf(M, slots, lane, 0, nN, my_rms_n, gn);
+        SSN_PL_BAR();
         Call call;
         call.score = -1; call.pass = false; call.candidate = false;
         if (nT && nN && ref16 != 15u) score_column(M, T.qadd, T.prior, (int)ref16, gt, gn, call);
