@@ -494,7 +494,15 @@ __device__ __forceinline__ int bar_error(float t1, float t3)
     return min(max(bar, 4), 63);
 }
 
-__device__ void sample_glf(const DevModel &M, const uint32_t *slots, int lane, int sample, uint32_t n,
+#ifndef SSN_GLF_NOINLINE
+#define SSN_GLF_NOINLINE 0
+#endif
+#if SSN_GLF_NOINLINE
+__device__ __noinline__
+#else
+__device__
+#endif
+void sample_glf(const DevModel &M, const uint32_t *slots, int lane, int sample, uint32_t n,
                            uint32_t rms_sum, Glf &g)
 {
     float es[4], fs[4];
