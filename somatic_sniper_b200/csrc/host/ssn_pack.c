@@ -23,6 +23,7 @@
 #include "ssn_pool.h"
 
 #define GROUP_MAX 16           /* windows pulled per batch at most */
+#define SEG_MAX 1024           /* fill tasks per batch at most */
 
 static __thread char h_err[512] = "";
 const char *ssn_host_last_error(void) { return h_err; }
@@ -71,7 +72,7 @@ struct ssn_packer {
     /* the batch being filled */
     const ssn_batch_view *view;
     const ssn_colmap *map;
-    segment seg[GROUP_MAX + 1];
+    segment seg[SEG_MAX];
 };
 
 /* ---- CIGAR walk -------------------------------------------------------------------------------------------- */
@@ -353,30 +354,41 @@ ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn
     if (pk->n_pending > fresh0) ssn_pool_for(pk->pool, pk->n_pending - fresh0, count_task, pk->pending + fresh0);
     t0 = now_s(); pk->st.t_count += t0 - t1;
 
-    /* 3. cut the batch: whole windows while they fit, then the longest prefix of the next one */
-    for (i = 0; i < pk->n_pending && !full; ++i) {
-        pair *p = pk->pending[i];
-        segment *sg = &pk->seg[nseg];
-        uint32_t j, c = 0;
-        uint64_t e = 0;
-        for (j = p->next_i; j < SSN_WINDOW; ++j) {
-            const uint32_t ct = p->cnt[0][j];
-            if (ct == 0) continue;
-            {
-                const uint64_t add = (uint64_t)ct + p->cnt[1][j];
-                if (ncol + c + 1 > view->max_columns || nent + e + add > view->max_entries) { full = 1; break; }
-                c += 1; e += add;
+    /* 3. cut the batch: whole windows while they fit, then the longest prefix of the next one.  Windows are split
+     * into position sub-ranges of about `span` so that a batch of few (deep) windows still fills in parallel. */
+    {
+        const int workers = ssn_pool_threads(pk->pool) + 1;
+        uint32_t span = (uint32_t)((uint64_t)SSN_WINDOW * (uint32_t)pk->n_pending / (uint32_t)(2 * workers));
+        if (span < 128u) span = 128u;
+        if (span > SSN_WINDOW) span = SSN_WINDOW;
+        for (i = 0; i < pk->n_pending && !full; ++i) {
+            pair *p = pk->pending[i];
+            uint32_t j, c = 0, seg_i0 = p->next_i, seg_c = 0;
+            uint64_t e = 0, seg_e = 0;
+            for (j = p->next_i; j < SSN_WINDOW; ++j) {
+                const uint32_t ct = p->cnt[0][j];
+                if (j - seg_i0 >= span && nseg < SEG_MAX - 2) {           /* close a sub-range */
+                    segment *sg = &pk->seg[nseg++];
+                    sg->p = p; sg->i0 = seg_i0; sg->i1 = j; sg->col_base = ncol + seg_c; sg->ent_base = nent + seg_e;
+                    seg_i0 = j; seg_c = c; seg_e = e;
+                }
+                if (ct == 0) continue;
+                {
+                    const uint64_t add = (uint64_t)ct + p->cnt[1][j];
+                    if (ncol + c + 1 > view->max_columns || nent + e + add > view->max_entries) { full = 1; break; }
+                    c += 1; e += add;
+                }
             }
-        }
-        if (full && c == 0 && ncol == 0) {
-            set_err("column %d:%u holds %llu read bases; the batch capacity is %llu", p->w[0]->tid,
-                    (p->w[0]->widx << SSN_WINDOW_SHIFT) + j, (unsigned long long)((uint64_t)p->cnt[0][j] + p->cnt[1][j]),
-                    (unsigned long long)view->max_entries);
-            return SSN_ERR_OVERFLOW;
-        }
-        if (j > p->next_i) {
-            sg->p = p; sg->i0 = p->next_i; sg->i1 = j; sg->col_base = ncol; sg->ent_base = nent;
-            ++nseg;
+            if (full && c == 0 && ncol == 0) {
+                set_err("column %d:%u holds %llu read bases; the batch capacity is %llu", p->w[0]->tid,
+                        (p->w[0]->widx << SSN_WINDOW_SHIFT) + j, (unsigned long long)((uint64_t)p->cnt[0][j] + p->cnt[1][j]),
+                        (unsigned long long)view->max_entries);
+                return SSN_ERR_OVERFLOW;
+            }
+            if (j > seg_i0) {
+                segment *sg = &pk->seg[nseg++];
+                sg->p = p; sg->i0 = seg_i0; sg->i1 = j; sg->col_base = ncol + seg_c; sg->ent_base = nent + seg_e;
+            }
             ncol += c; nent += e;
             p->next_i = j;
         }

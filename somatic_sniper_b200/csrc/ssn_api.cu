@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <vector>
 
 #include "ssn_internal.h"
@@ -162,9 +163,19 @@ static void slot_free(ssn_batch *b)
     delete b;
 }
 
+static double wall_now()
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
 extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slots, uint32_t max_columns,
                                  uint64_t max_entries, ssn_ctx **out)
 {
+    const bool trace = getenv("SSN_TRACE_SETUP") != nullptr;
+    double tt = wall_now();
+#define SSN_TRACE(what) do { if (trace) { double n_ = wall_now(); fprintf(stderr, "[ssn_create] %-28s %.3f s\n", what, n_ - tt); tt = n_; } } while (0)
     if (!p || !out || n_slots == 0 || max_columns == 0) { ssn_set_error("ssn_create: bad argument"); return SSN_ERR_ARG; }
     if (max_entries >= (1ull << 32) - 64) { ssn_set_error("ssn_create: max_entries must stay below 2^32"); return SSN_ERR_ARG; }
     int ndev = 0;
@@ -173,6 +184,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     CU(cudaSetDevice(device));
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
+    SSN_TRACE("device query (context)");
     if (prop.major < 10) { ssn_set_error("ssn_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return SSN_ERR_CUDA; }
 
     ssn_ctx *ctx = new ssn_ctx();
@@ -185,6 +197,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
     if (ssn_tables_build(p, &ctx->tab) != 0) { ssn_set_error("ssn_create: table construction failed (n_hap=%d)", p->n_hap); delete ctx; return SSN_ERR_ARG; }
 
+    SSN_TRACE("host tables");
     const size_t coef_n = (size_t)64 * 65536, lhet_n = 65536;
     CU(cudaMalloc(&ctx->d_coef_lhet, sizeof(double) * (coef_n + lhet_n)));
     CU(cudaMemcpy(ctx->d_coef_lhet, ctx->tab.coef, sizeof(double) * coef_n, cudaMemcpyHostToDevice));
@@ -204,6 +217,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     M.cap_mapq = p->cap_mapq; M.min_somatic_qual = p->min_somatic_qual;
     M.include_loh = p->include_loh; M.include_gor = p->include_gor; M.use_joint = p->use_joint_priors;
 
+    SSN_TRACE("table upload");
     CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&ctx->t0));
     CU(cudaEventCreate(&ctx->t1));
@@ -221,6 +235,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
         CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist));
         ctx->l2_window_bytes = std::min<size_t>(want, (size_t)prop.accessPolicyMaxWindowSize);
     }
+    SSN_TRACE("kernel attributes, L2 limit");
     for (uint32_t i = 0; i < n_slots; ++i) {
         ssn_batch *b = new ssn_batch();
         memset((void*)b, 0, sizeof(*b));
@@ -239,6 +254,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
             CU(cudaStreamSetAttribute(b->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
         }
     }
+    SSN_TRACE("batch slots (pinned + device)");
     ctx->timers.resize(64);
     for (auto &t : ctx->timers) {
         CU(cudaEventCreate(&t.a));
