@@ -100,10 +100,12 @@ typedef struct {
 } ssn_site;
 
 /* Optional per-column dump (SSN_SUBMIT_COLUMN_DUMP): both samples' quantised GLFs and the
- * value glf_somatic returns (somatic_sniper.c:268-272). 29 uint32 per column:
+ * value glf_somatic returns (somatic_sniper.c:268-272). 30 uint32 per column:
  *   [0..9] tumor lk, [10] min_lk, [11] rms mapQ, [12] depth, [13] consensus word,
- *   [14..27] the same for the normal sample, [28] (int32) return value. */
-#define SSN_COLUMN_DUMP_WORDS 29
+ *   [14..27] the same for the normal sample, [28] (int32) return value,
+ *   [29] 1 if the hom-reference pre-filter would have dropped the column before the full model (audit; the
+ *        dump itself always comes from the full model). */
+#define SSN_COLUMN_DUMP_WORDS 30
 
 /* Pinned host arrays of one batch, filled by the packer.  Column c owns entries
  * off[2c]..off[2c+1] (tumor) and off[2c+1]..off[2c+2] (normal) of bs/bq/mq.  Deleted bases and
@@ -122,6 +124,7 @@ typedef struct ssn_ctx ssn_ctx;
 typedef struct ssn_batch ssn_batch;
 
 #define SSN_SUBMIT_COLUMN_DUMP 1u  /* also produce the per-column dump (parity tests) */
+#define SSN_SUBMIT_NO_PREFILTER 2u /* run every column through the full model (measurement; results are identical) */
 
 int ssn_abi_version(void);
 const char *ssn_last_error(void);
@@ -167,6 +170,24 @@ ssn_status ssn_sync(ssn_ctx *ctx);
 uint64_t ssn_kernel_launches(const ssn_ctx *ctx);   /* kernels launched by this ctx so far */
 /* Sum of the scoring kernel's own durations (events on its launch stream) since the last reset. */
 ssn_status ssn_kernel_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_launches, int reset);
+/* The same split into the pre-filter kernel and the scoring kernel; n_batches = batches timed. */
+ssn_status ssn_kernel_time_split(ssn_ctx *ctx, float *prefilter_ms, float *score_ms, uint64_t *n_batches, int reset);
+/* 1 if this ctx runs the exact hom-reference pre-filter in front of the full model (default; the parameter set must
+ * satisfy the proof's preconditions, and SSN_NO_PREFILTER must be unset in the environment). */
+int ssn_prefilter_enabled(const ssn_ctx *ctx);
+/* Columns of a finished batch that the pre-filter handed to the full model (0 when it did not run). */
+ssn_status ssn_batch_survivors(const ssn_batch *b, uint32_t *n_columns);
+/* Host view of the pre-filter's bound tables (parity tests re-evaluate the filter on the CPU against the oracle):
+ * ab[(n*N + m)*4 + {0,1,2}] = {cmin_all, cmax_run, g2_run}, h[a*N + b], F[0..N]; see ssn_prefilter_tables.c. */
+typedef struct {
+    const float *ab;
+    const float *h;
+    const float *F;
+    int32_t n;        /* N = 256 */
+    int32_t enabled;
+} ssn_prefilter_view;
+ssn_status ssn_host_prefilter_create(const ssn_params *p, ssn_prefilter_view *view, void **handle);
+void ssn_host_prefilter_destroy(void *handle);
 /* Writes a buffer larger than L2 on the ctx's device (cold-cache timing). */
 ssn_status ssn_flush_l2(ssn_ctx *ctx);
 

@@ -14,8 +14,9 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SSN_LIB_PATH") or os.path.join(HERE, "lib", "libssn.so")   # override: kernel experiments only
-COLUMN_DUMP_WORDS = 29
+COLUMN_DUMP_WORDS = 30     # [29] = 1 if the hom-reference pre-filter would have dropped the column
 SUBMIT_COLUMN_DUMP = 1
+SUBMIT_NO_PREFILTER = 2    # every column through the full model (identical results; measurement only)
 
 
 class Params(C.Structure):
@@ -30,6 +31,12 @@ class Tables(C.Structure):
     _fields_ = [("coef", C.POINTER(C.c_double)), ("lhet", C.POINTER(C.c_double)), ("fk", C.POINTER(C.c_double)),
                 ("q_r", C.c_float), ("prior", C.POINTER(C.c_int32)), ("jointprior", C.POINTER(C.c_int32)),
                 ("qadd", C.POINTER(C.c_int32))]
+
+
+class PrefilterView(C.Structure):
+    """ssn_prefilter_view: the pre-filter's bound tables (ssn_prefilter_tables.c)."""
+    _fields_ = [("ab", C.POINTER(C.c_float)), ("h", C.POINTER(C.c_float)), ("F", C.POINTER(C.c_float)),
+                ("n", C.c_int32), ("enabled", C.c_int32)]
 
 
 class BatchView(C.Structure):
@@ -74,6 +81,11 @@ SIGNATURES = {
     "ssn_kernel_launches": (_U64, [_VP]),
     "ssn_kernel_time": (_I, [_VP, C.POINTER(C.c_float), C.POINTER(_U64), _I]),
     "ssn_flush_l2": (_I, [_VP]),
+    "ssn_kernel_time_split": (_I, [_VP, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(_U64), _I]),
+    "ssn_prefilter_enabled": (_I, [_VP]),
+    "ssn_batch_survivors": (_I, [_VP, C.POINTER(_U32)]),
+    "ssn_host_prefilter_create": (_I, [C.POINTER(Params), C.POINTER(PrefilterView), C.POINTER(_VP)]),
+    "ssn_host_prefilter_destroy": (None, [_VP]),
 }
 
 _lib = None
@@ -134,6 +146,22 @@ def host_tables(params=None):
         lib.ssn_host_tables_destroy(h)
 
 
+def host_prefilter_tables(params=None):
+    """The pre-filter's bound tables built by the product's host code (no device needed):
+    dict(ab float32[N,N,4], h float32[N,N], F float32[N+1], enabled bool)."""
+    lib = load_library()
+    p = params or default_params()
+    v, h = PrefilterView(), _VP()
+    _check(lib.ssn_host_prefilter_create(C.byref(p), C.byref(v), C.byref(h)))
+    try:
+        n = int(v.n)
+        arr = np.ctypeslib.as_array
+        return dict(ab=arr(v.ab, shape=(n, n, 4)).copy(), h=arr(v.h, shape=(n, n)).copy(),
+                    F=arr(v.F, shape=(n + 1,)).copy(), enabled=bool(v.enabled))
+    finally:
+        lib.ssn_host_prefilter_destroy(h)
+
+
 def nt16_of_chars(chars):
     lib = load_library()
     return np.array([lib.ssn_nt16_of_char(int(c)) for c in np.asarray(chars, np.uint8)], np.uint8)
@@ -181,6 +209,12 @@ class Batch:
     def set_size(self, ncol, n):
         _check(self.scorer.lib.ssn_batch_set_size(self.h, ncol, n))
         self.ncol, self.nent = ncol, n
+
+    def survivors(self):
+        """Columns the pre-filter handed to the full model (valid once the batch's results were drained)."""
+        n = _U32()
+        _check(self.scorer.lib.ssn_batch_survivors(self.h, C.byref(n)))
+        return int(n.value)
 
     def column_dump(self):
         p = _VP()
@@ -238,15 +272,19 @@ class Scorer:
     def release(self, batch):
         _check(self.lib.ssn_batch_release(self.ctx, batch.h))
 
-    def score(self, cols, dump=False):
+    def score(self, cols, dump=False, flags=0):
         """Convenience: one batch through acquire/fill/submit/results_next. Returns (sites, dump|None)."""
         b = self.acquire()
         b.fill(cols)
-        self.submit(b, SUBMIT_COLUMN_DUMP if dump else 0)
+        self.submit(b, flags | (SUBMIT_COLUMN_DUMP if dump else 0))
         sites, _ = self.results_next()
         d = b.column_dump() if dump else None
+        self.last_survivors = b.survivors()
         self.release(b)
         return sites, d
+
+    def prefilter_enabled(self):
+        return bool(self.lib.ssn_prefilter_enabled(self.ctx))
 
     # -- resident path ------------------------------------------------------------------------------
     def upload(self, batch):
@@ -279,6 +317,12 @@ class Scorer:
         ms, n = C.c_float(), _U64()
         _check(self.lib.ssn_kernel_time(self.ctx, C.byref(ms), C.byref(n), 1 if reset else 0))
         return ms.value, int(n.value)
+
+    def kernel_time_split(self, reset=False):
+        """(pre-filter ms, scoring ms, batches) summed over the batches timed since the last reset."""
+        a, b, n = C.c_float(), C.c_float(), _U64()
+        _check(self.lib.ssn_kernel_time_split(self.ctx, C.byref(a), C.byref(b), C.byref(n), 1 if reset else 0))
+        return a.value, b.value, int(n.value)
 
     def flush_l2(self):
         _check(self.lib.ssn_flush_l2(self.ctx))

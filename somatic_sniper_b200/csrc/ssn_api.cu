@@ -13,6 +13,7 @@
 
 #include "ssn_internal.h"
 #include "ssn_kernels.cuh"
+#include "ssn_prefilter.cuh"
 
 using namespace ssn;
 
@@ -54,7 +55,7 @@ struct ssn_batch {
     bool resident;            /* device copy matches the host arrays */
     /* pinned host */
     uint32_t *h_off; uint8_t *h_bs, *h_bq, *h_mq, *h_ref;
-    uint32_t *h_count;        /* 2 words */
+    uint32_t *h_count;        /* kCountWords: [0] sites, [1] score tiles, [2] pre-filter survivors, [3] pre-filter tiles */
     ssn_site *h_sites; uint32_t h_sites_cap;
     uint32_t *h_dump; size_t h_dump_words;
     /* device */
@@ -63,15 +64,19 @@ struct ssn_batch {
     ssn_site *d_sites; uint32_t site_cap;
     uint32_t *d_dump; size_t d_dump_words;
     uint32_t max_tile_words;
+    uint32_t max_col_words;   /* key-store words of the deepest column (list-mode tiles gather arbitrary columns) */
+    uint32_t *d_survivors;    /* column indices the pre-filter hands to the full model */
     cudaStream_t stream;
     cudaEvent_t done;
     uint32_t n_sites;
 };
 
 struct KernelTimer {
-    cudaEvent_t a, b;
-    bool pending;
+    cudaEvent_t a, m, b;      /* a -> m: pre-filter kernel (when it ran), m -> b: scoring kernel */
+    bool pending, filtered;
 };
+
+constexpr int kCountWords = 8;
 
 struct ssn_ctx {
     int device;
@@ -95,7 +100,13 @@ struct ssn_ctx {
     std::vector<KernelTimer> timers;
     size_t timer_next;
     double kernel_ms; uint64_t kernel_n;
+    double prefilter_ms, score_ms;
     size_t l2_window_bytes;
+    /* exact hom-reference pre-filter (ssn_prefilter.cuh) */
+    ssn_prefilter_tables pf;
+    float *d_pf_ab, *d_pf_h, *d_pf_F;
+    DevPrefilter dpf;
+    bool pf_on;
 };
 
 extern "C" ssn_status ssn_params_default(ssn_params *p)
@@ -120,6 +131,8 @@ extern "C" int ssn_nt16_of_char(int ch)
     return 15;
 }
 
+static size_t pf_smem_bytes() { return (size_t)kPfWarps * kPfStageBytes + 256; }   /* + slack for the words read past a tile's end */
+
 static size_t smem_bytes_for(uint32_t words_per_warp)
 {
     /* dynamic part only; the model tables and key LUTs are static shared memory (CtaTables) */
@@ -135,13 +148,14 @@ static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, u
     CU(cudaMallocHost(&b->h_bq, ent));
     CU(cudaMallocHost(&b->h_mq, ent));
     CU(cudaMallocHost(&b->h_ref, (size_t)max_columns + 64));
-    CU(cudaMallocHost(&b->h_count, 2 * sizeof(uint32_t)));
+    CU(cudaMallocHost(&b->h_count, kCountWords * sizeof(uint32_t)));
     CU(cudaMalloc(&b->d_off, sizeof(uint32_t) * (2 * (size_t)max_columns + 1)));
     CU(cudaMalloc(&b->d_bs, ent));
     CU(cudaMalloc(&b->d_bq, ent));
     CU(cudaMalloc(&b->d_mq, ent));
     CU(cudaMalloc(&b->d_ref, (size_t)max_columns + 64));
-    CU(cudaMalloc(&b->d_count, 2 * sizeof(uint32_t)));
+    CU(cudaMalloc(&b->d_count, kCountWords * sizeof(uint32_t)));
+    CU(cudaMalloc(&b->d_survivors, sizeof(uint32_t) * ((size_t)max_columns + 32)));
     b->site_cap = std::max<uint32_t>(4096u, max_columns / 16u);
     CU(cudaMalloc(&b->d_sites, sizeof(ssn_site) * (size_t)b->site_cap));
     b->h_sites_cap = 4096;
@@ -157,7 +171,7 @@ static void slot_free(ssn_batch *b)
     cudaFreeHost(b->h_off); cudaFreeHost(b->h_bs); cudaFreeHost(b->h_bq); cudaFreeHost(b->h_mq);
     cudaFreeHost(b->h_ref); cudaFreeHost(b->h_count); cudaFreeHost(b->h_sites); cudaFreeHost(b->h_dump);
     cudaFree(b->d_off); cudaFree(b->d_bs); cudaFree(b->d_bq); cudaFree(b->d_mq); cudaFree(b->d_ref);
-    cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump);
+    cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump); cudaFree(b->d_survivors);
     if (b->stream) cudaStreamDestroy(b->stream);
     if (b->done) cudaEventDestroy(b->done);
     delete b;
@@ -192,6 +206,8 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
     ctx->d_scratch = nullptr; ctx->scratch_words = 0; ctx->grid_cap = 0; ctx->d_flush = nullptr; ctx->flush_bytes = 0;
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
+    ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = nullptr; ctx->pf_on = false;
+    memset(&ctx->pf, 0, sizeof(ctx->pf));
     const char *env = getenv("SSN_SMEM_WORDS");
     ctx->smem_words_default = env ? (uint32_t)atoi(env) : (uint32_t)kFastWords * 32u;
     ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
@@ -217,6 +233,15 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     M.cap_mapq = p->cap_mapq; M.min_somatic_qual = p->min_somatic_qual;
     M.include_loh = p->include_loh; M.include_gor = p->include_gor; M.use_joint = p->use_joint_priors;
 
+    if (ssn_prefilter_build(&ctx->tab, M.q_r_int, &ctx->pf) != 0) { ssn_set_error("ssn_create: out of memory (pre-filter tables)"); ssn_destroy(ctx); return SSN_ERR_NOMEM; }
+    ctx->pf_on = ctx->pf.enabled && getenv("SSN_NO_PREFILTER") == nullptr;
+    CU(cudaMalloc(&ctx->d_pf_ab, sizeof(float) * 4 * SSN_PF_N * SSN_PF_N));
+    CU(cudaMemcpy(ctx->d_pf_ab, ctx->pf.ab, sizeof(float) * 4 * SSN_PF_N * SSN_PF_N, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_pf_h, sizeof(float) * SSN_PF_N * SSN_PF_N));
+    CU(cudaMemcpy(ctx->d_pf_h, ctx->pf.h, sizeof(float) * SSN_PF_N * SSN_PF_N, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&ctx->d_pf_F, sizeof(float) * (SSN_PF_N + 1)));
+    CU(cudaMemcpy(ctx->d_pf_F, ctx->pf.F, sizeof(float) * (SSN_PF_N + 1), cudaMemcpyHostToDevice));
+    ctx->dpf.ab = reinterpret_cast<const float4*>(ctx->d_pf_ab); ctx->dpf.h = ctx->d_pf_h; ctx->dpf.F = ctx->d_pf_F;
     SSN_TRACE("table upload");
     CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&ctx->t0));
@@ -227,6 +252,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     const int max_dyn = (int)(ctx->smem_optin - ctx->smem_static);
     CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
     CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+    CU(cudaFuncSetAttribute(ssn_prefilter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pf_smem_bytes()));
 
     /* keep coef+lhet resident in L2: persisting carve-out + per-stream access-policy window */
     size_t want = sizeof(double) * (coef_n + lhet_n);
@@ -258,8 +284,9 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->timers.resize(64);
     for (auto &t : ctx->timers) {
         CU(cudaEventCreate(&t.a));
+        CU(cudaEventCreate(&t.m));
         CU(cudaEventCreate(&t.b));
-        t.pending = false;
+        t.pending = false; t.filtered = false;
     }
     *out = ctx;
     return SSN_OK;
@@ -271,7 +298,9 @@ extern "C" void ssn_destroy(ssn_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     for (ssn_batch *b : ctx->slots) slot_free(b);
-    for (auto &t : ctx->timers) { if (t.a) cudaEventDestroy(t.a); if (t.b) cudaEventDestroy(t.b); }
+    for (auto &t : ctx->timers) { if (t.a) cudaEventDestroy(t.a); if (t.m) cudaEventDestroy(t.m); if (t.b) cudaEventDestroy(t.b); }
+    cudaFree(ctx->d_pf_ab); cudaFree(ctx->d_pf_h); cudaFree(ctx->d_pf_F);
+    ssn_prefilter_free(&ctx->pf);
     cudaFree(ctx->d_coef_lhet); cudaFree(ctx->d_fk); cudaFree(ctx->d_prior); cudaFree(ctx->d_jointprior);
     cudaFree(ctx->d_qadd); cudaFree(ctx->d_scratch); cudaFree(ctx->d_flush);
     if (ctx->main_stream) cudaStreamDestroy(ctx->main_stream);
@@ -358,6 +387,7 @@ static ssn_status scan_offsets(ssn_batch *b)
 {
     const uint32_t *off = b->h_off;
     const uint32_t ncol = b->ncol;
+    b->max_col_words = 0;
     if (ncol == 0) { b->max_tile_words = 0; return SSN_OK; }
     if (off[2 * (size_t)ncol] != b->nent) { ssn_set_error("batch: off[2*ncol]=%u but n_entries=%llu", off[2 * (size_t)ncol], (unsigned long long)b->nent); return SSN_ERR_ARG; }
     uint32_t max_tile = 0;
@@ -369,7 +399,9 @@ static ssn_status scan_offsets(ssn_batch *b)
             if (m < a || z < m) { ssn_set_error("batch: offsets of column %u decrease", c); return SSN_ERR_ARG; }
             const uint32_t n = z - a;
             if (n > (uint32_t)kRunLen * kMaxRuns) { ssn_set_error("batch: column %u holds %u read-bases; this build supports %d", c, n, kRunLen * kMaxRuns); return SSN_ERR_ARG; }
-            words += (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
+            const uint32_t cw = (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
+            words += cw;
+            b->max_col_words = std::max(b->max_col_words, cw);
         }
         max_tile = std::max(max_tile, words);
     }
@@ -383,17 +415,35 @@ static ssn_status copy_in(ssn_ctx *ctx, ssn_batch *b)
     if (b->ncol == 0) return SSN_OK;
     CU(cudaMemcpyAsync(b->d_off, b->h_off, sizeof(uint32_t) * (2 * (size_t)b->ncol + 1), cudaMemcpyHostToDevice, b->stream));
     CU(cudaMemcpyAsync(b->d_bs, b->h_bs, b->nent, cudaMemcpyHostToDevice, b->stream));
-    CU(cudaMemcpyAsync(b->d_bq, b->h_bq, b->nent, cudaMemcpyHostToDevice, b->stream));
+    /* the kernels' clean-tile check scans the last tile's base qualities up to the next 16-byte boundary: pad with a
+     * legal quality so stale bytes behind the batch cannot send that tile down the slow path (the slot has 64 spare bytes) */
+    memset(b->h_bq + b->nent, 1, 16);
+    CU(cudaMemcpyAsync(b->d_bq, b->h_bq, b->nent + 16, cudaMemcpyHostToDevice, b->stream));
     CU(cudaMemcpyAsync(b->d_mq, b->h_mq, b->nent, cudaMemcpyHostToDevice, b->stream));
     CU(cudaMemcpyAsync(b->d_ref, b->h_ref, b->ncol, cudaMemcpyHostToDevice, b->stream));
+    return SSN_OK;
+}
+
+static ssn_status timer_collect(ssn_ctx *ctx, KernelTimer &kt)
+{
+    if (!kt.pending) return SSN_OK;
+    float ms = 0, fm = 0;
+    CU(cudaEventSynchronize(kt.b));
+    CU(cudaEventElapsedTime(&ms, kt.a, kt.b));
+    if (kt.filtered) CU(cudaEventElapsedTime(&fm, kt.a, kt.m));
+    ctx->kernel_ms += ms; ctx->prefilter_ms += fm; ctx->score_ms += ms - fm; ctx->kernel_n += 1;
+    kt.pending = false;
     return SSN_OK;
 }
 
 static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
 {
     const bool dump = (flags & SSN_SUBMIT_COLUMN_DUMP) != 0;
+    /* the pre-filter runs unless switched off; with a column dump it only records its decisions (audit) */
+    const bool filter = ctx->pf_on && !(flags & SSN_SUBMIT_NO_PREFILTER);
+    const bool listed = filter && !dump;
     b->flags = flags;
-    CU(cudaMemsetAsync(b->d_count, 0, 2 * sizeof(uint32_t), b->stream));
+    CU(cudaMemsetAsync(b->d_count, 0, kCountWords * sizeof(uint32_t), b->stream));
     if (b->ncol == 0) return SSN_OK;
     if (dump) {
         const size_t need = (size_t)b->ncol * SSN_COLUMN_DUMP_WORDS;
@@ -405,6 +455,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
             CU(cudaMallocHost(&b->h_dump, need * 4));
             b->d_dump_words = b->h_dump_words = need;
         }
+        if (!filter) CU(cudaMemsetAsync(b->d_dump, 0, need * 4, b->stream));   /* word 29 = "not dropped" */
     }
     /* shared-memory key store per warp: kFastWords*32 words serve every fast tile (<= 128 key slots per
      * column); deeper tiles use it too when they fit and the global scratch otherwise */
@@ -418,9 +469,11 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     const uint32_t ntiles = (b->ncol + 31u) / 32u;
     uint32_t grid = (uint32_t)(ctx->num_sms * per_sm);
     const uint32_t need_ctas = (ntiles + kWarpsPerCta - 1) / kWarpsPerCta;
-    if (grid > need_ctas) grid = need_ctas;
-    if (b->max_tile_words > words) {
-        const size_t per_warp = ((size_t)b->max_tile_words + 63) / 64 * 64;
+    if (grid > need_ctas && !listed) grid = need_ctas;
+    /* a list-mode tile gathers up to 32 arbitrary columns: size the spill store for 32 of the deepest one */
+    const uint32_t tile_words = listed ? 32u * b->max_col_words : b->max_tile_words;
+    if (tile_words > words) {
+        const size_t per_warp = ((size_t)tile_words + 63) / 64 * 64;
         const size_t need = per_warp * grid * kWarpsPerCta;
         if (ctx->scratch_words < need) {
             CU(cudaDeviceSynchronize());
@@ -433,18 +486,26 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.off = b->d_off; B.bs = b->d_bs; B.bq = b->d_bq; B.mq = b->d_mq; B.ref_nt16 = b->d_ref; B.ncol = b->ncol;
     B.sites = b->d_sites; B.site_count = b->d_count; B.site_cap = b->site_cap;
     B.coldump = dump ? b->d_dump : nullptr;
-    B.scratch = b->max_tile_words > words ? ctx->d_scratch : nullptr;
-    B.scratch_words_per_warp = (uint32_t)(((size_t)b->max_tile_words + 63) / 64 * 64);
+    B.scratch = tile_words > words ? ctx->d_scratch : nullptr;
+    B.scratch_words_per_warp = (uint32_t)(((size_t)tile_words + 63) / 64 * 64);
     B.smem_words_per_warp = words;
+    B.collist = listed ? b->d_survivors : nullptr;
+    B.list_count = b->d_count + 2;
     KernelTimer &kt = ctx->timers[ctx->timer_next];
     ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
-    if (kt.pending) {
-        float ms = 0;
-        CU(cudaEventSynchronize(kt.b));
-        CU(cudaEventElapsedTime(&ms, kt.a, kt.b));
-        ctx->kernel_ms += ms; ctx->kernel_n += 1; kt.pending = false;
-    }
+    ssn_status st = timer_collect(ctx, kt);
+    if (st != SSN_OK) return st;
     CU(cudaEventRecord(kt.a, b->stream));
+    kt.filtered = filter;
+    if (filter) {
+        const uint32_t pf_need = (ntiles + kPfWarps - 1) / kPfWarps;
+        const uint32_t pf_grid = std::min<uint32_t>((uint32_t)ctx->num_sms, pf_need);
+        ssn_prefilter_kernel<<<pf_grid, kPfWarps * 32, pf_smem_bytes(), b->stream>>>(
+            ctx->dpf, B, b->d_survivors, b->d_count, dump ? b->d_dump + (SSN_COLUMN_DUMP_WORDS - 1) : nullptr, SSN_COLUMN_DUMP_WORDS);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(kt.m, b->stream));
+        ctx->launches += 1;
+    }
     if (dump) ssn_score_kernel<true><<<grid, kWarpsPerCta * 32, smem, b->stream>>>(ctx->model, B);
     else ssn_score_kernel<false><<<grid, kWarpsPerCta * 32, smem, b->stream>>>(ctx->model, B);
     CU(cudaGetLastError());
@@ -456,7 +517,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
 
 static ssn_status copy_out_async(ssn_batch *b)
 {
-    CU(cudaMemcpyAsync(b->h_count, b->d_count, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, b->stream));
+    CU(cudaMemcpyAsync(b->h_count, b->d_count, kCountWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, b->stream));
     if ((b->flags & SSN_SUBMIT_COLUMN_DUMP) && b->ncol)
         CU(cudaMemcpyAsync(b->h_dump, b->d_dump, (size_t)b->ncol * SSN_COLUMN_DUMP_WORDS * 4, cudaMemcpyDeviceToHost, b->stream));
     CU(cudaEventRecord(b->done, b->stream));
@@ -623,16 +684,59 @@ extern "C" ssn_status ssn_kernel_time(ssn_ctx *ctx, float *total_ms, uint64_t *n
     if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
     CU(cudaSetDevice(ctx->device));
     for (auto &kt : ctx->timers) {
-        if (!kt.pending) continue;
-        float ms = 0;
-        CU(cudaEventSynchronize(kt.b));
-        CU(cudaEventElapsedTime(&ms, kt.a, kt.b));
-        ctx->kernel_ms += ms; ctx->kernel_n += 1; kt.pending = false;
+        ssn_status st = timer_collect(ctx, kt);
+        if (st != SSN_OK) return st;
     }
     if (total_ms) *total_ms = (float)ctx->kernel_ms;
     if (n_launches) *n_launches = ctx->kernel_n;
-    if (reset) { ctx->kernel_ms = 0; ctx->kernel_n = 0; }
+    if (reset) { ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->prefilter_ms = 0; ctx->score_ms = 0; }
     return SSN_OK;
+}
+
+extern "C" ssn_status ssn_kernel_time_split(ssn_ctx *ctx, float *prefilter_ms, float *score_ms, uint64_t *n_batches, int reset)
+{
+    if (!ctx) { ssn_set_error("null ctx"); return SSN_ERR_ARG; }
+    CU(cudaSetDevice(ctx->device));
+    for (auto &kt : ctx->timers) {
+        ssn_status st = timer_collect(ctx, kt);
+        if (st != SSN_OK) return st;
+    }
+    if (prefilter_ms) *prefilter_ms = (float)ctx->prefilter_ms;
+    if (score_ms) *score_ms = (float)ctx->score_ms;
+    if (n_batches) *n_batches = ctx->kernel_n;
+    if (reset) { ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->prefilter_ms = 0; ctx->score_ms = 0; }
+    return SSN_OK;
+}
+
+extern "C" int ssn_prefilter_enabled(const ssn_ctx *ctx) { return ctx && ctx->pf_on ? 1 : 0; }
+
+extern "C" ssn_status ssn_batch_survivors(const ssn_batch *b, uint32_t *n_columns)
+{
+    if (!b || !n_columns) { ssn_set_error("ssn_batch_survivors: null"); return SSN_ERR_ARG; }
+    *n_columns = b->h_count[2];
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_host_prefilter_create(const ssn_params *p, ssn_prefilter_view *view, void **handle)
+{
+    if (!p || !view || !handle) { ssn_set_error("ssn_host_prefilter_create: null"); return SSN_ERR_ARG; }
+    ssn_host_tables m;
+    if (ssn_tables_build(p, &m) != 0) { ssn_set_error("table construction failed (n_hap=%d)", p->n_hap); return SSN_ERR_ARG; }
+    ssn_prefilter_tables *t = new ssn_prefilter_tables();
+    const int rc = ssn_prefilter_build(&m, (int)(m.q_r + 0.5), t);
+    ssn_tables_free(&m);
+    if (rc != 0) { delete t; ssn_set_error("out of memory"); return SSN_ERR_NOMEM; }
+    view->ab = t->ab; view->h = t->h; view->F = t->F; view->n = SSN_PF_N; view->enabled = t->enabled;
+    *handle = t;
+    return SSN_OK;
+}
+
+extern "C" void ssn_host_prefilter_destroy(void *handle)
+{
+    ssn_prefilter_tables *t = (ssn_prefilter_tables*)handle;
+    if (!t) return;
+    ssn_prefilter_free(t);
+    delete t;
 }
 
 __global__ void ssn_flush_kernel(uint4 *p, size_t n)

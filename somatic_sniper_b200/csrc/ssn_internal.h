@@ -21,6 +21,17 @@ typedef struct {
 } ssn_host_tables;
 
 int ssn_tables_build(const ssn_params *p, ssn_host_tables *t);
+
+/* bound tables of the exact hom-reference pre-filter (ssn_prefilter_tables.c) */
+#define SSN_PF_N 256
+typedef struct {
+    float *ab;                  /* [n][m][4] = { cmin_all, cmax_run, g2_run, 0 } */
+    float *h;                   /* [a][b] */
+    float F[SSN_PF_N + 1];      /* F[k] = (1 - 1e-4) * sum_{w<k} fk[w], rounded down */
+    int enabled;                /* 0: the parameter set breaks a precondition of the proof */
+} ssn_prefilter_tables;
+int ssn_prefilter_build(const ssn_host_tables *m, int q_r_int, ssn_prefilter_tables *t);
+void ssn_prefilter_free(ssn_prefilter_tables *t);
 void ssn_tables_free(ssn_host_tables *t);
 
 /* bam_nt16_table (samtools-0.1.6 bam_import.c:23-40): reference character -> 4-bit code */

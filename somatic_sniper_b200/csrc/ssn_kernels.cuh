@@ -105,6 +105,9 @@ struct DevBatch {
     uint32_t *scratch;      /* per-warp global key store for tiles that exceed shared memory */
     uint32_t scratch_words_per_warp;
     uint32_t smem_words_per_warp;
+    /* list mode (behind the pre-filter, ssn_prefilter.cuh): score columns collist[0 .. *list_count) instead of 0 .. ncol */
+    const uint32_t *collist;
+    const uint32_t *list_count;
 };
 
 /* -------------------------------------------------------------------------------------------- */
@@ -853,7 +856,17 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
     const uint32_t fk2_s = smem_u32(T.fk2), lut_s = smem_u32(T.lut3), tail_s = smem_u32(T.tail);
     const uint32_t gwarp = blockIdx.x * kWarpsPerCta + warp;
     uint32_t *keys_g = B.scratch ? B.scratch + (size_t)gwarp * B.scratch_words_per_warp : nullptr;
-    const uint32_t ntiles = (B.ncol + 31u) >> 5;
+    /* list mode: few columns, gathered from anywhere in the batch.  Narrow tiles (W columns per warp) spread them over
+     * every resident warp; the lanes past W idle.  Gathered columns are not contiguous, so they take the generic path. */
+    const bool listed = B.collist != nullptr;
+    uint32_t ncols = B.ncol, W = 32u;
+    if (listed) {
+        ncols = min(*B.list_count, B.ncol);
+        const uint32_t warps = gridDim.x * (uint32_t)kWarpsPerCta, per = (ncols + warps - 1u) / warps;
+        W = 4u;
+        while (W < per && W < 32u) W <<= 1;
+    }
+    const uint32_t ntiles = (ncols + W - 1u) / W;
     uint32_t phase = 0;
 
     for (;;) {
@@ -869,8 +882,9 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         tile = __shfl_sync(kFull, tile, 0);
         if (tile >= ntiles) break;
 #endif
-        const uint32_t col = tile * 32u + lane;
-        const bool live = col < B.ncol;
+        const uint32_t idx = tile * W + lane;
+        const bool live = (uint32_t)lane < W && idx < ncols;
+        const uint32_t col = listed ? (live ? B.collist[idx] : 0u) : idx;
         uint32_t o0 = 0, o1 = 0, o2 = 0, ref16 = 15;
         if (live) {
             o0 = B.off[2 * col]; o1 = B.off[2 * col + 1]; o2 = B.off[2 * col + 2];
@@ -881,7 +895,7 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         /* the tile's read-bases are contiguous: [off of its first column, end of its last live column) */
         const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
         const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
-        const bool fast = need <= 2u * kFastWords && bytes <= (uint32_t)kRawBytes && B.smem_words_per_warp >= kFastWords * 32u;
+        const bool fast = !listed && need <= 2u * kFastWords && bytes <= (uint32_t)kRawBytes && B.smem_words_per_warp >= kFastWords * 32u;
 
         uint32_t my_rms_t = 0, my_rms_n = 0;
         bool done = false;

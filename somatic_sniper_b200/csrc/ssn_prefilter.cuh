@@ -1,0 +1,160 @@
+/*
+ * ssn_prefilter.cuh — the exact hom-reference pre-filter kernel (sm_100a).  DESIGN.md §4b has the derivation.
+ *
+ * glf_somatic emits nothing for a column whose two consensus genotypes agree (somatic_sniper.c:156).  This kernel
+ * streams over every column of a batch once (TMA bulk-staged tiles of 32 columns, lane-per-column, packed byte
+ * arithmetic: ~9 instructions per read-base instead of the ~95 of the full model) and PROVES, for most columns, that
+ * sniper_glf2cns (sniper_maqcns.c:250-273) calls the homozygous reference genotype in both samples.  Those columns are
+ * finished.  Every other column - real variants, noisy columns, anything the bounds cannot decide, every column of a
+ * tile that is not "clean" (a base quality outside [1,63]) or too deep for the staging area - is appended to the
+ * survivor list and goes through the full model (ssn_score_kernel in list mode).  Results are identical to scoring
+ * every column; SSN_SUBMIT_NO_PREFILTER switches the filter off, SSN_SUBMIT_COLUMN_DUMP records its decision next to the
+ * full model's output so tests can audit it.
+ *
+ * Per sample the filter needs (all from one pass over bs/bq/mq):
+ *   n      read-bases                         m   read-bases whose nt16 code differs from the reference's
+ *   S      sum over those m of base quality    n1  reference read-bases on the reverse strand
+ *   Q1,Q0  sum of min(baseQ, mapQ & 0x7f) over the reference read-bases of the reverse / forward strand
+ * and evaluates (tables: ssn_prefilter_tables.c)
+ *   t1 = F[n1] * Q1 / (n1 + m) + F[n0] * Q0 / (n0 + m)            lower bound of the reference base's esum chain
+ *   SU = (S + 3 m) (1 + 1e-4)                                      upper bound of the other bases' esum chains
+ *   U  = max(SU + cmax_run[n][m], 0) + 1.1                         upper bound of p[RR], plus the margin RR must win by
+ *   keep scoring unless  t1 > SU  and  t1 + cmin_all[n][m] >= U  and  h[n-m][m] + g2_run[n][m] >= U   (both samples)
+ */
+#pragma once
+#include "ssn_kernels.cuh"
+
+namespace ssn {
+
+#ifndef SSN_PF_WARPS
+#define SSN_PF_WARPS 20
+#endif
+constexpr int kPfWarps = SSN_PF_WARPS;                 /* 20 x 9.6 KB of staging per SM */
+constexpr int kPfStageBytes = 3 * kRawBytes;
+
+struct DevPrefilter {
+    const float4 *ab;     /* [n*256 + m] = { cmin_all, cmax_run, g2_run, 0 } */
+    const float *h;       /* [(n-m)*256 + m] */
+    const float *F;       /* 257 */
+};
+
+struct PfShared {
+    float F[260];
+    unsigned long long mbar[kPfWarps];
+};
+
+struct PfStats { uint32_t m, S, n1, qref, q1; };
+
+/* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.
+ * C = tile-uniform number of 4-read-base chunks; R4 = the reference's nt16 code in every byte. */
+__device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, int C, uint32_t R4, PfStats &st)
+{
+    const uint32_t a = raw_s + (r & ~3u), sh = (r & 3u) * 8u;
+    uint32_t ws = lds_u32(a), wq = lds_u32(a + kRawBytes), wm = lds_u32(a + 2 * kRawBytes);
+    uint32_t bits = len * 8u;                      /* live bits left in this sample */
+    uint32_t acc_m = 0, acc_n1 = 0, S = 0, qref = 0, q1 = 0;
+    const uint32_t ones = 0x01010101u;
+#pragma unroll 2
+    for (int c = 0; c < C; ++c) {
+        const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
+        const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);          /* low min(bits,32) bits */
+        bits = max(bits, 32u) - 32u;
+        /* dead bytes become "reference base, forward strand, quality 0": they add nothing to any sum */
+        const uint32_t BS = (__funnelshift_r(ws, ns, sh) & keep) | (R4 & ~keep);
+        const uint32_t BQ = __funnelshift_r(wq, nq, sh) & keep;
+        const uint32_t M7 = __funnelshift_r(wm, nm, sh) & 0x7f7f7f7fu;
+        ws = ns; wq = nq; wm = nm;
+        /* nz: 1 in every byte whose nt16 code differs from the reference's */
+        const uint32_t nz = ((((BS ^ R4) & 0x0f0f0f0fu) + 0x7f7f7f7fu) >> 7) & ones;
+        const uint32_t NM = nz * 0xffu;
+        acc_m += nz;
+        S = __dp4a(BQ & NM, ones, S);
+        const uint32_t s1 = (BS >> 4) & ones & ~nz;                            /* reference read-base on the reverse strand */
+        acc_n1 += s1;
+        /* q = min(baseQ, mapQ & 0x7f) per byte: baseQ <= 63, so (baseQ + 0x80 - m7) keeps bit 7 iff baseQ >= m7 */
+        const uint32_t ge = ((BQ + 0x80808080u - M7) >> 7) & ones;
+        const uint32_t GM = ge * 0xffu;
+        const uint32_t q = (M7 & GM) | (BQ & ~GM);
+        qref = __dp4a(q & ~NM, ones, qref);
+        q1 = __dp4a(q & (s1 * 0xffu), ones, q1);
+    }
+    st.m = __dp4a(acc_m, ones, 0u); st.n1 = __dp4a(acc_n1, ones, 0u);
+    st.S = S; st.qref = qref; st.q1 = q1;
+}
+
+/* true: genotype RR provably wins sniper_glf2cns for this sample */
+__device__ __forceinline__ bool pf_eval(const DevPrefilter &P, const float *F, uint32_t n, const PfStats &st)
+{
+    const uint32_t m = st.m, n1 = st.n1, n0 = n - m - n1;
+    const float4 ab = __ldg(P.ab + n * 256u + m);
+    const float hs = __ldg(P.h + (n - m) * 256u + m);
+    const float t1 = __fdividef(F[n1] * (float)st.q1, (float)max(n1 + m, 1u)) + __fdividef(F[n0] * (float)(st.qref - st.q1), (float)max(n0 + m, 1u));
+    const float SU = (float)(st.S + 3u * m) * 1.0001f;
+    const float U = fmaxf(SU + ab.y, 0.0f) + 1.1f;
+    return t1 > SU && t1 + ab.x >= U && hs + ab.z >= U;
+}
+
+/* counters: [2] = survivors appended, [3] = tile counter.  decision (optional, stride words per column): 1 = dropped. */
+__global__ void __launch_bounds__(kPfWarps * 32, 1)
+ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors, uint32_t *counters, uint32_t *decision, uint32_t decision_stride)
+{
+    __shared__ PfShared T;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 257; i += blockDim.x) T.F[i] = P.F[i];
+    const uint32_t mbar_s = smem_u32(&T.mbar[warp]);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar_s) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint32_t raw_s = smem_u32(smem_raw + (size_t)warp * kPfStageBytes);
+    const uint32_t ntiles = (B.ncol + 31u) >> 5;
+    uint32_t phase = 0;
+
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(counters + 3, 1u);
+        tile = __shfl_sync(kFull, tile, 0);
+        if (tile >= ntiles) break;
+        const uint32_t col = tile * 32u + lane;
+        const bool live = col < B.ncol;
+        uint32_t o0 = 0, o1 = 0, o2 = 0, ref16 = 15;
+        if (live) {
+            o0 = B.off[2 * col]; o1 = B.off[2 * col + 1]; o2 = B.off[2 * col + 2];
+            ref16 = B.ref_nt16[col] & 15u;
+        }
+        const uint32_t nT = o1 - o0, nN = o2 - o1;
+        /* a column can only reach the output with read-bases in both samples and a called reference (somatic_sniper.c:127,156) */
+        const bool wanted = live && nT != 0u && nN != 0u && ref16 != 15u;
+        const uint32_t maxT = __reduce_max_sync(kFull, nT), maxN = __reduce_max_sync(kFull, nN);
+        const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
+        const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
+        bool drop = false;
+        __syncwarp();
+        if (__any_sync(kFull, wanted) && maxT <= 255u && maxN <= 255u && bytes <= (uint32_t)kRawBytes) {
+            if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
+            stage_wait(mbar_s, phase);
+            phase ^= 1u;
+            if (tile_is_clean(raw_s, bytes, lane)) {
+                const uint32_t r0 = live ? o0 - a0 : 0u;
+                const uint32_t R4 = ref16 * 0x01010101u;
+                PfStats sT, sN;
+                pf_sample(raw_s, r0, nT, (int)((maxT + 3u) >> 2), R4, sT);
+                pf_sample(raw_s, r0 + nT, nN, (int)((maxN + 3u) >> 2), R4, sN);
+                drop = wanted && __popc(ref16) == 1 && pf_eval(P, T.F, nT, sT) && pf_eval(P, T.F, nN, sN);
+            }
+        }
+        const bool survive = wanted && !drop;
+        const uint32_t mask = __ballot_sync(kFull, survive);
+        if (mask) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(counters + 2, (uint32_t)__popc(mask));
+            base = __shfl_sync(kFull, base, 0);
+            if (survive) survivors[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = col;
+        }
+        if (decision && live) decision[(size_t)col * decision_stride] = drop ? 1u : 0u;
+    }
+}
+
+}  // namespace ssn

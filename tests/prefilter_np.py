@@ -1,0 +1,63 @@
+"""numpy restatement of the hom-reference pre-filter's decision (somatic_sniper_b200/csrc/ssn_prefilter.cuh), evaluated with
+the bound tables the product's host code builds (ssn_prefilter_tables.c).  Test infrastructure: lets the CPU suite check
+the filter's proof obligations against the oracle without a GPU, and gives the GPU tests an independent expectation of
+how many columns the kernel should drop."""
+import numpy as np
+
+from somatic_sniper_b200 import api
+
+RAW_BYTES = 3200      # kRawBytes: staged read-bases per array of one 32-column tile
+
+
+def decide(cols, tables=None, tile_rules=True):
+    """Returns bool[ncol]: True where the pre-filter drops the column (both samples provably call hom-reference).
+    tile_rules: also apply the kernel's per-tile conditions (clean base qualities, depth and staging limits)."""
+    t = tables or api.host_prefilter_tables()
+    ab, h, F = t["ab"].astype(np.float64), t["h"].astype(np.float64), t["F"].astype(np.float64)
+    ncol = int(cols["ncol"])
+    if not t["enabled"] or ncol == 0:
+        return np.zeros(ncol, bool)
+    off = cols["off"].astype(np.int64)
+    bs, bq, mq = cols["bs"], cols["bq"].astype(np.int64), cols["mq"].astype(np.int64)
+    ref16 = api.nt16_lut()[cols["ref_char"]].astype(np.int64)
+    n = np.diff(off)
+    seg = np.repeat(np.arange(2 * ncol), n)
+    col = seg >> 1
+    nonref = (bs & 15) != ref16[col]
+    rev = ((bs >> 4) & 1) == 1
+    q = np.minimum(bq, mq & 0x7f)
+    cnt = lambda w: np.bincount(seg, w, 2 * ncol)
+    m = cnt(nonref).astype(np.int64)
+    S = cnt(nonref * bq)
+    n1 = cnt(~nonref & rev).astype(np.int64)
+    q1 = cnt((~nonref & rev) * q)
+    q0 = cnt((~nonref & ~rev) * q)
+    n0 = n - m - n1
+    ok = n <= 255
+    nn, mm = np.minimum(n, 255), np.minimum(m, 255)
+    t1 = F[np.minimum(n1, 256)] * q1 / np.maximum(n1 + m, 1) + F[np.minimum(n0, 256)] * q0 / np.maximum(n0 + m, 1)
+    SU = (S + 3 * m) * 1.0001
+    U = np.maximum(SU + ab[nn, mm, 1], 0.0) + 1.1
+    hs = h[np.minimum(n - m, 255), mm]
+    sample_ok = ok & (t1 > SU) & (t1 + ab[nn, mm, 0] >= U) & (hs + ab[nn, mm, 2] >= U)
+    nT, nN = n[0::2], n[1::2]
+    wanted = (nT > 0) & (nN > 0) & (ref16 != 15)
+    drop = wanted & np.isin(ref16, [1, 2, 4, 8]) & sample_ok[0::2] & sample_ok[1::2]
+    if tile_rules:
+        bad_bq = np.bincount(col, (bq < 1) | (bq > 63), ncol) > 0
+        ntile = (ncol + 31) // 32
+        tile = np.arange(ncol) >> 5
+        pad = ntile * 32 - ncol
+        tile_bad = np.bincount(tile, bad_bq, ntile) > 0
+        tmax = lambda v: np.pad(v, (0, pad)).reshape(ntile, 32).max(1)
+        first = off[0:2 * ncol:64] & ~15
+        last = off[np.minimum(np.arange(1, ntile + 1) * 64, 2 * ncol)]
+        tile_bad |= (tmax(nT) > 255) | (tmax(nN) > 255) | (((last - first + 15) & ~15) > RAW_BYTES)
+        # slack bytes of the neighbouring tiles are scanned too (conservative in the kernel); ignore that here
+        drop &= ~tile_bad[tile]
+    return drop
+
+
+def consensus_genotypes(glf):
+    """(tumor, normal) best genotype masks from the oracle's / the kernel's 28-word column dump."""
+    return glf[:, 13] >> 28, glf[:, 27] >> 28

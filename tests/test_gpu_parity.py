@@ -203,3 +203,80 @@ def test_reference_integration_columns(mods, cfg):
     if cfg == "default":
         pos = np.load(os.path.join(GOLD, "integration.npz"))["pos"]
         assert [int(pos[c]) + 1 for c in want["emit_col"]] == [63, 73, 260]
+
+
+# ---- the exact hom-reference pre-filter (ssn_prefilter.cuh) ------------------------------------
+
+PF_CASES = [
+    ("wgs", dict(ncol=400000, seed=41)),
+    ("unbinned", dict(ncol=150000, seed=42, binned=False)),
+    ("edge", dict(ncol=150000, seed=43, edge=0.5, p_som=5e-3)),
+    ("shallow", dict(ncol=150000, depth_t=12, depth_n=6, seed=44, edge=0.1)),
+    ("very shallow", dict(ncol=150000, depth_t=3, depth_n=2, seed=45)),
+    ("mid", dict(ncol=40000, depth_t=110, depth_n=100, seed=46, binned=False)),
+    ("variant rich", dict(ncol=100000, seed=47, p_het=0.05, p_hom=0.02, p_som=0.05, p_loh=0.01, p_gor=0.01)),
+    ("deep", dict(ncol=400, depth_t=1500, depth_n=900, seed=48)),
+]
+
+
+@pytest.mark.parametrize("name,kw", PF_CASES, ids=[c[0] for c in PF_CASES])
+def test_prefilter_audit_and_identical_sites(mods, name, kw):
+    """(1) Every column the pre-filter kernel drops has, in the full model's own dump, the homozygous reference as the
+    consensus of both samples - so glf_somatic could not have emitted it.  (2) The product path (filter + list-mode
+    scoring) returns exactly the sites of the all-columns path.  (3) The kernel drops what the numpy restatement drops."""
+    import prefilter_np
+    api, synth, Oracle = mods
+    kw = dict(kw)
+    n = kw.pop("ncol")
+    cols = synth.make_columns(n, **kw)
+    ent = int(cols["n_entries"]) + 64
+    for joint in (0, 1):
+        prm = api.default_params(use_joint_priors=joint, min_somatic_qual=0 if joint else 15)
+        sc = api.Scorer(prm, device=0, n_slots=1, max_columns=n, max_entries=ent)
+        assert sc.prefilter_enabled()
+        _, dump = sc.score(cols, dump=True)
+        dropped = dump[:, 29] == 1
+        tg, ng = prefilter_np.consensus_genotypes(dump)
+        ref16 = api.nt16_lut()[cols["ref_char"]]
+        bad = dropped & ((tg != ref16) | (ng != ref16))
+        assert bad.sum() == 0, "dropped columns with a non-reference consensus: %s" % np.nonzero(bad)[0][:5]
+        full, _ = sc.score(cols, flags=api.SUBMIT_NO_PREFILTER)
+        assert sc.last_survivors == 0
+        fast, _ = sc.score(cols)
+        survivors = sc.last_survivors
+        sc.close()
+        assert fast.tobytes() == full.tobytes(), "the filtered path returned different sites"
+        assert not dropped[full["column"]].any()
+        if joint == 0:
+            want = prefilter_np.decide(cols)
+            wanted = (np.diff(cols["off"].astype(np.int64))[0::2] > 0) & (np.diff(cols["off"].astype(np.int64))[1::2] > 0) & (ref16 != 15)
+            assert survivors == int((wanted & ~dropped).sum())
+            # float rounding (device: fp32 + MUFU.RCP, numpy: fp64) may flip columns that sit exactly on a bound
+            # (the kernel's clean-tile check also sees the neighbouring tiles' alignment bytes, so only compare where every
+            # base quality is legal)
+            if name in ("wgs", "unbinned", "very shallow", "mid", "variant rich", "deep"):
+                assert int((dropped ^ want).sum()) <= 3, (dropped.sum(), want.sum())
+            if name in ("wgs", "unbinned"):
+                assert dropped.mean() > 0.95
+
+
+def test_prefilter_through_the_pipeline(mods):
+    """Several batches in flight through acquire/submit/results_next with the filter on: same sites as with it off."""
+    api, synth, _ = mods
+    batches = [synth.make_columns(50000 + 1000 * i, seed=60 + i, edge=0.02 * i) for i in range(5)]
+    cap = max(int(b["n_entries"]) for b in batches) + 64
+    out = {}
+    for flags in (0, api.SUBMIT_NO_PREFILTER):
+        sc = api.Scorer(api.default_params(), device=0, n_slots=3, max_columns=60000, max_entries=cap)
+        got, pending = [], 0
+        for cols in batches:
+            if pending == 3:
+                s, h = sc.results_next(); got.append(s); pending -= 1
+            b = sc.acquire(); b.fill(cols); sc.submit(b, flags); pending += 1
+        while pending:
+            s, h = sc.results_next(); got.append(s); pending -= 1
+        sc.close()
+        out[flags] = got
+    for a, b in zip(out[0], out[api.SUBMIT_NO_PREFILTER]):
+        assert a.tobytes() == b.tobytes()
+    assert sum(len(a) for a in out[0]) > 0

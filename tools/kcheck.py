@@ -37,14 +37,20 @@ def rate(ncol=1_000_000, steps=10):
     cols = synth.make_columns(ncol, seed=1234)
     sc = api.Scorer(api.default_params(), device=0, n_slots=1, max_columns=ncol, max_entries=int(cols["n_entries"]) + 64)
     b = sc.acquire(); b.fill(cols); sc.upload(b)
-    for _ in range(3): sc.score_resident(b)
-    sc.sync(); sc.kernel_time(reset=True)
-    sc.timer_start()
-    for _ in range(steps): sc.score_resident(b)
-    ms = sc.timer_stop()
-    n = len(sc.fetch(b))
+    ref = None
+    for name, flags in (("full model, every column", api.SUBMIT_NO_PREFILTER), ("pre-filter + full model on survivors", 0)):
+        for _ in range(3): sc.score_resident(b, flags)
+        sc.sync(); sc.kernel_time(reset=True)
+        sc.timer_start()
+        for _ in range(steps): sc.score_resident(b, flags)
+        ms = sc.timer_stop()
+        sites = sc.fetch(b)
+        pf, scms, nb = sc.kernel_time_split(reset=True)
+        if ref is None: ref = sites
+        same = sites.tobytes() == ref.tobytes()
+        print("rate %-38s %.4g columns/s  (%.3f ms per 1e6-column step; pre-filter %.3f ms, scoring %.3f ms; %d sites, %d survivors, identical=%s)"
+              % (name, ncol * steps / (ms * 1e-3), ms / steps, pf / max(nb, 1), scms / max(nb, 1), len(sites), b.survivors(), same), flush=True)
     sc.close()
-    print("rate %.4g columns/s  (%.3f ms per 1e6-column launch, %d sites)" % (ncol * steps / (ms * 1e-3), ms / steps, n), flush=True)
 
 if __name__ == "__main__":
     ok = True
