@@ -9,11 +9,14 @@ BASELINE.json configs[1] — a synthetic 1 Mb region, normal 30x / tumor 60x, de
 (-Q 15, independent priors): 1,000,000 columns per GPU (weak scaling: region shards are independent,
 no collective on the data path; torch.distributed only carries the barrier and the max-over-ranks).
 
-value      columns/s, all ranks, batches already resident in HBM, timed with CUDA events
+value      columns/s, all ranks, batches already resident in HBM, timed with CUDA events; the product path:
+           the exact hom-reference pre-filter kernel over every column, then the full model on the survivors
+full_model the same with SSN_SUBMIT_NO_PREFILTER: every column through the full model (identical sites)
 e2e        the same through ssn_batch_submit/ssn_results_next with pinned HOST batches:
            H2D of every column + kernel + D2H of the site ring inside the timed region
 roofline   HBM: algorithmic bytes (3 B per read-base + 9 B per column) per launch /
-           the kernel's mean launch duration (events around each launch on its own stream)
+           the dominant kernel's mean launch duration (events around each launch on its own stream); the dominant
+           kernel is the pre-filter (it reads every byte of the batch); step_frac = the same over both kernels
 cpu_baseline  the unmodified reference (oracle/_ref, 1 thread) on a bounded sample, rank 0, N=1 only
 """
 import argparse
@@ -60,12 +63,12 @@ def measured_peak():
         return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
 
 
-def ncu_traffic():
-    """dram bytes per launch of the scoring kernel from the committed ncu capture, or None."""
+def ncu_traffic(key="dram_bytes_per_launch"):
+    """dram bytes per launch of a kernel from the committed ncu capture (profiles/traffic.json), or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(p) as f:
-            return json.load(f).get("dram_bytes_per_launch")
+            return json.load(f).get(key)
     except Exception:
         return None
 
@@ -271,10 +274,26 @@ def run_b200(args):
     b = sc.acquire()
     b.fill(cols)
     sc.upload(b)
+    filtered = sc.prefilter_enabled()
+    # every column through the full model (the pre-filter switched off): same sites, reported beside the product path
+    for _ in range(max(args.warmup, 3)):
+        sc.score_resident(b, api.SUBMIT_NO_PREFILTER)
+    sc.sync()
+    sites_full = sc.fetch(b)
+    sc.kernel_time(reset=True)
+    dist_barrier(dist)
+    sc.timer_start()
+    for _ in range(args.steps):
+        sc.score_resident(b, api.SUBMIT_NO_PREFILTER)
+    ms_full = sc.timer_stop()
+    dist_barrier(dist)
+    _, full_kms, full_kn = sc.kernel_time_split(reset=True)
     for _ in range(max(args.warmup, 3)):
         sc.score_resident(b)
     sc.sync()
     sites_ref = sc.fetch(b)
+    survivors = b.survivors()
+    assert sites_ref.tobytes() == sites_full.tobytes(), "pre-filtered path and full-model path disagree"
     sc.kernel_time(reset=True)
     l0 = sc.kernel_launches()
     sampler = ClockSampler(local)
@@ -288,14 +307,21 @@ def run_b200(args):
     ms = sc.timer_stop()
     dist_barrier(dist)
     launches = sc.kernel_launches() - l0
-    kms, kn = sc.kernel_time(reset=True)
+    pf_ms, score_ms, kn = sc.kernel_time_split(reset=True)
+    kms = pf_ms + score_ms
     n_sites = len(sites_ref)
     sc.release(b)
     sc.close()
     value, ms_max, total_cols = whole_job_rate(dist, ncol, args.steps, ms)
     peak, peak_src = measured_peak()
     k_avg_ms = kms / max(kn, 1)
-    achieved = alg_bytes / (k_avg_ms * 1e-3) / 1e9
+    full_value, full_ms_max, _ = whole_job_rate(dist, ncol, args.steps, ms_full)
+    full_k_ms = full_kms / max(full_kn, 1)
+    if filtered:
+        dom_name, dom_ms, dom_traffic = "ssn_prefilter_kernel", pf_ms / max(kn, 1), ncu_traffic("prefilter_dram_bytes_per_launch")
+    else:
+        dom_name, dom_ms, dom_traffic = "ssn_score_kernel<false>", k_avg_ms, ncu_traffic()
+    achieved = alg_bytes / (dom_ms * 1e-3) / 1e9
 
     # ---- e2e: pinned host batches through submit/results_next ----------------------------------------
     e2e = None
@@ -351,13 +377,22 @@ def run_b200(args):
             "dtype": "f64/f32+int", "data": "synthetic",
             "config": {"workload": WORKLOAD, "columns_per_gpu_per_step": ncol, "read_bases_per_step": nent,
                        "depth_tumor": args.depth_t, "depth_normal": args.depth_n, "sites_per_step": n_sites,
+                       "prefilter": "exact hom-reference pre-filter on; %d of %d columns go on to the full model" % (survivors, ncol)
+                                    if filtered else "off",
                        "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (alg_bytes / 1e6),
                        "parallelism": "region shards, %d GPU(s), no collective" % args.gpus},
             "clocks": sampler.summary(),
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "ssn_score_kernel<false>",
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": k_avg_ms},
+                         "traffic": dom_traffic, "peak_source": peak_src, "kernel": dom_name,
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": dom_ms,
+                         "step_kernels_ms": {"ssn_prefilter_kernel": pf_ms / max(kn, 1), "ssn_score_kernel<false> (survivors)": score_ms / max(kn, 1)},
+                         "step_frac": alg_bytes / (k_avg_ms * 1e-3) / 1e9 / peak},
+            "full_model": {"value": full_value, "unit": UNIT, "ms_per_step": full_ms_max / args.steps,
+                           "note": "SSN_SUBMIT_NO_PREFILTER: every column through ssn_score_kernel<false>; identical sites",
+                           "roofline": {"bound": "hbm", "achieved": alg_bytes / (full_k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                        "frac": alg_bytes / (full_k_ms * 1e-3) / 1e9 / peak, "traffic": ncu_traffic(),
+                                        "kernel": "ssn_score_kernel<false>", "kernel_ms_per_launch": full_k_ms}},
             }
     if e2e is not None:
         line["e2e"] = e2e
