@@ -10,7 +10,9 @@ BASELINE.json configs[1] — a synthetic 1 Mb region, normal 30x / tumor 60x, de
 no collective on the data path; torch.distributed only carries the barrier and the max-over-ranks).
 
 value      columns/s, all ranks, batches already resident in HBM, timed with CUDA events; the product path:
-           the exact hom-reference pre-filter kernel over every column, then the full model on the survivors
+           the exact hom-reference pre-filter kernel over every column, then the full model on the survivors;
+           4 resident batches in flight on their slot streams (the survivors' kernel of one batch overlaps the
+           next batch's pre-filter); single_stream = the same with one batch at a time
 full_model the same with SSN_SUBMIT_NO_PREFILTER: every column through the full model (identical sites)
 e2e        the same through ssn_batch_submit/ssn_results_next with pinned HOST batches:
            H2D of every column + kernel + D2H of the site ring inside the timed region
@@ -35,6 +37,7 @@ METRIC = "pileup_columns_per_sec_scored"
 UNIT = "columns/s"
 COLUMNS = 1_000_000
 CHUNKS = 8                      # e2e: the step's columns travel as 8 pinned batches on 8 streams
+STREAMS = 4                     # value: resident batches in flight (slot streams), the way the packer pipeline runs
 WORKLOAD = "synthetic 1 Mb region, normal 30x / tumor 60x, -Q 15 independent priors (BASELINE configs[1])"
 
 
@@ -270,10 +273,14 @@ def run_b200(args):
     chunks = [slice_columns(cols, int(bounds[i]), int(bounds[i + 1])) for i in range(CHUNKS)]
 
     # ---- value: resident batch, kernel only --------------------------------------------------------
-    sc = api.Scorer(api.default_params(), device=local, n_slots=1, max_columns=ncol, max_entries=nent + 64)
-    b = sc.acquire()
-    b.fill(cols)
-    sc.upload(b)
+    sc = api.Scorer(api.default_params(), device=local, n_slots=STREAMS, max_columns=ncol, max_entries=nent + 64)
+    resident = []
+    for _ in range(STREAMS):
+        b = sc.acquire()
+        b.fill(cols)
+        sc.upload(b)
+        resident.append(b)
+    b = resident[0]
     filtered = sc.prefilter_enabled()
     # every column through the full model (the pre-filter switched off): same sites, reported beside the product path
     for _ in range(max(args.warmup, 3)):
@@ -295,24 +302,42 @@ def run_b200(args):
     survivors = b.survivors()
     assert sites_ref.tobytes() == sites_full.tobytes(), "pre-filtered path and full-model path disagree"
     sc.kernel_time(reset=True)
-    l0 = sc.kernel_launches()
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.25)                    # nvidia-smi needs a moment before its first sample
+    # one batch at a time: the kernels run back to back, so their durations are their own (roofline)
     dist_barrier(dist)
     sc.sync()
     sc.timer_start()
     for _ in range(args.steps):
         sc.score_resident(b)
-    ms = sc.timer_stop()
+    ms_single = sc.timer_stop()
     dist_barrier(dist)
-    launches = sc.kernel_launches() - l0
     pf_ms, score_ms, kn = sc.kernel_time_split(reset=True)
     kms = pf_ms + score_ms
     n_sites = len(sites_ref)
-    sc.release(b)
+    # STREAMS batches in flight
+    for i in range(2 * STREAMS):
+        sc.score_resident(resident[i % STREAMS])
+    sc.sync()
+    for r in resident:
+        assert sc.fetch(r).tobytes() == sites_ref.tobytes()
+    sc.kernel_time(reset=True)
+    l0 = sc.kernel_launches()
+    dist_barrier(dist)
+    sc.sync()
+    sc.timer_start()
+    for i in range(args.steps):
+        sc.score_resident(resident[i % STREAMS])
+    ms = sc.timer_stop()
+    dist_barrier(dist)
+    launches = sc.kernel_launches() - l0
+    ov_pf_ms, ov_score_ms, ov_kn = sc.kernel_time_split(reset=True)
+    for r in resident:
+        sc.release(r)
     sc.close()
     value, ms_max, total_cols = whole_job_rate(dist, ncol, args.steps, ms)
+    single_value, single_ms_max, _ = whole_job_rate(dist, ncol, args.steps, ms_single)
     peak, peak_src = measured_peak()
     k_avg_ms = kms / max(kn, 1)
     full_value, full_ms_max, _ = whole_job_rate(dist, ncol, args.steps, ms_full)
@@ -379,6 +404,7 @@ def run_b200(args):
                        "depth_tumor": args.depth_t, "depth_normal": args.depth_n, "sites_per_step": n_sites,
                        "prefilter": "exact hom-reference pre-filter on; %d of %d columns go on to the full model" % (survivors, ncol)
                                     if filtered else "off",
+                       "resident_batches_in_flight": STREAMS,
                        "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (alg_bytes / 1e6),
                        "parallelism": "region shards, %d GPU(s), no collective" % args.gpus},
             "clocks": sampler.summary(),
@@ -387,7 +413,11 @@ def run_b200(args):
                          "traffic": dom_traffic, "peak_source": peak_src, "kernel": dom_name,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": dom_ms,
                          "step_kernels_ms": {"ssn_prefilter_kernel": pf_ms / max(kn, 1), "ssn_score_kernel<false> (survivors)": score_ms / max(kn, 1)},
-                         "step_frac": alg_bytes / (k_avg_ms * 1e-3) / 1e9 / peak},
+                         "step_frac": alg_bytes / (k_avg_ms * 1e-3) / 1e9 / peak,
+                         "measured_in": "single_stream pass (kernels back to back); with %d batches in flight the kernels share the SMs: "
+                                        "pre-filter %.4f ms, survivors %.4f ms per launch" % (STREAMS, ov_pf_ms / max(ov_kn, 1), ov_score_ms / max(ov_kn, 1)),
+                         "whole_step_frac": alg_bytes / (ms_max / args.steps * 1e-3) / 1e9 / peak},
+            "single_stream": {"value": single_value, "unit": UNIT, "ms_per_step": single_ms_max / args.steps},
             "full_model": {"value": full_value, "unit": UNIT, "ms_per_step": full_ms_max / args.steps,
                            "note": "SSN_SUBMIT_NO_PREFILTER: every column through ssn_score_kernel<false>; identical sites",
                            "roofline": {"bound": "hbm", "achieved": alg_bytes / (full_k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",

@@ -107,6 +107,7 @@ struct ssn_ctx {
     float *d_pf_ab, *d_pf_h, *d_pf_F;
     DevPrefilter dpf;
     bool pf_on;
+    double survivor_frac;     /* survivors / columns of the last collected batch: sizes the list-mode grid */
 };
 
 extern "C" ssn_status ssn_params_default(ssn_params *p)
@@ -208,6 +209,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
     ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = nullptr; ctx->pf_on = false;
     memset(&ctx->pf, 0, sizeof(ctx->pf));
+    ctx->survivor_frac = 1.0;
     const char *env = getenv("SSN_SMEM_WORDS");
     ctx->smem_words_default = env ? (uint32_t)atoi(env) : (uint32_t)kFastWords * 32u;
     ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
@@ -470,6 +472,15 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     uint32_t grid = (uint32_t)(ctx->num_sms * per_sm);
     const uint32_t need_ctas = (ntiles + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > need_ctas && !listed) grid = need_ctas;
+    if (listed) {
+        /* The survivor count is only known on the device.  Size the grid from the last collected batch (x1.5, 16-column
+         * tiles, one tile per warp) so that the SMs it does not need stay free for the next batch's pre-filter kernel on
+         * another stream; the persistent tile loop keeps any estimate correct. */
+        static const int tiles_per_warp = getenv("SSN_LIST_TPW") ? std::max(1, atoi(getenv("SSN_LIST_TPW"))) : 1;
+        const double est = std::min(1.0, ctx->survivor_frac * 1.25) * (double)b->ncol;
+        const uint32_t want = (uint32_t)(est / (kListWidth * kWarpsPerCta * tiles_per_warp)) + 1u;
+        grid = std::min(grid, std::max(want, 8u));
+    }
     /* a list-mode tile gathers up to 32 arbitrary columns: size the spill store for 32 of the deepest one */
     const uint32_t tile_words = listed ? 32u * b->max_col_words : b->max_tile_words;
     if (tile_words > words) {
@@ -491,6 +502,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.smem_words_per_warp = words;
     B.collist = listed ? b->d_survivors : nullptr;
     B.list_count = b->d_count + 2;
+    { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 4 || w == 8 || w == 16) ? (uint32_t)w : 0u; }
     KernelTimer &kt = ctx->timers[ctx->timer_next];
     ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
     ssn_status st = timer_collect(ctx, kt);
@@ -554,6 +566,8 @@ static ssn_status collect(ssn_ctx *ctx, ssn_batch *b)
         std::sort(b->h_sites, b->h_sites + n, [](const ssn_site &x, const ssn_site &y) { return x.column < y.column; });
     }
     b->n_sites = n;
+    if ((b->flags & (SSN_SUBMIT_COLUMN_DUMP | SSN_SUBMIT_NO_PREFILTER)) == 0 && ctx->pf_on && b->ncol)
+        ctx->survivor_frac = (double)b->h_count[2] / (double)b->ncol;
     return SSN_OK;
 }
 

@@ -72,6 +72,9 @@ constexpr int kFastWords = 64;         /* largest NW of the fast path: 128 key s
 constexpr int kRawBytes = 3200;        /* per array: staged read-bases of one fast tile (16-byte aligned window) */
 constexpr int kAuxWords = 3 * kRawBytes / 4;   /* raw staging of a fast tile: aliases the key store and the head of the slots */
 static_assert(kAuxWords <= kFastWords * 32 + kSlotWords, "the raw staging must fit in key store + slots");
+constexpr int kListSlot = 160;         /* list mode: staged bytes of one gathered column (<= 128 read-bases + 2 x 15 alignment bytes) */
+constexpr int kListWidth = 16;         /* list mode: at most this many columns per tile (kListWidth * kListSlot <= kRawBytes) */
+static_assert(kListWidth * kListSlot <= kRawBytes, "gathered tiles must fit the staging area");
 constexpr uint32_t kPadPair = 0xffff0000u;     /* an empty register of the sorting network: key 0 | ~key 0 << 16 */
 constexpr unsigned kFull = 0xffffffffu;
 
@@ -108,6 +111,7 @@ struct DevBatch {
     /* list mode (behind the pre-filter, ssn_prefilter.cuh): score columns collist[0 .. *list_count) instead of 0 .. ncol */
     const uint32_t *collist;
     const uint32_t *list_count;
+    uint32_t list_width;    /* 0: pick the tile width from the list length; else 4, 8 or 16 */
 };
 
 /* -------------------------------------------------------------------------------------------- */
@@ -358,6 +362,21 @@ __device__ __forceinline__ bool tile_is_clean(uint32_t raw_s, uint32_t bytes, in
         bad |= (w.y & 0xc0c0c0c0u) | ((w.y - 0x01010101u) & ~w.y & 0x80808080u);
         bad |= (w.z & 0xc0c0c0c0u) | ((w.z - 0x01010101u) & ~w.z & 0x80808080u);
         bad |= (w.w & 0xc0c0c0c0u) | ((w.w - 0x01010101u) & ~w.w & 0x80808080u);
+    }
+    return !__any_sync(kFull, bad != 0u);
+}
+
+/* The same for the gathered tiles of list mode: every lane checks the n staged base qualities of its own column
+ * (bytes [r0, r0+n) of the staged bq array; W = tile-uniform word count). */
+__device__ __forceinline__ bool column_is_clean(uint32_t bq_s, uint32_t r0, uint32_t n, int W)
+{
+    uint32_t bad = 0;
+    const uint32_t a = bq_s + (r0 & ~3u);
+    int lo = (int)(r0 & 3u) * 8, hi = lo + (int)n * 8;                        /* live bit range relative to the current word */
+    for (int i = 0; i < W; ++i, lo -= 32, hi -= 32) {
+        const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, (uint32_t)max(hi, 0)) & ~__funnelshift_lc(0xffffffffu, 0u, (uint32_t)max(lo, 0));
+        const uint32_t w = (lds_u32(a + 4u * (uint32_t)i) & keep) | (0x01010101u & ~keep);
+        bad |= (w & 0xc0c0c0c0u) | ((w - 0x01010101u) & ~w & 0x80808080u);
     }
     return !__any_sync(kFull, bad != 0u);
 }
@@ -864,7 +883,8 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         ncols = min(*B.list_count, B.ncol);
         const uint32_t warps = gridDim.x * (uint32_t)kWarpsPerCta, per = (ncols + warps - 1u) / warps;
         W = 4u;
-        while (W < per && W < 32u) W <<= 1;
+        while (W < per && W < (uint32_t)kListWidth) W <<= 1;
+        if (B.list_width) W = B.list_width;
     }
     const uint32_t ntiles = (ncols + W - 1u) / W;
     uint32_t phase = 0;
@@ -895,18 +915,43 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         /* the tile's read-bases are contiguous: [off of its first column, end of its last live column) */
         const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
         const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
-        const bool fast = !listed && need <= 2u * kFastWords && bytes <= (uint32_t)kRawBytes && B.smem_words_per_warp >= kFastWords * 32u;
+        const bool fast = need <= 2u * kFastWords && (listed || bytes <= (uint32_t)kRawBytes) && B.smem_words_per_warp >= kFastWords * 32u;
 
         uint32_t my_rms_t = 0, my_rms_n = 0;
         bool done = false;
         __syncwarp();                                   /* the previous tile is done with slots / keys */
         if (need != 0u && fast) {
-            if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
             const int C = (int)((need + 3u) >> 2);       /* tile-uniform chunk count (4 read-bases = 2 registers per chunk) */
-            stage_wait(mbar_s, phase);
-            phase ^= 1u;
-            if (tile_is_clean(raw_s, bytes, lane)) {
-                const uint32_t r0 = live ? o0 - a0 : 0u;
+            uint32_t r0 = 0;
+            bool clean;
+            if (!listed) {
+                if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
+                stage_wait(mbar_s, phase);
+                phase ^= 1u;
+                clean = tile_is_clean(raw_s, bytes, lane);
+                r0 = live ? o0 - a0 : 0u;
+            } else {
+                /* gathered tile: every lane bulk-copies its own column's 16-byte aligned window into its slot */
+                const uint32_t s0 = o0 & ~15u, sz = n ? ((o2 - s0 + 15u) & ~15u) : 0u;
+                const uint32_t total = __reduce_add_sync(kFull, sz);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar_s), "r"(3u * total) : "memory");
+                __syncwarp();
+                r0 = sz ? (uint32_t)lane * (uint32_t)kListSlot + (o0 & 15u) : 0u;   /* idle lanes read (and mask) slot 0 */
+                if (sz) {
+                    const uint32_t dst = raw_s + (uint32_t)lane * (uint32_t)kListSlot;
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 :: "r"(dst), "l"(B.bs + s0), "r"(sz), "r"(mbar_s) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 :: "r"(dst + (uint32_t)kRawBytes), "l"(B.bq + s0), "r"(sz), "r"(mbar_s) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 :: "r"(dst + 2u * (uint32_t)kRawBytes), "l"(B.mq + s0), "r"(sz), "r"(mbar_s) : "memory");
+                }
+                stage_wait(mbar_s, phase);
+                phase ^= 1u;
+                clean = column_is_clean(raw_s + (uint32_t)kRawBytes, r0, n, (int)((need + 6u) >> 2));
+            }
+            if (clean) {
                 const uint32_t lutK = lut_s + ref16 * 64u;
                 if (C <= 8) fast_tile<16>(raw_s, r0, nT, n, C, lutK, tail_s, M.cap_mapq, keys_s, slots, fk2_s, lane, my_rms_t, my_rms_n);
                 else if (C <= 16) fast_tile<32>(raw_s, r0, nT, n, C, lutK, tail_s, M.cap_mapq, keys_s, slots, fk2_s, lane, my_rms_t, my_rms_n);

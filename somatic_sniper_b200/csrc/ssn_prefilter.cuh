@@ -27,9 +27,9 @@
 namespace ssn {
 
 #ifndef SSN_PF_WARPS
-#define SSN_PF_WARPS 20
+#define SSN_PF_WARPS 23
 #endif
-constexpr int kPfWarps = SSN_PF_WARPS;                 /* 20 x 9.6 KB of staging per SM */
+constexpr int kPfWarps = SSN_PF_WARPS;                 /* 23 x 9.6 KB of staging per SM */
 constexpr int kPfStageBytes = 3 * kRawBytes;
 
 struct DevPrefilter {
@@ -42,6 +42,14 @@ struct PfShared {
     float F[260];
     unsigned long long mbar[kPfWarps];
 };
+
+/* 0xff in every byte whose bit 7 is set, else 0x00: PRMT with the sign-replication bit of each selector nibble */
+__device__ __forceinline__ uint32_t sign_bytes(uint32_t x)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %1, 0xba98;" : "=r"(r) : "r"(x));
+    return r;
+}
 
 struct PfStats { uint32_t m, S, n1, qref, q1; };
 
@@ -64,21 +72,20 @@ __device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t l
         const uint32_t BQ = __funnelshift_r(wq, nq, sh) & keep;
         const uint32_t M7 = __funnelshift_r(wm, nm, sh) & 0x7f7f7f7fu;
         ws = ns; wq = nq; wm = nm;
-        /* nz: 1 in every byte whose nt16 code differs from the reference's */
-        const uint32_t nz = ((((BS ^ R4) & 0x0f0f0f0fu) + 0x7f7f7f7fu) >> 7) & ones;
-        const uint32_t NM = nz * 0xffu;
-        acc_m += nz;
+        /* byte masks by sign replication (PRMT): NM = 0xff where the nt16 code differs from the reference's,
+         * RV = 0xff where a reference read-base sits on the reverse strand */
+        const uint32_t NM = sign_bytes(((BS ^ R4) & 0x0f0f0f0fu) + 0x7f7f7f7fu);
+        const uint32_t RV = sign_bytes(BS << 3) & ~NM;
+        acc_m = __dp4a(NM, ones, acc_m);                                        /* 255 per non-reference read-base */
+        acc_n1 = __dp4a(RV, ones, acc_n1);
         S = __dp4a(BQ & NM, ones, S);
-        const uint32_t s1 = (BS >> 4) & ones & ~nz;                            /* reference read-base on the reverse strand */
-        acc_n1 += s1;
         /* q = min(baseQ, mapQ & 0x7f) per byte: baseQ <= 63, so (baseQ + 0x80 - m7) keeps bit 7 iff baseQ >= m7 */
-        const uint32_t ge = ((BQ + 0x80808080u - M7) >> 7) & ones;
-        const uint32_t GM = ge * 0xffu;
-        const uint32_t q = (M7 & GM) | (BQ & ~GM);
-        qref = __dp4a(q & ~NM, ones, qref);
-        q1 = __dp4a(q & (s1 * 0xffu), ones, q1);
+        const uint32_t GM = sign_bytes(BQ + 0x80808080u - M7);
+        const uint32_t q = ((M7 & GM) | (BQ & ~GM)) & ~NM;                     /* reference read-bases only */
+        qref = __dp4a(q, ones, qref);
+        q1 = __dp4a(q & RV, ones, q1);
     }
-    st.m = __dp4a(acc_m, ones, 0u); st.n1 = __dp4a(acc_n1, ones, 0u);
+    st.m = acc_m / 255u; st.n1 = acc_n1 / 255u;
     st.S = S; st.qref = qref; st.q1 = q1;
 }
 

@@ -33,28 +33,31 @@ def parity():
             ok &= g and s and r
     return ok
 
-def rate(ncol=1_000_000, steps=10):
+def rate(ncol=1_000_000, steps=10, nslots=2):
     cols = synth.make_columns(ncol, seed=1234)
-    sc = api.Scorer(api.default_params(), device=0, n_slots=1, max_columns=ncol, max_entries=int(cols["n_entries"]) + 64)
-    b = sc.acquire(); b.fill(cols); sc.upload(b)
+    sc = api.Scorer(api.default_params(), device=0, n_slots=nslots, max_columns=ncol, max_entries=int(cols["n_entries"]) + 64)
+    bs = []
+    for _ in range(nslots):
+        b = sc.acquire(); b.fill(cols); sc.upload(b); bs.append(b)
     ref = None
-    for name, flags in (("full model, every column", api.SUBMIT_NO_PREFILTER), ("pre-filter + full model on survivors", 0)):
-        for _ in range(3): sc.score_resident(b, flags)
-        sc.sync(); sc.kernel_time(reset=True)
+    for name, flags, use in (("full model, every column", api.SUBMIT_NO_PREFILTER, bs[:1]), ("pre-filter + survivors, 1 stream", 0, bs[:1]),
+                             ("pre-filter + survivors, %d streams" % nslots, 0, bs)):
+        for i in range(4): sc.score_resident(use[i % len(use)], flags)
+        sc.sync(); [sc.fetch(b) for b in use]; sc.kernel_time(reset=True)
         sc.timer_start()
-        for _ in range(steps): sc.score_resident(b, flags)
+        for i in range(steps): sc.score_resident(use[i % len(use)], flags)
         ms = sc.timer_stop()
-        sites = sc.fetch(b)
+        sites = sc.fetch(use[0])
         pf, scms, nb = sc.kernel_time_split(reset=True)
         if ref is None: ref = sites
         same = sites.tobytes() == ref.tobytes()
         print("rate %-38s %.4g columns/s  (%.3f ms per 1e6-column step; pre-filter %.3f ms, scoring %.3f ms; %d sites, %d survivors, identical=%s)"
-              % (name, ncol * steps / (ms * 1e-3), ms / steps, pf / max(nb, 1), scms / max(nb, 1), len(sites), b.survivors(), same), flush=True)
+              % (name, ncol * steps / (ms * 1e-3), ms / steps, pf / max(nb, 1), scms / max(nb, 1), len(sites), use[0].survivors(), same), flush=True)
     sc.close()
 
 if __name__ == "__main__":
     ok = True
     if "--no-parity" not in sys.argv:
         ok = parity()
-    rate()
+    rate(nslots=int(os.environ.get("KCHECK_SLOTS", "2")))
     sys.exit(0 if ok else 1)
