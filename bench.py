@@ -139,6 +139,7 @@ def dist_setup(n, backend="nccl"):
     import torch.distributed as dist
     rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
     if backend == "nccl":
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     else:                                   # gloo: the CPU tests of the N>1 bookkeeping

@@ -178,11 +178,12 @@ int ssn_prefilter_enabled(const ssn_ctx *ctx);
 /* Columns of a finished batch that the pre-filter handed to the full model (0 when it did not run). */
 ssn_status ssn_batch_survivors(const ssn_batch *b, uint32_t *n_columns);
 /* Host view of the pre-filter's bound tables (parity tests re-evaluate the filter on the CPU against the oracle):
- * ab[(n*N + m)*4 + {0,1,2}] = {cmin_all, cmax_run, g2_run}, h[a*N + b], F[0..N]; see ssn_prefilter_tables.c. */
+ * ab[(n*N + m)*4 + {0,1,2}] = {cmin_all, cmax_run, g2_run}, h[a*N + b], F[0..N], vt; see ssn_prefilter_tables.c. */
 typedef struct {
     const float *ab;
     const float *h;
     const float *F;
+    const float *vt;  /* [(n*8 + m-1)*256 + s], m in 1..8, s in 0..255 */
     int32_t n;        /* N = 256 */
     int32_t enabled;
 } ssn_prefilter_view;

@@ -36,7 +36,7 @@ class Tables(C.Structure):
 class PrefilterView(C.Structure):
     """ssn_prefilter_view: the pre-filter's bound tables (ssn_prefilter_tables.c)."""
     _fields_ = [("ab", C.POINTER(C.c_float)), ("h", C.POINTER(C.c_float)), ("F", C.POINTER(C.c_float)),
-                ("n", C.c_int32), ("enabled", C.c_int32)]
+                ("vt", C.POINTER(C.c_float)), ("n", C.c_int32), ("enabled", C.c_int32)]
 
 
 class BatchView(C.Structure):
@@ -148,7 +148,7 @@ def host_tables(params=None):
 
 def host_prefilter_tables(params=None):
     """The pre-filter's bound tables built by the product's host code (no device needed):
-    dict(ab float32[N,N,4], h float32[N,N], F float32[N+1], enabled bool)."""
+    dict(ab float32[N,N,4], h float32[N,N], F float32[N+1], vt float32[N,8,256], enabled bool)."""
     lib = load_library()
     p = params or default_params()
     v, h = PrefilterView(), _VP()
@@ -157,7 +157,7 @@ def host_prefilter_tables(params=None):
         n = int(v.n)
         arr = np.ctypeslib.as_array
         return dict(ab=arr(v.ab, shape=(n, n, 4)).copy(), h=arr(v.h, shape=(n, n)).copy(),
-                    F=arr(v.F, shape=(n + 1,)).copy(), enabled=bool(v.enabled))
+                    F=arr(v.F, shape=(n + 1,)).copy(), vt=arr(v.vt, shape=(n, 8, 256)).copy(), enabled=bool(v.enabled))
     finally:
         lib.ssn_host_prefilter_destroy(h)
 

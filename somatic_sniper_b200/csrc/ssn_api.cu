@@ -104,7 +104,7 @@ struct ssn_ctx {
     size_t l2_window_bytes;
     /* exact hom-reference pre-filter (ssn_prefilter.cuh) */
     ssn_prefilter_tables pf;
-    float *d_pf_ab, *d_pf_h, *d_pf_F;
+    float *d_pf_ab, *d_pf_h, *d_pf_F, *d_pf_vt;
     DevPrefilter dpf;
     bool pf_on;
     double survivor_frac;     /* survivors / columns of the last collected batch: sizes the list-mode grid */
@@ -207,7 +207,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
     ctx->d_scratch = nullptr; ctx->scratch_words = 0; ctx->grid_cap = 0; ctx->d_flush = nullptr; ctx->flush_bytes = 0;
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
-    ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = nullptr; ctx->pf_on = false;
+    ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = ctx->d_pf_vt = nullptr; ctx->pf_on = false;
     memset(&ctx->pf, 0, sizeof(ctx->pf));
     ctx->survivor_frac = 1.0;
     const char *env = getenv("SSN_SMEM_WORDS");
@@ -243,7 +243,9 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     CU(cudaMemcpy(ctx->d_pf_h, ctx->pf.h, sizeof(float) * SSN_PF_N * SSN_PF_N, cudaMemcpyHostToDevice));
     CU(cudaMalloc(&ctx->d_pf_F, sizeof(float) * (SSN_PF_N + 1)));
     CU(cudaMemcpy(ctx->d_pf_F, ctx->pf.F, sizeof(float) * (SSN_PF_N + 1), cudaMemcpyHostToDevice));
-    ctx->dpf.ab = reinterpret_cast<const float4*>(ctx->d_pf_ab); ctx->dpf.h = ctx->d_pf_h; ctx->dpf.F = ctx->d_pf_F;
+    CU(cudaMalloc(&ctx->d_pf_vt, sizeof(float) * SSN_PF_N * SSN_PF_VK * SSN_PF_VS));
+    CU(cudaMemcpy(ctx->d_pf_vt, ctx->pf.vt, sizeof(float) * SSN_PF_N * SSN_PF_VK * SSN_PF_VS, cudaMemcpyHostToDevice));
+    ctx->dpf.ab = reinterpret_cast<const float4*>(ctx->d_pf_ab); ctx->dpf.h = ctx->d_pf_h; ctx->dpf.F = ctx->d_pf_F; ctx->dpf.vt = ctx->d_pf_vt;
     SSN_TRACE("table upload");
     CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&ctx->t0));
@@ -301,7 +303,7 @@ extern "C" void ssn_destroy(ssn_ctx *ctx)
     cudaDeviceSynchronize();
     for (ssn_batch *b : ctx->slots) slot_free(b);
     for (auto &t : ctx->timers) { if (t.a) cudaEventDestroy(t.a); if (t.m) cudaEventDestroy(t.m); if (t.b) cudaEventDestroy(t.b); }
-    cudaFree(ctx->d_pf_ab); cudaFree(ctx->d_pf_h); cudaFree(ctx->d_pf_F);
+    cudaFree(ctx->d_pf_ab); cudaFree(ctx->d_pf_h); cudaFree(ctx->d_pf_F); cudaFree(ctx->d_pf_vt);
     ssn_prefilter_free(&ctx->pf);
     cudaFree(ctx->d_coef_lhet); cudaFree(ctx->d_fk); cudaFree(ctx->d_prior); cudaFree(ctx->d_jointprior);
     cudaFree(ctx->d_qadd); cudaFree(ctx->d_scratch); cudaFree(ctx->d_flush);
@@ -511,7 +513,10 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     kt.filtered = filter;
     if (filter) {
         const uint32_t pf_need = (ntiles + kPfWarps - 1) / kPfWarps;
-        const uint32_t pf_grid = std::min<uint32_t>((uint32_t)ctx->num_sms, pf_need);
+        /* leave the SMs the survivors' kernel of the previous batch (another slot stream) needs, so the two overlap */
+        uint32_t pf_sms = (uint32_t)ctx->num_sms;
+        if (listed && grid <= pf_sms / 4u) pf_sms -= grid;
+        const uint32_t pf_grid = std::min<uint32_t>(pf_sms, pf_need);
         ssn_prefilter_kernel<<<pf_grid, kPfWarps * 32, pf_smem_bytes(), b->stream>>>(
             ctx->dpf, B, b->d_survivors, b->d_count, dump ? b->d_dump + (SSN_COLUMN_DUMP_WORDS - 1) : nullptr, SSN_COLUMN_DUMP_WORDS);
         CU(cudaGetLastError());
@@ -740,7 +745,7 @@ extern "C" ssn_status ssn_host_prefilter_create(const ssn_params *p, ssn_prefilt
     const int rc = ssn_prefilter_build(&m, (int)(m.q_r + 0.5), t);
     ssn_tables_free(&m);
     if (rc != 0) { delete t; ssn_set_error("out of memory"); return SSN_ERR_NOMEM; }
-    view->ab = t->ab; view->h = t->h; view->F = t->F; view->n = SSN_PF_N; view->enabled = t->enabled;
+    view->ab = t->ab; view->h = t->h; view->F = t->F; view->vt = t->vt; view->n = SSN_PF_N; view->enabled = t->enabled;
     *handle = t;
     return SSN_OK;
 }

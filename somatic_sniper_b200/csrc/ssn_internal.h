@@ -24,9 +24,12 @@ int ssn_tables_build(const ssn_params *p, ssn_host_tables *t);
 
 /* bound tables of the exact hom-reference pre-filter (ssn_prefilter_tables.c) */
 #define SSN_PF_N 256
+#define SSN_PF_VK 8
+#define SSN_PF_VS 256
 typedef struct {
     float *ab;                  /* [n][m][4] = { cmin_all, cmax_run, g2_run, 0 } */
     float *h;                   /* [a][b] */
+    float *vt;                  /* [n][k-1][s], k in 1..SSN_PF_VK, s in 0..SSN_PF_VS-1: upper bound of p[RR] given SU <= s */
     float F[SSN_PF_N + 1];      /* F[k] = (1 - 1e-4) * sum_{w<k} fk[w], rounded down */
     int enabled;                /* 0: the parameter set breaks a precondition of the proof */
 } ssn_prefilter_tables;

@@ -18,7 +18,7 @@
  * and evaluates (tables: ssn_prefilter_tables.c)
  *   t1 = F[n1] * Q1 / (n1 + m) + F[n0] * Q0 / (n0 + m)            lower bound of the reference base's esum chain
  *   SU = (S + 3 m) (1 + 1e-4)                                      upper bound of the other bases' esum chains
- *   U  = max(SU + cmax_run[n][m], 0) + 1.1                         upper bound of p[RR], plus the margin RR must win by
+ *   U  = max(min(SU + cmax_run[n][m], vt[n][m][ceil SU]), 0) + 1.1 upper bound of p[RR], plus the margin RR must win by
  *   keep scoring unless  t1 > SU  and  t1 + cmin_all[n][m] >= U  and  h[n-m][m] + g2_run[n][m] >= U   (both samples)
  */
 #pragma once
@@ -36,6 +36,7 @@ struct DevPrefilter {
     const float4 *ab;     /* [n*256 + m] = { cmin_all, cmax_run, g2_run, 0 } */
     const float *h;       /* [(n-m)*256 + m] */
     const float *F;       /* 257 */
+    const float *vt;      /* [(n*8 + m-1)*256 + ceil(SU)]: tighter upper bound of p[RR] for m <= 8, SU <= 255 */
 };
 
 struct PfShared {
@@ -97,7 +98,9 @@ __device__ __forceinline__ bool pf_eval(const DevPrefilter &P, const float *F, u
     const float hs = __ldg(P.h + (n - m) * 256u + m);
     const float t1 = __fdividef(F[n1] * (float)st.q1, (float)max(n1 + m, 1u)) + __fdividef(F[n0] * (float)(st.qref - st.q1), (float)max(n0 + m, 1u));
     const float SU = (float)(st.S + 3u * m) * 1.0001f;
-    const float U = fmaxf(SU + ab.y, 0.0f) + 1.1f;
+    float U = fmaxf(SU + ab.y, 0.0f) + 1.1f;
+    if (m - 1u < 8u && SU <= 255.0f)                                       /* few other read-bases: the tabulated bound is tighter */
+        U = fminf(U, __ldg(P.vt + ((n * 8u + m - 1u) << 8) + (uint32_t)__float2int_ru(SU)) + 1.1f);
     return t1 > SU && t1 + ab.x >= U && hs + ab.z >= U;
 }
 

@@ -18,6 +18,9 @@
  *     g2_run   = min(0, min_{1 <= k <= m} min_e ((e - 0.5) * F[k] + coef[e][n][k]))    (p[RX] >= h + g2_run)
  *   h[a][b]  = min_{a' >= a, b' <= b, a'+b' <= 255} -4.343 * max(lhet[a'][b'], lhet[b'][a'])
  *   F[k]     = (1 - 1e-4) * sum_{w < k} fk[w]
+ *   vt[n][m][s] = max_{1 <= k <= m} max_e ( min(s, (e + 0.5) k (1 + 1e-4)) + coef[e][n][k] )   for m <= 8, s < 256:
+ *              a tighter upper bound of p[RR] than SU + cmax_run when the m other read-bases' qualities sum to SU <= s
+ *              (esum <= SU, and esum <= (bar_e + 0.5) * fsum <= (bar_e + 0.5) * k because bar_e = round(esum / fsum))
  * Lower bounds are rounded down to float, upper bounds up.
  */
 #include "ssn_internal.h"
@@ -32,8 +35,8 @@ static float f_up(double x) { float f = (float)x; return (double)f < x ? nextaft
 
 void ssn_prefilter_free(ssn_prefilter_tables *t)
 {
-    free(t->ab); free(t->h);
-    t->ab = t->h = 0; t->enabled = 0;
+    free(t->ab); free(t->h); free(t->vt);
+    t->ab = t->h = t->vt = 0; t->enabled = 0;
 }
 
 int ssn_prefilter_build(const ssn_host_tables *m, int q_r_int, ssn_prefilter_tables *t)
@@ -45,11 +48,12 @@ int ssn_prefilter_build(const ssn_host_tables *m, int q_r_int, ssn_prefilter_tab
     memset(t, 0, sizeof(*t));
     t->ab = (float*)calloc((size_t)N * N * 4, sizeof(float));
     t->h = (float*)calloc((size_t)N * N, sizeof(float));
+    t->vt = (float*)calloc((size_t)N * SSN_PF_VK * SSN_PF_VS, sizeof(float));
     cmin = (double*)malloc(sizeof(double) * N * N);
     cmax = (double*)malloc(sizeof(double) * N * N);
     g2 = (double*)malloc(sizeof(double) * N * N);
     hh = (double*)malloc(sizeof(double) * N * N);
-    if (!t->ab || !t->h || !cmin || !cmax || !g2 || !hh) { free(cmin); free(cmax); free(g2); free(hh); ssn_prefilter_free(t); return -1; }
+    if (!t->ab || !t->h || !t->vt || !cmin || !cmax || !g2 || !hh) { free(cmin); free(cmax); free(g2); free(hh); ssn_prefilter_free(t); return -1; }
 
     /* preconditions of the proof: dependency weights in (0,1], non-increasing, fk[0] = 1; lhet <= 0; a positive
      * heterozygote penalty.  Parameter sets that break one of them simply run without the pre-filter. */
@@ -90,6 +94,24 @@ int ssn_prefilter_build(const ssn_host_tables *m, int q_r_int, ssn_prefilter_tab
             for (k = n - b < 1 ? 1 : n - b; k <= n; ++k)
                 if (cmin[n * N + k] < all) all = cmin[n * N + k];
             dst[0] = f_down(all); dst[1] = f_up(run_max); dst[2] = f_down(run_g2); dst[3] = 0.0f;
+        }
+    }
+    for (n = 1; n < N; ++n) {
+        double run[SSN_PF_VS];
+        for (k = 0; k < SSN_PF_VS; ++k) run[k] = -DBL_MAX;
+        for (k = 1; k <= SSN_PF_VK; ++k) {
+            float *dst = t->vt + ((size_t)n * SSN_PF_VK + (k - 1)) * SSN_PF_VS;
+            if (k <= n) {
+                for (e = 4; e < 64; ++e) {
+                    const double c = m->coef[(size_t)e << 16 | (size_t)n << 8 | (size_t)k];
+                    const double cap = ((double)e + 0.5) * (double)k * (1.0 + 1e-4);
+                    for (b = 0; b < SSN_PF_VS; ++b) {
+                        const double v = ((double)b < cap ? (double)b : cap) + c;
+                        if (v > run[b]) run[b] = v;
+                    }
+                }
+            }
+            for (b = 0; b < SSN_PF_VS; ++b) dst[b] = f_up(run[b] > 0.0 ? run[b] : 0.0);
         }
     }
     /* h: closed under a' >= a, b' <= b inside a+b <= 255 */

@@ -38,6 +38,9 @@ def decide(cols, tables=None, tile_rules=True):
     t1 = F[np.minimum(n1, 256)] * q1 / np.maximum(n1 + m, 1) + F[np.minimum(n0, 256)] * q0 / np.maximum(n0 + m, 1)
     SU = (S + 3 * m) * 1.0001
     U = np.maximum(SU + ab[nn, mm, 1], 0.0) + 1.1
+    tight = (m >= 1) & (m <= 8) & (SU <= 255.0)
+    vt = t["vt"].astype(np.float64)
+    U = np.where(tight, np.minimum(U, vt[nn, np.clip(m, 1, 8) - 1, np.minimum(np.ceil(SU), 255).astype(np.int64)] + 1.1), U)
     hs = h[np.minimum(n - m, 255), mm]
     sample_ok = ok & (t1 > SU) & (t1 + ab[nn, mm, 0] >= U) & (hs + ab[nn, mm, 2] >= U)
     nT, nN = n[0::2], n[1::2]

@@ -114,6 +114,19 @@ def test_tables_are_closed_and_conservative():
             assert ab[n, mm, 0] <= min(0.0, coef[4:64, n, ks].min()) + 1e-4
             if mm:
                 assert ab[n, mm, 1] >= coef[4:64, n, 1:mm + 1].max() - 1e-4
+    # vt: upper bound of p[RR] = esum + coef[e][n][k] for every (e, k <= m) with esum <= min(s, (e + 0.5) k)
+    vt = t["vt"]
+    for n in (5, 22, 30, 90, 200):
+        for mm in (1, 2, 5, 8):
+            if mm > n:
+                continue
+            assert np.all(np.diff(vt[n, mm - 1]) >= 0)                      # monotone in the quality sum
+            if mm > 1:
+                assert np.all(vt[n, mm - 1] >= vt[n, mm - 2])                # and in m
+            for sv in (0, 4, 37, 80, 255):
+                for k in range(1, mm + 1):
+                    for e in (4, 20, 37, 63):
+                        assert vt[n, mm - 1, sv] >= min(sv, (e + 0.5) * k) + coef[e, n, k] - 1e-3
     lhet = m["lhet"].reshape(256, 256)
     for a, b in ((30, 0), (29, 1), (88, 2), (5, 5), (200, 55)):
         assert h[a, b] <= -4.343 * max(lhet[a, b], lhet[b, a]) + 1e-3
