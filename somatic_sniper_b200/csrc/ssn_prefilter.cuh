@@ -122,38 +122,67 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
     const uint32_t ntiles = (B.ncol + 31u) >> 5;
     uint32_t phase = 0;
 
-    for (;;) {
-        uint32_t tile = 0;
-        if (lane == 0) tile = atomicAdd(counters + 3, 1u);
-        tile = __shfl_sync(kFull, tile, 0);
-        if (tile >= ntiles) break;
+    /* software pipeline over tiles: the tile index for the tile after next is being claimed (atomic in flight) and the
+     * next tile's offsets are being loaded while the current tile is staged and evaluated */
+    struct Hdr { uint32_t o0, o1, o2, ref16; };
+    auto load_hdr = [&](uint32_t t, Hdr &h) {
+        const uint32_t c = t * 32u + lane;
+        h.o0 = h.o1 = h.o2 = 0u; h.ref16 = 15u;
+        if (t < ntiles && c < B.ncol) {
+            h.o0 = B.off[2 * c]; h.o1 = B.off[2 * c + 1]; h.o2 = B.off[2 * c + 2];
+            h.ref16 = B.ref_nt16[c] & 15u;
+        }
+    };
+    uint32_t tile = 0, claim = 0;
+    if (lane == 0) tile = atomicAdd(counters + 3, 1u);
+    tile = __shfl_sync(kFull, tile, 0);
+    Hdr cur;
+    load_hdr(tile, cur);
+    if (lane == 0) claim = atomicAdd(counters + 3, 1u);
+
+    while (tile < ntiles) {
         const uint32_t col = tile * 32u + lane;
         const bool live = col < B.ncol;
-        uint32_t o0 = 0, o1 = 0, o2 = 0, ref16 = 15;
-        if (live) {
-            o0 = B.off[2 * col]; o1 = B.off[2 * col + 1]; o2 = B.off[2 * col + 2];
-            ref16 = B.ref_nt16[col] & 15u;
-        }
+        const uint32_t o0 = cur.o0, o1 = cur.o1, o2 = cur.o2, ref16 = cur.ref16;
         const uint32_t nT = o1 - o0, nN = o2 - o1;
         /* a column can only reach the output with read-bases in both samples and a called reference (somatic_sniper.c:127,156) */
         const bool wanted = live && nT != 0u && nN != 0u && ref16 != 15u;
-        const uint32_t maxT = __reduce_max_sync(kFull, nT), maxN = __reduce_max_sync(kFull, nN);
-        const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
-        const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
+        const bool cand = wanted && nT <= 255u && nN <= 255u && __popc(ref16) == 1;   /* the bound tables cover n <= 255 */
         bool drop = false;
         __syncwarp();
-        if (__any_sync(kFull, wanted) && maxT <= 255u && maxN <= 255u && bytes <= (uint32_t)kRawBytes) {
-            if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
-            stage_wait(mbar_s, phase);
-            phase ^= 1u;
-            if (tile_is_clean(raw_s, bytes, lane)) {
-                const uint32_t r0 = live ? o0 - a0 : 0u;
-                const uint32_t R4 = ref16 * 0x01010101u;
-                PfStats sT, sN;
-                pf_sample(raw_s, r0, nT, (int)((maxT + 3u) >> 2), R4, sT);
-                pf_sample(raw_s, r0 + nT, nN, (int)((maxN + 3u) >> 2), R4, sN);
-                drop = wanted && __popc(ref16) == 1 && pf_eval(P, T.F, nT, sT) && pf_eval(P, T.F, nN, sN);
+        const uint32_t next_tile = __shfl_sync(kFull, claim, 0);      /* claimed one iteration ago */
+        Hdr nxt;
+        load_hdr(next_tile, nxt);
+        if (lane == 0) claim = atomicAdd(counters + 3, 1u);
+        /* The tile is staged in passes of consecutive columns whose read-bases fit the staging area: one pass at WGS
+         * 30x/60x, two or three at 100x; the lanes outside the current pass idle. */
+        uint32_t first = 0;
+        while (__any_sync(kFull, cand && (uint32_t)lane >= first)) {
+            const uint32_t a0 = __shfl_sync(kFull, o0, (int)first) & ~15u;
+            const bool fits = (uint32_t)lane >= first && live && o2 - a0 <= (uint32_t)kRawBytes - 16u;
+            const uint32_t run = ~(__ballot_sync(kFull, fits) >> first);            /* offsets rise with the lane: a prefix fits */
+            const uint32_t cnt = run ? (uint32_t)__ffs((int)run) - 1u : 32u - first;
+            if (cnt == 0u) { ++first; continue; }                                   /* one column deeper than the staging area */
+            const uint32_t last = first + cnt;
+            const bool mine = cand && (uint32_t)lane >= first && (uint32_t)lane < last;
+            if (__any_sync(kFull, mine)) {
+                const uint32_t bytes = (__shfl_sync(kFull, o2, (int)last - 1) - a0 + 15u) & ~15u;
+                if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
+                const uint32_t lT = mine ? nT : 0u, lN = mine ? nN : 0u;
+                const uint32_t maxT = __reduce_max_sync(kFull, lT), maxN = __reduce_max_sync(kFull, lN);
+                stage_wait(mbar_s, phase);
+                phase ^= 1u;
+                if (tile_is_clean(raw_s, bytes, lane)) {
+                    const uint32_t r0 = mine ? o0 - a0 : 0u;
+                    const uint32_t R4 = ref16 * 0x01010101u;
+                    PfStats sT, sN;
+                    pf_sample(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
+                    pf_sample(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
+                    if (mine) drop = pf_eval(P, T.F, nT, sT) && pf_eval(P, T.F, nN, sN);
+                }
+                __syncwarp();                       /* every lane is done with the staged bytes before the next pass overwrites them */
             }
+            first = last;
         }
         const bool survive = wanted && !drop;
         const uint32_t mask = __ballot_sync(kFull, survive);
@@ -164,6 +193,7 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
             if (survive) survivors[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = col;
         }
         if (decision && live) decision[(size_t)col * decision_stride] = drop ? 1u : 0u;
+        tile = next_tile; cur = nxt;
     }
 }
 

@@ -52,10 +52,8 @@ def decide(cols, tables=None, tile_rules=True):
         tile = np.arange(ncol) >> 5
         pad = ntile * 32 - ncol
         tile_bad = np.bincount(tile, bad_bq, ntile) > 0
-        tmax = lambda v: np.pad(v, (0, pad)).reshape(ntile, 32).max(1)
-        first = off[0:2 * ncol:64] & ~15
-        last = off[np.minimum(np.arange(1, ntile + 1) * 64, 2 * ncol)]
-        tile_bad |= (tmax(nT) > 255) | (tmax(nN) > 255) | (((last - first + 15) & ~15) > RAW_BYTES)
+        # (tiles deeper than the staging area are staged in several passes of consecutive columns; the clean check
+        # is then per pass, i.e. the kernel may drop columns of a tile this restatement gives up on)
         # slack bytes of the neighbouring tiles are scanned too (conservative in the kernel); ignore that here
         drop &= ~tile_bad[tile]
     return drop

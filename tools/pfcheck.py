@@ -2,7 +2,8 @@ import sys, numpy as np
 sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/tests')
 from somatic_sniper_b200 import api, synth
 import prefilter_np
-for name, kw in (("wgs", dict(ncol=300000, seed=41)), ("edge", dict(ncol=100000, seed=43, edge=0.5, p_som=5e-3)), ("shallow", dict(ncol=100000, depth_t=12, depth_n=6, seed=44, edge=0.1))):
+for name, kw in (("wgs", dict(ncol=300000, seed=41)), ("edge", dict(ncol=100000, seed=43, edge=0.5, p_som=5e-3)), ("shallow", dict(ncol=100000, depth_t=12, depth_n=6, seed=44, edge=0.1)), ("wgs100x", dict(ncol=100000, depth_t=110, depth_n=100, seed=46, binned=False)),
+                 ("ragged", dict(ncol=100000, depth_t=150, depth_n=20, seed=49, edge=0.0, min_depth=0))):
     n = kw.pop("ncol"); cols = synth.make_columns(n, **kw)
     sc = api.Scorer(api.default_params(), device=0, n_slots=1, max_columns=n, max_entries=int(cols["n_entries"]) + 64)
     _, dump = sc.score(cols, dump=True)
