@@ -139,7 +139,6 @@ def dist_setup(n, backend="nccl"):
     import torch.distributed as dist
     rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
     if backend == "nccl":
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     else:                                   # gloo: the CPU tests of the N>1 bookkeeping
@@ -258,7 +257,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -429,12 +428,20 @@ def run_b200(args):
         line["e2e"] = e2e
     if args.gpus == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_single(cols, args.cpu_sample)
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
 
+_JSON_OUT = sys.stdout
+
+
 def main():
+    # stdout carries exactly one JSON line: libraries that write to fd 1 (NCCL prints its version there) go to stderr
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
