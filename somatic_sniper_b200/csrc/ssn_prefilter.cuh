@@ -12,7 +12,7 @@
  * full model's output so tests can audit it.
  *
  * Per sample the filter needs (all from one pass over bs/bq/mq):
- *   n      read-bases                         m   read-bases whose nt16 code differs from the reference's
+ *   n      read-bases with a non-zero quality m   of those, the ones whose nt16 code differs from the reference's
  *   S      sum over those m of base quality    n1  reference read-bases on the reverse strand
  *   Q1,Q0  sum of min(baseQ, mapQ & 0x7f) over the reference read-bases of the reverse / forward strand
  * and evaluates (tables: ssn_prefilter_tables.c)
@@ -52,22 +52,43 @@ __device__ __forceinline__ uint32_t sign_bytes(uint32_t x)
     return r;
 }
 
-struct PfStats { uint32_t m, S, n1, qref, q1; };
+struct PfStats { uint32_t m, S, n1, qref, q1, z; };
+
+/* What the staged base qualities of a pass look like: 0 = all in [1,63]; 1 = some are 0 (those read-bases contribute
+ * nothing to the model, sniper_maqcns.c:165-167: the filter ignores them and lowers n); 2 = some are >= 64 (baseQ 64/128/
+ * 192 keep q < 4 unpromoted, :165): not filtered.  Slack bytes of the neighbouring tiles only make the answer conservative. */
+__device__ __forceinline__ int pass_quality_class(uint32_t raw_s, uint32_t bytes, int lane)
+{
+    uint32_t hi = 0, zero = 0;
+    for (uint32_t i = (uint32_t)lane * 16u; i < bytes; i += 512u) {
+        const uint4 w = lds_u32x4(raw_s + (uint32_t)kRawBytes + i);
+        hi |= (w.x | w.y | w.z | w.w) & 0xc0c0c0c0u;
+        zero |= ((w.x - 0x01010101u) & ~w.x) | ((w.y - 0x01010101u) & ~w.y) | ((w.z - 0x01010101u) & ~w.z) | ((w.w - 0x01010101u) & ~w.w);
+    }
+    if (__any_sync(kFull, hi != 0u)) return 2;
+    return __any_sync(kFull, (zero & 0x80808080u) != 0u) ? 1 : 0;
+}
 
 /* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.
  * C = tile-uniform number of 4-read-base chunks; R4 = the reference's nt16 code in every byte. */
+template <bool ZEROS>
 __device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, int C, uint32_t R4, PfStats &st)
 {
     const uint32_t a = raw_s + (r & ~3u), sh = (r & 3u) * 8u;
     uint32_t ws = lds_u32(a), wq = lds_u32(a + kRawBytes), wm = lds_u32(a + 2 * kRawBytes);
     uint32_t bits = len * 8u;                      /* live bits left in this sample */
-    uint32_t acc_m = 0, acc_n1 = 0, S = 0, qref = 0, q1 = 0;
+    uint32_t acc_m = 0, acc_n1 = 0, S = 0, qref = 0, q1 = 0, acc_z = 0;
     const uint32_t ones = 0x01010101u;
 #pragma unroll 2
     for (int c = 0; c < C; ++c) {
         const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
-        const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);          /* low min(bits,32) bits */
+        uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);                /* low min(bits,32) bits */
         bits = max(bits, 32u) - 32u;
+        if (ZEROS) {                                                            /* quality-0 read-bases: dead bytes, counted */
+            const uint32_t nzq = sign_bytes(__funnelshift_r(wq, nq, sh) + 0x7f7f7f7fu);   /* every quality is < 64 here */
+            acc_z = __dp4a(keep & ~nzq, ones, acc_z);
+            keep &= nzq;
+        }
         /* dead bytes become "reference base, forward strand, quality 0": they add nothing to any sum */
         const uint32_t BS = (__funnelshift_r(ws, ns, sh) & keep) | (R4 & ~keep);
         const uint32_t BQ = __funnelshift_r(wq, nq, sh) & keep;
@@ -86,7 +107,7 @@ __device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t l
         qref = __dp4a(q, ones, qref);
         q1 = __dp4a(q & RV, ones, q1);
     }
-    st.m = acc_m / 255u; st.n1 = acc_n1 / 255u;
+    st.m = acc_m / 255u; st.n1 = acc_n1 / 255u; st.z = acc_z / 255u;
     st.S = S; st.qref = qref; st.q1 = q1;
 }
 
@@ -172,13 +193,19 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
                 const uint32_t maxT = __reduce_max_sync(kFull, lT), maxN = __reduce_max_sync(kFull, lN);
                 stage_wait(mbar_s, phase);
                 phase ^= 1u;
-                if (tile_is_clean(raw_s, bytes, lane)) {
+                const int qc = pass_quality_class(raw_s, bytes, lane);
+                if (qc < 2) {
                     const uint32_t r0 = mine ? o0 - a0 : 0u;
                     const uint32_t R4 = ref16 * 0x01010101u;
                     PfStats sT, sN;
-                    pf_sample(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
-                    pf_sample(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
-                    if (mine) drop = pf_eval(P, T.F, nT, sT) && pf_eval(P, T.F, nN, sN);
+                    if (qc == 0) {
+                        pf_sample<false>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
+                        pf_sample<false>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
+                    } else {
+                        pf_sample<true>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
+                        pf_sample<true>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
+                    }
+                    if (mine) drop = pf_eval(P, T.F, nT - sT.z, sT) && pf_eval(P, T.F, nN - sN.z, sN);
                 }
                 __syncwarp();                       /* every lane is done with the staged bytes before the next pass overwrites them */
             }

@@ -20,20 +20,22 @@ def decide(cols, tables=None, tile_rules=True):
     off = cols["off"].astype(np.int64)
     bs, bq, mq = cols["bs"], cols["bq"].astype(np.int64), cols["mq"].astype(np.int64)
     ref16 = api.nt16_lut()[cols["ref_char"]].astype(np.int64)
-    n = np.diff(off)
-    seg = np.repeat(np.arange(2 * ncol), n)
+    n_all = np.diff(off)
+    seg = np.repeat(np.arange(2 * ncol), n_all)
     col = seg >> 1
-    nonref = (bs & 15) != ref16[col]
+    live = bq != 0                      # quality-0 read-bases contribute nothing to the model (sniper_maqcns.c:165-167)
+    n = np.bincount(seg, live, 2 * ncol).astype(np.int64)
+    nonref = ((bs & 15) != ref16[col]) & live
     rev = ((bs >> 4) & 1) == 1
     q = np.minimum(bq, mq & 0x7f)
     cnt = lambda w: np.bincount(seg, w, 2 * ncol)
     m = cnt(nonref).astype(np.int64)
     S = cnt(nonref * bq)
-    n1 = cnt(~nonref & rev).astype(np.int64)
-    q1 = cnt((~nonref & rev) * q)
-    q0 = cnt((~nonref & ~rev) * q)
+    n1 = cnt(~nonref & rev & live).astype(np.int64)
+    q1 = cnt((~nonref & rev & live) * q)
+    q0 = cnt((~nonref & ~rev & live) * q)
     n0 = n - m - n1
-    ok = n <= 255
+    ok = n_all <= 255
     nn, mm = np.minimum(n, 255), np.minimum(m, 255)
     t1 = F[np.minimum(n1, 256)] * q1 / np.maximum(n1 + m, 1) + F[np.minimum(n0, 256)] * q0 / np.maximum(n0 + m, 1)
     SU = (S + 3 * m) * 1.0001
@@ -43,11 +45,11 @@ def decide(cols, tables=None, tile_rules=True):
     U = np.where(tight, np.minimum(U, vt[nn, np.clip(m, 1, 8) - 1, np.minimum(np.ceil(SU), 255).astype(np.int64)] + 1.1), U)
     hs = h[np.minimum(n - m, 255), mm]
     sample_ok = ok & (t1 > SU) & (t1 + ab[nn, mm, 0] >= U) & (hs + ab[nn, mm, 2] >= U)
-    nT, nN = n[0::2], n[1::2]
+    nT, nN = n_all[0::2], n_all[1::2]
     wanted = (nT > 0) & (nN > 0) & (ref16 != 15)
     drop = wanted & np.isin(ref16, [1, 2, 4, 8]) & sample_ok[0::2] & sample_ok[1::2]
     if tile_rules:
-        bad_bq = np.bincount(col, (bq < 1) | (bq > 63), ncol) > 0
+        bad_bq = np.bincount(col, bq > 63, ncol) > 0
         ntile = (ncol + 31) // 32
         tile = np.arange(ncol) >> 5
         pad = ntile * 32 - ncol

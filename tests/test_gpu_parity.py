@@ -217,6 +217,7 @@ PF_CASES = [
     ("variant rich", dict(ncol=100000, seed=47, p_het=0.05, p_hom=0.02, p_som=0.05, p_loh=0.01, p_gor=0.01)),
     ("deep", dict(ncol=400, depth_t=1500, depth_n=900, seed=48)),
     ("ragged", dict(ncol=100000, depth_t=150, depth_n=20, seed=49, min_depth=0)),   # several staging passes per tile, empty samples
+    ("q0", dict(ncol=100000, seed=50)),                                              # quality-0 read-bases (N calls of real BAMs)
 ]
 
 
@@ -230,6 +231,10 @@ def test_prefilter_audit_and_identical_sites(mods, name, kw):
     kw = dict(kw)
     n = kw.pop("ncol")
     cols = synth.make_columns(n, **kw)
+    if name == "q0":
+        rng = np.random.default_rng(3)
+        zero = ((cols["bs"] & 15) == 15) | (rng.random(len(cols["bq"])) < 2e-3)
+        cols["bq"] = np.where(zero, 0, cols["bq"]).astype(np.uint8)
     ent = int(cols["n_entries"]) + 64
     for joint in (0, 1):
         prm = api.default_params(use_joint_priors=joint, min_somatic_qual=0 if joint else 15)
@@ -255,9 +260,9 @@ def test_prefilter_audit_and_identical_sites(mods, name, kw):
             # float rounding (device: fp32 + MUFU.RCP, numpy: fp64) may flip columns that sit exactly on a bound
             # (the kernel's clean-tile check also sees the neighbouring tiles' alignment bytes, so only compare where every
             # base quality is legal)
-            if name in ("wgs", "unbinned", "very shallow", "mid", "variant rich", "deep", "ragged"):
+            if name in ("wgs", "unbinned", "very shallow", "mid", "variant rich", "deep", "ragged", "q0"):
                 assert int((dropped ^ want).sum()) <= 3, (dropped.sum(), want.sum())
-            if name in ("wgs", "unbinned", "mid", "ragged"):
+            if name in ("wgs", "unbinned", "mid", "ragged", "q0"):
                 assert dropped.mean() > 0.95
 
 

@@ -60,7 +60,7 @@ def _adversarial(seed, ncol=6000):
             alt = acgt[(acgt.index(ref) + int(rng.integers(1, 4))) & 3]
             e = []
             for i in range(n):
-                if qmode == 0: bq = int(rng.choice([2, 12, 23, 37]))
+                if qmode == 0: bq = int(rng.choice([2, 12, 23, 37, 0]))
                 elif qmode == 1: bq = int(rng.integers(1, 8))
                 elif qmode == 2: bq = int(rng.integers(1, 64))
                 elif qmode == 3: bq = 40
