@@ -108,6 +108,7 @@ struct ssn_ctx {
     DevPrefilter dpf;
     bool pf_on;
     double survivor_frac;     /* survivors / columns of the last collected batch: sizes the list-mode grid */
+    int last_slot;            /* slot of the previous launch: another slot's survivors' kernel may still be running */
 };
 
 extern "C" ssn_status ssn_params_default(ssn_params *p)
@@ -209,7 +210,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
     ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = ctx->d_pf_vt = nullptr; ctx->pf_on = false;
     memset(&ctx->pf, 0, sizeof(ctx->pf));
-    ctx->survivor_frac = 1.0;
+    ctx->survivor_frac = 1.0; ctx->last_slot = -1;
     const char *env = getenv("SSN_SMEM_WORDS");
     ctx->smem_words_default = env ? (uint32_t)atoi(env) : (uint32_t)kFastWords * 32u;
     ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
@@ -515,7 +516,8 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
         const uint32_t pf_need = (ntiles + kPfWarps - 1) / kPfWarps;
         /* leave the SMs the survivors' kernel of the previous batch (another slot stream) needs, so the two overlap */
         uint32_t pf_sms = (uint32_t)ctx->num_sms;
-        if (listed && grid <= pf_sms / 4u) pf_sms -= grid;
+        if (listed && grid <= pf_sms / 4u && ctx->last_slot >= 0 && ctx->last_slot != b->index) pf_sms -= grid;
+        ctx->last_slot = b->index;
         const uint32_t pf_grid = std::min<uint32_t>(pf_sms, pf_need);
         ssn_prefilter_kernel<<<pf_grid, kPfWarps * 32, pf_smem_bytes(), b->stream>>>(
             ctx->dpf, B, b->d_survivors, b->d_count, dump ? b->d_dump + (SSN_COLUMN_DUMP_WORDS - 1) : nullptr, SSN_COLUMN_DUMP_WORDS);
