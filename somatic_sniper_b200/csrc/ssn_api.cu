@@ -475,13 +475,19 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     uint32_t grid = (uint32_t)(ctx->num_sms * per_sm);
     const uint32_t need_ctas = (ntiles + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > need_ctas && !listed) grid = need_ctas;
+    uint32_t list_width = 0;
     if (listed) {
         /* The survivor count is only known on the device.  Size the grid from the last collected batch (x1.5, 16-column
          * tiles, one tile per warp) so that the SMs it does not need stay free for the next batch's pre-filter kernel on
          * another stream; the persistent tile loop keeps any estimate correct. */
         static const int tiles_per_warp = getenv("SSN_LIST_TPW") ? std::max(1, atoi(getenv("SSN_LIST_TPW"))) : 1;
         const double est = std::min(1.0, ctx->survivor_frac * 1.25) * (double)b->ncol;
-        const uint32_t want = (uint32_t)(est / (kListWidth * kWarpsPerCta * tiles_per_warp)) + 1u;
+        /* batches alternating between slots: 16-column tiles on few SMs (throughput; the rest filter the next batch).
+         * One slot used back to back: nothing overlaps, so spread 4-column tiles over more SMs (latency). */
+        const bool alternating = ctx->last_slot >= 0 && ctx->last_slot != b->index;
+        list_width = alternating ? 0u : 4u;
+        const uint32_t cols_per_warp = alternating ? (uint32_t)kListWidth : 4u;
+        const uint32_t want = (uint32_t)(est / (cols_per_warp * kWarpsPerCta * tiles_per_warp)) + 1u;
         grid = std::min(grid, std::max(want, 8u));
     }
     /* a list-mode tile gathers up to 32 arbitrary columns: size the spill store for 32 of the deepest one */
@@ -505,7 +511,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.smem_words_per_warp = words;
     B.collist = listed ? b->d_survivors : nullptr;
     B.list_count = b->d_count + 2;
-    { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 4 || w == 8 || w == 16) ? (uint32_t)w : 0u; }
+    { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 4 || w == 8 || w == 16) ? (uint32_t)w : list_width; }
     KernelTimer &kt = ctx->timers[ctx->timer_next];
     ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
     ssn_status st = timer_collect(ctx, kt);
