@@ -205,7 +205,9 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
                         pf_sample<true>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
                         pf_sample<true>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
                     }
-                    if (mine) drop = pf_eval(P, T.F, nT - sT.z, sT) && pf_eval(P, T.F, nN - sN.z, sN);
+                    /* both samples' table lookups are issued together (no short-circuit): lT/lN are 0 outside the pass */
+                    const bool eT = pf_eval(P, T.F, lT - sT.z, sT), eN = pf_eval(P, T.F, lN - sN.z, sN);
+                    if (mine) drop = eT && eN;
                 }
                 __syncwarp();                       /* every lane is done with the staged bytes before the next pass overwrites them */
             }
