@@ -115,6 +115,8 @@ static slot_meta *meta_of(gpu_t *g, ssn_batch *b)
     return &g->meta[g->n_meta++];
 }
 
+static uint64_t g_survivors;   /* columns the pre-filter handed to the full model (statistics only) */
+
 /* waits for the oldest batch in flight and writes its sites */
 static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, ssn_packer *pk, ssn_writer *wr, uint64_t *n_sites)
 {
@@ -134,6 +136,10 @@ static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, 
         ssn_writer_site(wr, name ? name : "", m->map.pos[c], m->map.ref_char[c], &sites[i]);
     }
     *n_sites += n;
+    {
+        uint32_t surv = 0;
+        if (ssn_batch_survivors(b, &surv) == SSN_OK) g_survivors += surv;
+    }
     g->in_flight -= 1;
     *head = (*head + 1) % cap;
     *count -= 1;
@@ -291,10 +297,11 @@ done:
                 fprintf(sf, "{\"columns\": %llu, \"read_bases\": %llu, \"batches\": %llu, \"sites\": %llu, \"records_tumor\": %llu, "
                         "\"records_normal\": %llu, \"wall_s\": %.6f, \"setup_s\": %.6f, \"pack_wait_s\": %.6f, \"pack_count_s\": %.6f, "
                         "\"pack_fill_s\": %.6f, \"gpu_wait_s\": %.6f, \"gpus\": %d, \"threads\": %d, \"slots\": %d, \"kernel_launches\": %llu, "
-                        "\"columns_per_s\": %.1f}\n",
+                        "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"columns_per_s\": %.1f}\n",
                         (unsigned long long)st.columns, (unsigned long long)st.entries, (unsigned long long)n_batches,
                         (unsigned long long)n_sites, (unsigned long long)st.records[0], (unsigned long long)st.records[1], wall, t_setup,
                         st.t_wait, st.t_count, st.t_fill, t_gpu_wait, n_gpus, n_threads, n_slots, (unsigned long long)launches,
+                        ssn_prefilter_enabled(gpus[0].ctx), (unsigned long long)g_survivors,
                         wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
                 fclose(sf);
             }
