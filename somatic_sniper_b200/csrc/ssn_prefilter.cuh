@@ -5,9 +5,10 @@
  * streams over every column of a batch once (TMA bulk-staged tiles of 32 columns, lane-per-column, packed byte
  * arithmetic: ~9 instructions per read-base instead of the ~95 of the full model) and PROVES, for most columns, that
  * sniper_glf2cns (sniper_maqcns.c:250-273) calls the homozygous reference genotype in both samples.  Those columns are
- * finished.  Every other column - real variants, noisy columns, anything the bounds cannot decide, every column of a
- * tile that is not "clean" (a base quality outside [1,63]) or too deep for the staging area - is appended to the
- * survivor list and goes through the full model (ssn_score_kernel in list mode).  Results are identical to scoring
+ * finished.  Every other column - real variants, noisy columns, anything the bounds cannot decide, columns with more than
+ * 255 read-bases in a sample, every column of a staging pass that holds a base quality >= 64 - is appended to the
+ * survivor list and goes through the full model (ssn_score_kernel in list mode).  Tiles deeper than the staging area are
+ * staged in passes of consecutive columns; read-bases of quality 0 (invisible to the model) are masked out.  Results are identical to scoring
  * every column; SSN_SUBMIT_NO_PREFILTER switches the filter off, SSN_SUBMIT_COLUMN_DUMP records its decision next to the
  * full model's output so tests can audit it.
  *

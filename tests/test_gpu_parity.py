@@ -286,3 +286,18 @@ def test_prefilter_through_the_pipeline(mods):
     for a, b in zip(out[0], out[api.SUBMIT_NO_PREFILTER]):
         assert a.tobytes() == b.tobytes()
     assert sum(len(a) for a in out[0]) > 0
+
+
+def test_prefilter_off_when_a_precondition_fails(mods):
+    """A heterozygote prior so large that the consensus penalty q_r is not positive: the proof does not apply, the ctx runs
+    every column through the full model, and the result still matches the oracle."""
+    api, synth, Oracle = mods
+    cols = synth.make_columns(30000, seed=71, p_som=5e-3, p_het=5e-3)
+    sc = api.Scorer(api.default_params(het_rate=0.4), device=0, n_slots=1, max_columns=30000, max_entries=int(cols["n_entries"]) + 64)
+    assert not sc.prefilter_enabled()
+    sites, _ = sc.score(cols)
+    assert sc.last_survivors == 0
+    sc.close()
+    want = Oracle(het_rate=0.4).score_batch(cols["off"], cols["bs"], cols["bq"], cols["mq"], cols["ref_char"])
+    assert np.array_equal(sites["column"].astype(np.int64), want["emit_col"].astype(np.int64))
+    assert np.array_equal(api.sites_to_records(sites, cols["ref_char"]), want["recs"])
