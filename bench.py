@@ -11,7 +11,7 @@ no collective on the data path; torch.distributed only carries the barrier and t
 
 value      columns/s, all ranks, batches already resident in HBM, timed with CUDA events; the product path:
            the exact hom-reference pre-filter kernel over every column, then the full model on the survivors;
-           4 resident batches in flight on their slot streams (the survivors' kernel of one batch overlaps the
+           8 resident batches in flight on their slot streams (the survivors' kernel of one batch overlaps the
            next batch's pre-filter); single_stream = the same with one batch at a time
 full_model the same with SSN_SUBMIT_NO_PREFILTER: every column through the full model (identical sites)
 e2e        the same through ssn_batch_submit/ssn_results_next with pinned HOST batches, 8 batches in flight
@@ -38,7 +38,7 @@ METRIC = "pileup_columns_per_sec_scored"
 UNIT = "columns/s"
 COLUMNS = 1_000_000
 CHUNKS = 8                      # e2e: the step's columns travel as 8 pinned batches on 8 streams
-STREAMS = 4                     # value: resident batches in flight (slot streams), the way the packer pipeline runs
+STREAMS = 8                     # value: resident batches in flight (slot streams), the way the packer pipeline runs (same as CHUNKS)
 WORKLOAD = "synthetic 1 Mb region, normal 30x / tumor 60x, -Q 15 independent priors (BASELINE configs[1])"
 
 

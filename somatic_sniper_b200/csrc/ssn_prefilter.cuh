@@ -72,44 +72,66 @@ __device__ __forceinline__ int pass_quality_class(uint32_t raw_s, uint32_t bytes
 
 /* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.
  * C = tile-uniform number of 4-read-base chunks; R4 = the reference's nt16 code in every byte. */
+struct PfAcc { uint32_t m, n1, S, qref, q1, z; };
+
+/* four read-bases of one sample: BSr/BQr/MQr = the aligned words, keep = live-byte mask (MASKED) */
+template <bool ZEROS, bool MASKED>
+__device__ __forceinline__ void pf_chunk(uint32_t BSr, uint32_t BQr, uint32_t MQr, uint32_t keep, uint32_t R4, PfAcc &A)
+{
+    const uint32_t ones = 0x01010101u;
+    if (ZEROS) {                                                                /* quality-0 read-bases: dead bytes, counted */
+        const uint32_t nzq = sign_bytes(BQr + 0x7f7f7f7fu);                     /* every quality is < 64 here */
+        A.z = __dp4a(keep & ~nzq, ones, A.z);
+        keep &= nzq;
+    }
+    /* dead bytes become "reference base, forward strand, quality 0": they add nothing to any sum */
+    const uint32_t BS = MASKED ? ((BSr & keep) | (R4 & ~keep)) : BSr;
+    const uint32_t BQ = MASKED ? (BQr & keep) : BQr;
+    const uint32_t M7 = MQr & 0x7f7f7f7fu;
+    /* byte masks by sign replication (PRMT): NM = 0xff where the nt16 code differs from the reference's,
+     * RV = 0xff where a reference read-base sits on the reverse strand */
+    const uint32_t NM = sign_bytes(((BS ^ R4) & 0x0f0f0f0fu) + 0x7f7f7f7fu);
+    const uint32_t RV = sign_bytes(BS << 3) & ~NM;
+    A.m = __dp4a(NM, ones, A.m);                                                /* 255 per non-reference read-base */
+    A.n1 = __dp4a(RV, ones, A.n1);
+    A.S = __dp4a(BQ & NM, ones, A.S);
+    /* q = min(baseQ, mapQ & 0x7f) per byte: baseQ <= 63, so (baseQ + 0x80 - m7) keeps bit 7 iff baseQ >= m7 */
+    const uint32_t GM = sign_bytes(BQ + 0x80808080u - M7);
+    const uint32_t q = ((M7 & GM) | (BQ & ~GM)) & ~NM;                         /* reference read-bases only */
+    A.qref = __dp4a(q, ones, A.qref);
+    A.q1 = __dp4a(q & RV, ones, A.q1);
+}
+
+/* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.  C = tile-uniform
+ * number of 4-read-base chunks, Cfull = tile-uniform number of leading chunks that are completely live in every lane
+ * that matters (no masking there).  R4 = the reference's nt16 code in every byte. */
 template <bool ZEROS>
-__device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, int C, uint32_t R4, PfStats &st)
+__device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, int C, int Cfull, uint32_t R4, PfStats &st)
 {
     const uint32_t a = raw_s + (r & ~3u), sh = (r & 3u) * 8u;
     uint32_t ws = lds_u32(a), wq = lds_u32(a + kRawBytes), wm = lds_u32(a + 2 * kRawBytes);
-    uint32_t bits = len * 8u;                      /* live bits left in this sample */
-    uint32_t acc_m = 0, acc_n1 = 0, S = 0, qref = 0, q1 = 0, acc_z = 0;
-    const uint32_t ones = 0x01010101u;
+    PfAcc A = {0u, 0u, 0u, 0u, 0u, 0u};
+    int c = 0;
+    if (!ZEROS) {
 #pragma unroll 2
-    for (int c = 0; c < C; ++c) {
-        const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
-        uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);                /* low min(bits,32) bits */
-        bits = max(bits, 32u) - 32u;
-        if (ZEROS) {                                                            /* quality-0 read-bases: dead bytes, counted */
-            const uint32_t nzq = sign_bytes(__funnelshift_r(wq, nq, sh) + 0x7f7f7f7fu);   /* every quality is < 64 here */
-            acc_z = __dp4a(keep & ~nzq, ones, acc_z);
-            keep &= nzq;
+        for (; c < Cfull; ++c) {
+            const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
+            pf_chunk<false, false>(__funnelshift_r(ws, ns, sh), __funnelshift_r(wq, nq, sh), __funnelshift_r(wm, nm, sh), 0xffffffffu, R4, A);
+            ws = ns; wq = nq; wm = nm;
         }
-        /* dead bytes become "reference base, forward strand, quality 0": they add nothing to any sum */
-        const uint32_t BS = (__funnelshift_r(ws, ns, sh) & keep) | (R4 & ~keep);
-        const uint32_t BQ = __funnelshift_r(wq, nq, sh) & keep;
-        const uint32_t M7 = __funnelshift_r(wm, nm, sh) & 0x7f7f7f7fu;
-        ws = ns; wq = nq; wm = nm;
-        /* byte masks by sign replication (PRMT): NM = 0xff where the nt16 code differs from the reference's,
-         * RV = 0xff where a reference read-base sits on the reverse strand */
-        const uint32_t NM = sign_bytes(((BS ^ R4) & 0x0f0f0f0fu) + 0x7f7f7f7fu);
-        const uint32_t RV = sign_bytes(BS << 3) & ~NM;
-        acc_m = __dp4a(NM, ones, acc_m);                                        /* 255 per non-reference read-base */
-        acc_n1 = __dp4a(RV, ones, acc_n1);
-        S = __dp4a(BQ & NM, ones, S);
-        /* q = min(baseQ, mapQ & 0x7f) per byte: baseQ <= 63, so (baseQ + 0x80 - m7) keeps bit 7 iff baseQ >= m7 */
-        const uint32_t GM = sign_bytes(BQ + 0x80808080u - M7);
-        const uint32_t q = ((M7 & GM) | (BQ & ~GM)) & ~NM;                     /* reference read-bases only */
-        qref = __dp4a(q, ones, qref);
-        q1 = __dp4a(q & RV, ones, q1);
     }
-    st.m = acc_m / 255u; st.n1 = acc_n1 / 255u; st.z = acc_z / 255u;
-    st.S = S; st.qref = qref; st.q1 = q1;
+    uint32_t bits = len * 8u;                      /* live bits left in this sample */
+    bits = max(bits, 32u * (uint32_t)c) - 32u * (uint32_t)c;
+#pragma unroll 2
+    for (; c < C; ++c) {
+        const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
+        const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);          /* low min(bits,32) bits */
+        bits = max(bits, 32u) - 32u;
+        pf_chunk<ZEROS, true>(__funnelshift_r(ws, ns, sh), __funnelshift_r(wq, nq, sh), __funnelshift_r(wm, nm, sh), keep, R4, A);
+        ws = ns; wq = nq; wm = nm;
+    }
+    st.m = A.m / 255u; st.n1 = A.n1 / 255u; st.z = A.z / 255u;
+    st.S = A.S; st.qref = A.qref; st.q1 = A.q1;
 }
 
 /* true: genotype RR provably wins sniper_glf2cns for this sample */
@@ -199,13 +221,17 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
                     const uint32_t r0 = mine ? o0 - a0 : 0u;
                     const uint32_t R4 = ref16 * 0x01010101u;
                     PfStats sT, sN;
+                    /* leading chunks that are fully live in every column of the pass need no masks; the lanes outside
+                     * the pass run them on whatever is staged and their sums are thrown away below */
+                    const int fullT = (int)(__reduce_min_sync(kFull, mine ? nT : 0xffffu) >> 2), fullN = (int)(__reduce_min_sync(kFull, mine ? nN : 0xffffu) >> 2);
                     if (qc == 0) {
-                        pf_sample<false>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
-                        pf_sample<false>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
+                        pf_sample<false>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), fullT, R4, sT);
+                        pf_sample<false>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), fullN, R4, sN);
                     } else {
-                        pf_sample<true>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), R4, sT);
-                        pf_sample<true>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), R4, sN);
+                        pf_sample<true>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), 0, R4, sT);
+                        pf_sample<true>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), 0, R4, sN);
                     }
+                    if (!mine) { sT.m = sT.S = sT.n1 = sT.qref = sT.q1 = sT.z = 0u; sN = sT; }
                     /* both samples' table lookups are issued together (no short-circuit): lT/lN are 0 outside the pass */
                     const bool eT = pf_eval(P, T.F, lT - sT.z, sT), eN = pf_eval(P, T.F, lN - sN.z, sN);
                     if (mine) drop = eT && eN;
