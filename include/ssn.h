@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SSN_ABI_VERSION 1
+#define SSN_ABI_VERSION 2
 
 typedef enum {
     SSN_OK = 0,
@@ -189,6 +189,58 @@ typedef struct {
 } ssn_prefilter_view;
 ssn_status ssn_host_prefilter_create(const ssn_params *p, ssn_prefilter_view *view, void **handle);
 void ssn_host_prefilter_destroy(void *handle);
+/* ---- device-side pileup: reads in, sites out ----------------------------------------------------------------
+ * Replaces, on the GPU, the column construction of get_next_pos / resolve_cigar
+ * (src/lib/sniper/sniper_pileup.c:57-104,186-205): instead of packed columns (3 bytes per read-base) the host ships
+ * the filtered reads themselves (≈1.6 bytes per read-base), filed under windows of SSN_READ_WINDOW positions, and the
+ * device builds the very same column batch (ssn_batch_view layout, same entry order) before scoring it.  Which reads
+ * are kept (flag/mapQ filter, keep rule, sortedness abort: sniper_pileup.c:207-222) stays with the caller.
+ *
+ * A record = ssn_read_rec header, then cigar[n_cigar] (uint32, BAM encoding), seq[(l_qseq+1)/2] (4-bit codes, BAM
+ * order), qual[l_qseq]; `bytes` = record size rounded up to a multiple of 4.  Within one window and sample the
+ * records must be in non-decreasing `beg` order (a coordinate-sorted BAM's order); a read appears in every window it
+ * overlaps.  CIGAR semantics: M adds a read-base per position, D/N skip positions, I/S skip query bases, everything
+ * else (H, P, =, X) advances nothing (samtools-0.1.6, QUIRK B6 in SURVEY.md). */
+#define SSN_READ_WINDOW_SHIFT 13
+#define SSN_READ_WINDOW (1u << SSN_READ_WINDOW_SHIFT)
+typedef struct {
+    int32_t beg, end;          /* 0-based start; bam_calend() end (informational: the device walks the CIGAR) */
+    uint32_t l_qseq;
+    uint16_t n_cigar;
+    uint8_t mapq, strand;      /* strand 1 = reverse */
+    uint32_t bytes;
+} ssn_read_rec;
+typedef struct {
+    uint32_t rec_first[2];     /* index into rec_off of the window's first read: tumor, normal */
+    uint32_t n_reads[2];
+    uint32_t lo;               /* first position of the window (a multiple of SSN_READ_WINDOW) */
+    int32_t tid;
+} ssn_read_window;
+/* Pinned host arrays of one read batch (owned by the slot; fill them in place). */
+typedef struct {
+    uint8_t *recs;             /* records back to back */
+    uint32_t *rec_off;         /* byte offset / 4 of every record, window after window, tumor reads before normal */
+    ssn_read_window *win;
+    uint8_t *ref_nt16;         /* [max_windows][SSN_READ_WINDOW]: bam_nt16_table[reference char]; 15 => no column */
+    uint64_t max_rec_bytes;
+    uint32_t max_reads, max_windows;
+} ssn_reads_view;
+/* Capacity of the read buffers every slot gets on its first ssn_batch_reads_view (call before that). */
+ssn_status ssn_reads_reserve(ssn_ctx *ctx, uint64_t max_rec_bytes, uint32_t max_reads, uint32_t max_windows);
+ssn_status ssn_batch_reads_view(ssn_ctx *ctx, ssn_batch *b, ssn_reads_view *out);
+/* Asynchronous: H2D of the reads, the pileup kernels (count, column scan, fill).  The scoring kernels are queued when
+ * the batch reaches the head of ssn_results_next (their launch geometry needs the column count the device found).
+ * The columns must fit the slot (max_columns / max_entries of ssn_create), else results_next fails with
+ * SSN_ERR_OVERFLOW. */
+ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_t n_windows, uint32_t n_reads, uint64_t rec_bytes,
+                                  uint32_t flags);
+/* After ssn_results_next: genome position of every column the device built, pos[c] = window index << 13 | offset. */
+ssn_status ssn_batch_column_positions(ssn_batch *b, const uint32_t **pos, uint32_t *n_columns, uint64_t *n_entries);
+/* Copies the device-built column batch into the slot's pinned ssn_batch_view arrays (parity tests). */
+ssn_status ssn_batch_download_columns(ssn_ctx *ctx, ssn_batch *b);
+/* Sum of the pileup kernels' durations since the last reset. */
+ssn_status ssn_pileup_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_batches, int reset);
+
 /* Writes a buffer larger than L2 on the ctx's device (cold-cache timing). */
 ssn_status ssn_flush_l2(ssn_ctx *ctx);
 

@@ -50,6 +50,11 @@ const char *ssn_packer_target_name(const ssn_packer *p, int which, int32_t tid);
  * at the end of the walk. */
 ssn_status ssn_packer_next(ssn_packer *p, const ssn_batch_view *view, const ssn_colmap *map,
                            uint32_t *n_columns, uint64_t *n_entries);
+/* Packs whole read windows — the input of the device pileup, ssn_batch_submit_reads (include/ssn.h) — with the packer's
+ * own count/fill code, single-threaded: the CPU side of the device pileup's parity tests.  The records of one window
+ * and sample must lie back to back in `recs`.  pos[c] (optional) = window index << 13 | offset inside the window. */
+ssn_status ssn_pack_read_windows(const ssn_reads_view *in, uint32_t n_windows, const ssn_batch_view *view,
+                                 uint32_t *pos, uint32_t *n_columns, uint64_t *n_entries);
 void ssn_packer_get_stats(const ssn_packer *p, ssn_packer_stats *out);
 const char *ssn_host_last_error(void);
 

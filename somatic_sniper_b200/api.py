@@ -45,6 +45,19 @@ class BatchView(C.Structure):
                 ("max_columns", C.c_uint32), ("max_entries", C.c_uint64)]
 
 
+class ReadsView(C.Structure):
+    """ssn_reads_view: pinned arrays of one read batch (device pileup)."""
+    _fields_ = [("recs", C.POINTER(C.c_uint8)), ("rec_off", C.POINTER(C.c_uint32)), ("win", C.c_void_p),
+                ("ref_nt16", C.POINTER(C.c_uint8)), ("max_rec_bytes", C.c_uint64), ("max_reads", C.c_uint32),
+                ("max_windows", C.c_uint32)]
+
+
+READ_WINDOW = 1 << 13
+READ_REC_DTYPE = np.dtype([("beg", "<i4"), ("end", "<i4"), ("l_qseq", "<u4"), ("n_cigar", "<u2"), ("mapq", "u1"),
+                           ("strand", "u1"), ("bytes", "<u4")])
+READ_WINDOW_DTYPE = np.dtype([("rec_first", "<u4", 2), ("n_reads", "<u4", 2), ("lo", "<u4"), ("tid", "<i4")])
+assert READ_REC_DTYPE.itemsize == 20 and READ_WINDOW_DTYPE.itemsize == 24
+
 SAMPLE_DTYPE = np.dtype([
     ("genotype", "<i4"), ("joint_genotype", "<i4"), ("joint_consensus_quality", "<i4"),
     ("consensus_quality", "<i4"), ("variant_allele_quality", "<i4"), ("somatic_score", "<i4"),
@@ -86,6 +99,12 @@ SIGNATURES = {
     "ssn_batch_survivors": (_I, [_VP, C.POINTER(_U32)]),
     "ssn_host_prefilter_create": (_I, [C.POINTER(Params), C.POINTER(PrefilterView), C.POINTER(_VP)]),
     "ssn_host_prefilter_destroy": (None, [_VP]),
+    "ssn_reads_reserve": (_I, [_VP, _U64, _U32, _U32]),
+    "ssn_batch_reads_view": (_I, [_VP, _VP, C.POINTER(ReadsView)]),
+    "ssn_batch_submit_reads": (_I, [_VP, _VP, _U32, _U32, _U64, _U32]),
+    "ssn_batch_column_positions": (_I, [_VP, C.POINTER(_VP), C.POINTER(_U32), C.POINTER(_U64)]),
+    "ssn_batch_download_columns": (_I, [_VP, _VP]),
+    "ssn_pileup_time": (_I, [_VP, C.POINTER(C.c_float), C.POINTER(_U64), _I]),
 }
 
 _lib = None
@@ -285,6 +304,55 @@ class Scorer:
 
     def prefilter_enabled(self):
         return bool(self.lib.ssn_prefilter_enabled(self.ctx))
+
+    # -- read batches: the device builds the columns (ssn_pileup.cuh) -------------------------------
+    def reads_reserve(self, max_rec_bytes, max_reads, max_windows):
+        _check(self.lib.ssn_reads_reserve(self.ctx, max_rec_bytes, max_reads, max_windows))
+
+    def reads_view(self, batch):
+        """numpy views of the slot's pinned read arrays: dict(recs u8, rec_off u32, win READ_WINDOW_DTYPE, ref_nt16 u8[w, 8192])."""
+        v = ReadsView()
+        _check(self.lib.ssn_batch_reads_view(self.ctx, batch.h, C.byref(v)))
+        arr = np.ctypeslib.as_array
+        nw = int(v.max_windows)
+        win = arr(C.cast(v.win, C.POINTER(C.c_uint8)), shape=(nw * READ_WINDOW_DTYPE.itemsize,)).view(READ_WINDOW_DTYPE)
+        return dict(recs=arr(v.recs, shape=(int(v.max_rec_bytes),)), rec_off=arr(v.rec_off, shape=(int(v.max_reads),)),
+                    win=win, ref_nt16=arr(v.ref_nt16, shape=(nw, READ_WINDOW)))
+
+    def fill_reads(self, batch, rw):
+        """rw: dict from reads.build_read_windows. Copies it into the slot's pinned arrays; returns the submit arguments."""
+        v = self.reads_view(batch)
+        nb, nr, nw = rw["recs"].size, rw["rec_off"].size, rw["win"].size
+        if nb > v["recs"].size or nr > v["rec_off"].size or nw > v["win"].size:
+            raise SsnError("read batch of %d bytes / %d reads / %d windows exceeds the reserved capacity" % (nb, nr, nw))
+        v["recs"][:nb] = rw["recs"]
+        v["rec_off"][:nr] = rw["rec_off"]
+        v["win"][:nw] = rw["win"]
+        v["ref_nt16"][:nw] = rw["ref_nt16"]
+        return nw, nr, nb
+
+    def submit_reads(self, batch, n_windows, n_reads, rec_bytes, flags=0):
+        _check(self.lib.ssn_batch_submit_reads(self.ctx, batch.h, n_windows, n_reads, rec_bytes, flags))
+
+    def column_positions(self, batch):
+        """(pos u32[ncol] = window << 13 | offset, n_entries) of a finished read batch."""
+        p, n, e = _VP(), _U32(), _U64()
+        _check(self.lib.ssn_batch_column_positions(batch.h, C.byref(p), C.byref(n), C.byref(e)))
+        pos = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), shape=(int(n.value),)).copy() if n.value else np.zeros(0, np.uint32)
+        return pos, int(e.value)
+
+    def download_columns(self, batch):
+        """The column batch the device built from a read batch, as a dict like synth.make_columns' (minus ref_char)."""
+        pos, nent = self.column_positions(batch)
+        _check(self.lib.ssn_batch_download_columns(self.ctx, batch.h))
+        ncol = pos.size
+        return dict(ncol=ncol, n_entries=nent, off=batch.off[:2 * ncol + 1].copy(), bs=batch.bs[:nent].copy(),
+                    bq=batch.bq[:nent].copy(), mq=batch.mq[:nent].copy(), ref_nt16=batch.ref_nt16[:ncol].copy(), pos=pos)
+
+    def pileup_time(self, reset=False):
+        ms, n = C.c_float(), _U64()
+        _check(self.lib.ssn_pileup_time(self.ctx, C.byref(ms), C.byref(n), 1 if reset else 0))
+        return ms.value, int(n.value)
 
     # -- resident path ------------------------------------------------------------------------------
     def upload(self, batch):

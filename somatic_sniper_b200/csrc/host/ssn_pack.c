@@ -413,3 +413,66 @@ ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn
     if (ncol == 0) return ssn_packer_next(pk, view, map, n_columns, n_entries);   /* windows without a common column */
     return SSN_OK;
 }
+
+/* ---- whole read windows (the input of the device pileup) through the very same count/fill code ---------------- */
+
+ssn_status ssn_pack_read_windows(const ssn_reads_view *in, uint32_t n_windows, const ssn_batch_view *view,
+                                 uint32_t *pos, uint32_t *n_columns, uint64_t *n_entries)
+{
+    static const char nt16_char[] = "=ACMGRSVTWYHKDBN";
+    ssn_packer *pk;
+    ssn_colmap map;
+    char *ref;
+    uint32_t ncol = 0, w;
+    uint64_t nent = 0;
+    ssn_status rc = SSN_OK;
+    if (!in || !view || !n_columns || !n_entries) { set_err("ssn_pack_read_windows: null argument"); return SSN_ERR_ARG; }
+    pk = (ssn_packer*)calloc(1, sizeof(*pk));
+    ref = (char*)malloc(SSN_WINDOW);
+    map.tid = (int32_t*)malloc(sizeof(int32_t) * view->max_columns);
+    map.pos = (uint32_t*)malloc(sizeof(uint32_t) * view->max_columns);
+    map.ref_char = (uint8_t*)malloc(view->max_columns);
+    pk->view = view; pk->map = &map;
+    for (w = 0; w < n_windows && rc == SSN_OK; ++w) {
+        const ssn_read_window *W = &in->win[w];
+        ssn_window win[2];
+        pair p;
+        uint32_t i, c = 0;
+        uint64_t e = 0;
+        int s;
+        memset(&p, 0, sizeof(p));
+        for (s = 0; s < 2; ++s) {
+            uint32_t k, words = 0;
+            memset(&win[s], 0, sizeof(win[s]));
+            win[s].tid = W->tid; win[s].widx = W->lo >> SSN_WINDOW_SHIFT; win[s].n_reads = W->n_reads[s];
+            win[s].buf = in->recs + 4 * (size_t)(W->n_reads[s] ? in->rec_off[W->rec_first[s]] : 0);
+            for (k = 0; k < W->n_reads[s]; ++k) {
+                const ssn_read *h = (const ssn_read*)(win[s].buf + 4 * (size_t)words);
+                if (in->rec_off[W->rec_first[s] + k] != in->rec_off[W->rec_first[s]] + words) { set_err("ssn_pack_read_windows: records of window %u are not contiguous", w); rc = SSN_ERR_ARG; break; }
+                words += h->bytes >> 2;
+            }
+            win[s].len = 4 * (size_t)words;
+            p.w[s] = &win[s];
+        }
+        if (rc != SSN_OK) break;
+        for (i = 0; i < SSN_WINDOW; ++i) ref[i] = nt16_char[in->ref_nt16[(size_t)w * SSN_WINDOW + i] & 15];
+        p.ref = ref - W->lo; p.ref_len = (int)(W->lo + SSN_WINDOW);
+        {
+            pair *pp = &p;
+            count_task(&pp, 0);
+        }
+        for (i = 0; i < SSN_WINDOW; ++i) if (p.cnt[0][i]) { c += 1; e += (uint64_t)p.cnt[0][i] + p.cnt[1][i]; }
+        if (ncol + c > view->max_columns || nent + e > view->max_entries) { set_err("ssn_pack_read_windows: batch capacity exceeded"); rc = SSN_ERR_OVERFLOW; }
+        else {
+            segment *sg = &pk->seg[0];
+            sg->p = &p; sg->i0 = 0; sg->i1 = SSN_WINDOW; sg->col_base = ncol; sg->ent_base = nent;
+            fill_task(pk, 0);
+            if (pos) for (i = 0; i < c; ++i) pos[ncol + i] = (w << SSN_WINDOW_SHIFT) | (map.pos[ncol + i] - W->lo);
+            ncol += c; nent += e;
+        }
+        free(p.cnt[0]); free(p.cnt[1]);
+    }
+    if (rc == SSN_OK) { view->off[2 * (size_t)ncol] = (uint32_t)nent; *n_columns = ncol; *n_entries = nent; }
+    free(map.tid); free(map.pos); free(map.ref_char); free(ref); free(pk);
+    return rc;
+}

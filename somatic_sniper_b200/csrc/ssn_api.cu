@@ -14,6 +14,7 @@
 #include "ssn_internal.h"
 #include "ssn_kernels.cuh"
 #include "ssn_prefilter.cuh"
+#include "ssn_pileup.cuh"
 
 using namespace ssn;
 
@@ -69,6 +70,13 @@ struct ssn_batch {
     cudaStream_t stream;
     cudaEvent_t done;
     uint32_t n_sites;
+    /* read batch: the device builds the columns (ssn_pileup.cuh) */
+    bool reads_alloc, reads_pending, from_reads;
+    uint32_t n_win;
+    uint8_t *h_recs; uint32_t *h_rec_off; ssn_read_window *h_win; uint8_t *h_wref; uint32_t *h_summary, *h_colpos;
+    uint8_t *d_recs; uint32_t *d_rec_off; ssn_read_window *d_win; uint8_t *d_wref;
+    uint32_t *d_A, *d_P, *d_wspan, *d_summary, *d_colpos; int32_t *d_rbeg, *d_rend; uint2 *d_wtot;
+    cudaEvent_t piled, pa, pb;
 };
 
 struct KernelTimer {
@@ -109,6 +117,8 @@ struct ssn_ctx {
     bool pf_on;
     double survivor_frac;     /* survivors / columns of the last collected batch: sizes the list-mode grid */
     int last_slot;            /* slot of the previous launch: another slot's survivors' kernel may still be running */
+    uint64_t reads_cap_bytes; uint32_t reads_cap_reads, reads_cap_windows;   /* ssn_reads_reserve */
+    double pileup_ms; uint64_t pileup_n;
 };
 
 extern "C" ssn_status ssn_params_default(ssn_params *p)
@@ -174,6 +184,13 @@ static void slot_free(ssn_batch *b)
     cudaFreeHost(b->h_ref); cudaFreeHost(b->h_count); cudaFreeHost(b->h_sites); cudaFreeHost(b->h_dump);
     cudaFree(b->d_off); cudaFree(b->d_bs); cudaFree(b->d_bq); cudaFree(b->d_mq); cudaFree(b->d_ref);
     cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump); cudaFree(b->d_survivors);
+    cudaFreeHost(b->h_recs); cudaFreeHost(b->h_rec_off); cudaFreeHost(b->h_win); cudaFreeHost(b->h_wref);
+    cudaFreeHost(b->h_summary); cudaFreeHost(b->h_colpos);
+    cudaFree(b->d_recs); cudaFree(b->d_rec_off); cudaFree(b->d_win); cudaFree(b->d_wref); cudaFree(b->d_A); cudaFree(b->d_P);
+    cudaFree(b->d_wspan); cudaFree(b->d_summary); cudaFree(b->d_colpos); cudaFree(b->d_rbeg); cudaFree(b->d_rend); cudaFree(b->d_wtot);
+    if (b->piled) cudaEventDestroy(b->piled);
+    if (b->pa) cudaEventDestroy(b->pa);
+    if (b->pb) cudaEventDestroy(b->pb);
     if (b->stream) cudaStreamDestroy(b->stream);
     if (b->done) cudaEventDestroy(b->done);
     delete b;
@@ -355,6 +372,7 @@ extern "C" ssn_status ssn_batch_acquire(ssn_ctx *ctx, ssn_batch **out)
     }
     if (!pick) { ssn_set_error("ssn_batch_acquire: all %zu slots are in flight; drain ssn_results_next first", ctx->slots.size()); return SSN_ERR_STATE; }
     pick->state = SLOT_FILLING; pick->ncol = 0; pick->nent = 0; pick->resident = false; pick->n_sites = 0;
+    pick->reads_pending = false; pick->from_reads = false;
     *out = pick;
     return SSN_OK;
 }
@@ -599,6 +617,178 @@ extern "C" ssn_status ssn_batch_submit(ssn_ctx *ctx, ssn_batch *b, uint32_t flag
     return SSN_OK;
 }
 
+/* ---- read batches: pileup on the device --------------------------------------------------------------- */
+
+extern "C" ssn_status ssn_reads_reserve(ssn_ctx *ctx, uint64_t max_rec_bytes, uint32_t max_reads, uint32_t max_windows)
+{
+    if (!ctx || !max_rec_bytes || !max_reads || !max_windows) { ssn_set_error("ssn_reads_reserve: bad argument"); return SSN_ERR_ARG; }
+    if (max_rec_bytes >= (1ull << 34) || (uint64_t)max_windows * SSN_READ_WINDOW >= (1ull << 32)) { ssn_set_error("ssn_reads_reserve: capacity too large"); return SSN_ERR_ARG; }
+    for (ssn_batch *b : ctx->slots) if (b->reads_alloc) { ssn_set_error("ssn_reads_reserve: read buffers already exist"); return SSN_ERR_STATE; }
+    ctx->reads_cap_bytes = (max_rec_bytes + 3) & ~3ull; ctx->reads_cap_reads = max_reads; ctx->reads_cap_windows = max_windows;
+    return SSN_OK;
+}
+
+static ssn_status reads_alloc(ssn_ctx *ctx, ssn_batch *b)
+{
+    if (b->reads_alloc) return SSN_OK;
+    if (!ctx->reads_cap_bytes) { ssn_set_error("call ssn_reads_reserve first"); return SSN_ERR_STATE; }
+    const size_t nb = ctx->reads_cap_bytes, nr = ctx->reads_cap_reads, nw = ctx->reads_cap_windows;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMallocHost(&b->h_recs, nb));
+    CU(cudaMallocHost(&b->h_rec_off, nr * 4));
+    CU(cudaMallocHost(&b->h_win, nw * sizeof(ssn_read_window)));
+    CU(cudaMallocHost(&b->h_wref, nw * SSN_READ_WINDOW));
+    CU(cudaMallocHost(&b->h_summary, pileup::kSummaryWords * 4));
+    CU(cudaMallocHost(&b->h_colpos, (size_t)b->max_columns * 4));
+    CU(cudaMalloc(&b->d_recs, nb));
+    CU(cudaMalloc(&b->d_rec_off, nr * 4));
+    CU(cudaMalloc(&b->d_win, nw * sizeof(ssn_read_window)));
+    CU(cudaMalloc(&b->d_wref, nw * SSN_READ_WINDOW));
+    CU(cudaMalloc(&b->d_A, nw * 2 * SSN_READ_WINDOW * 4));
+    CU(cudaMalloc(&b->d_P, nw * SSN_READ_WINDOW * 4));
+    CU(cudaMalloc(&b->d_wspan, nw * 2 * 4));
+    CU(cudaMalloc(&b->d_wtot, nw * sizeof(uint2)));
+    CU(cudaMalloc(&b->d_rbeg, nr * 4));
+    CU(cudaMalloc(&b->d_rend, nr * 4));
+    CU(cudaMalloc(&b->d_summary, pileup::kSummaryWords * 4));
+    CU(cudaMalloc(&b->d_colpos, (size_t)b->max_columns * 4));
+    CU(cudaEventCreateWithFlags(&b->piled, cudaEventDisableTiming));
+    CU(cudaEventCreate(&b->pa));
+    CU(cudaEventCreate(&b->pb));
+    b->reads_alloc = true;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_reads_view(ssn_ctx *ctx, ssn_batch *b, ssn_reads_view *out)
+{
+    if (!ctx || !b || b->ctx != ctx || !out) { ssn_set_error("ssn_batch_reads_view: bad argument"); return SSN_ERR_ARG; }
+    ssn_status st = reads_alloc(ctx, b);
+    if (st != SSN_OK) return st;
+    out->recs = b->h_recs; out->rec_off = b->h_rec_off; out->win = b->h_win; out->ref_nt16 = b->h_wref;
+    out->max_rec_bytes = ctx->reads_cap_bytes; out->max_reads = ctx->reads_cap_reads; out->max_windows = ctx->reads_cap_windows;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_t n_windows, uint32_t n_reads, uint64_t rec_bytes,
+                                             uint32_t flags)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_submit_reads: bad batch"); return SSN_ERR_ARG; }
+    if (b->state != SLOT_FILLING) { ssn_set_error("ssn_batch_submit_reads: batch was not acquired"); return SSN_ERR_STATE; }
+    if (!b->reads_alloc) { ssn_set_error("ssn_batch_submit_reads: no read buffers (ssn_batch_reads_view)"); return SSN_ERR_STATE; }
+    if (n_windows > ctx->reads_cap_windows || n_reads > ctx->reads_cap_reads || rec_bytes > ctx->reads_cap_bytes || (rec_bytes & 3)) {
+        ssn_set_error("ssn_batch_submit_reads: %u windows / %u reads / %llu bytes exceed the reserved %u / %u / %llu", n_windows, n_reads,
+                      (unsigned long long)rec_bytes, ctx->reads_cap_windows, ctx->reads_cap_reads, (unsigned long long)ctx->reads_cap_bytes);
+        return SSN_ERR_ARG;
+    }
+    /* the device trusts the index: check what is cheap to check */
+    {
+        uint64_t reads = 0;
+        for (uint32_t w = 0; w < n_windows; ++w) {
+            const ssn_read_window &W = b->h_win[w];
+            if ((W.lo & (SSN_READ_WINDOW - 1u)) || (uint64_t)W.rec_first[0] + W.n_reads[0] > n_reads || (uint64_t)W.rec_first[1] + W.n_reads[1] > n_reads) {
+                ssn_set_error("ssn_batch_submit_reads: window %u is malformed", w);
+                return SSN_ERR_ARG;
+            }
+            reads += (uint64_t)W.n_reads[0] + W.n_reads[1];
+        }
+        if (reads > n_reads) { ssn_set_error("ssn_batch_submit_reads: windows hold %llu reads, the index %u", (unsigned long long)reads, n_reads); return SSN_ERR_ARG; }
+    }
+    CU(cudaSetDevice(ctx->device));
+    b->flags = flags; b->n_win = n_windows; b->from_reads = true; b->ncol = 0; b->nent = 0; b->resident = false;
+    cudaStream_t st = b->stream;
+    CU(cudaMemsetAsync(b->d_summary, 0, pileup::kSummaryWords * 4, st));
+    if (n_windows) {
+        CU(cudaMemcpyAsync(b->d_recs, b->h_recs, rec_bytes, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b->d_rec_off, b->h_rec_off, (size_t)n_reads * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b->d_win, b->h_win, (size_t)n_windows * sizeof(ssn_read_window), cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b->d_wref, b->h_wref, (size_t)n_windows * SSN_READ_WINDOW, cudaMemcpyHostToDevice, st));
+        pileup::DevReads R;
+        R.recs = (const uint32_t*)b->d_recs; R.rec_off = b->d_rec_off; R.win = b->d_win; R.wref = b->d_wref; R.n_win = n_windows;
+        R.A = b->d_A; R.P = b->d_P; R.rbeg = b->d_rbeg; R.rend = b->d_rend; R.wspan = b->d_wspan; R.wtot = b->d_wtot; R.summary = b->d_summary;
+        R.off = b->d_off; R.bs = b->d_bs; R.bq = b->d_bq; R.mq = b->d_mq; R.ref_nt16 = b->d_ref; R.colpos = b->d_colpos;
+        R.max_columns = b->max_columns; R.max_entries = (uint32_t)std::min<uint64_t>(b->max_entries, 0xfffffff0ull);
+        R.run_len = (uint32_t)kRunLen; R.max_runs = (uint32_t)kMaxRuns;
+        const uint32_t npos = n_windows * SSN_READ_WINDOW;
+        CU(cudaEventRecord(b->pa, st));
+        pileup::count_kernel<<<n_windows * 2, pileup::kThreads, 0, st>>>(R);
+        pileup::columns_kernel<<<n_windows, pileup::kThreads, 0, st>>>(R);
+        pileup::bases_kernel<<<1, 32, 0, st>>>(R);
+        pileup::offsets_kernel<<<npos / pileup::kThreads, pileup::kThreads, 0, st>>>(R);
+        pileup::fill_kernel<<<2 * (npos / pileup::kThreads), pileup::kThreads, 0, st>>>(R);
+        pileup::shape_kernel<<<(npos / 32 + pileup::kThreads - 1) / pileup::kThreads, pileup::kThreads, 0, st>>>(R);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(b->pb, st));
+        ctx->launches += 6;
+    }
+    CU(cudaMemcpyAsync(b->h_summary, b->d_summary, pileup::kSummaryWords * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(b->piled, st));
+    b->reads_pending = true;
+    b->state = SLOT_SUBMITTED; b->seq = ctx->next_seq++;
+    return SSN_OK;
+}
+
+/* the device knows the batch's shape now: queue the scoring kernels and the copies back */
+static ssn_status finish_reads(ssn_ctx *ctx, ssn_batch *b)
+{
+    CU(cudaEventSynchronize(b->piled));
+    b->reads_pending = false;
+    const uint32_t *S = b->h_summary;
+    if (S[2]) {
+        if (S[2] & pileup::kErrUnsorted) { ssn_set_error("read batch: the reads of a window are not sorted by start"); return SSN_ERR_ARG; }
+        if (S[2] & (pileup::kErrColumns | pileup::kErrEntries)) {
+            ssn_set_error("read batch: %u columns / %u read-bases exceed the slot capacity %u / %llu", S[0], S[1], b->max_columns, (unsigned long long)b->max_entries);
+            return SSN_ERR_OVERFLOW;
+        }
+        ssn_set_error("read batch: a column holds more than %d read-bases", kRunLen * kMaxRuns);
+        return SSN_ERR_ARG;
+    }
+    if (b->n_win) {
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, b->pa, b->pb));
+        ctx->pileup_ms += ms; ctx->pileup_n += 1;
+    }
+    b->ncol = S[0]; b->nent = S[1]; b->max_tile_words = S[3]; b->max_col_words = S[4];
+    b->resident = true;
+    ssn_status st = launch(ctx, b, b->flags);
+    if (st != SSN_OK) return st;
+    if (b->ncol) CU(cudaMemcpyAsync(b->h_colpos, b->d_colpos, (size_t)b->ncol * 4, cudaMemcpyDeviceToHost, b->stream));
+    return copy_out_async(b);
+}
+
+extern "C" ssn_status ssn_batch_column_positions(ssn_batch *b, const uint32_t **pos, uint32_t *n_columns, uint64_t *n_entries)
+{
+    if (!b || !pos || !n_columns) { ssn_set_error("ssn_batch_column_positions: null"); return SSN_ERR_ARG; }
+    if (!b->from_reads || b->reads_pending || b->state == SLOT_SUBMITTED) { ssn_set_error("ssn_batch_column_positions: not a finished read batch"); return SSN_ERR_STATE; }
+    *pos = b->h_colpos; *n_columns = b->ncol;
+    if (n_entries) *n_entries = b->nent;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_batch_download_columns(ssn_ctx *ctx, ssn_batch *b)
+{
+    if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_download_columns: bad batch"); return SSN_ERR_ARG; }
+    if (!b->from_reads || b->reads_pending || !b->resident) { ssn_set_error("ssn_batch_download_columns: not a finished read batch"); return SSN_ERR_STATE; }
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpyAsync(b->h_off, b->d_off, sizeof(uint32_t) * (2 * (size_t)b->ncol + 1), cudaMemcpyDeviceToHost, b->stream));
+    if (b->nent) {
+        CU(cudaMemcpyAsync(b->h_bs, b->d_bs, b->nent, cudaMemcpyDeviceToHost, b->stream));
+        CU(cudaMemcpyAsync(b->h_bq, b->d_bq, b->nent, cudaMemcpyDeviceToHost, b->stream));
+        CU(cudaMemcpyAsync(b->h_mq, b->d_mq, b->nent, cudaMemcpyDeviceToHost, b->stream));
+    }
+    if (b->ncol) CU(cudaMemcpyAsync(b->h_ref, b->d_ref, b->ncol, cudaMemcpyDeviceToHost, b->stream));
+    CU(cudaStreamSynchronize(b->stream));
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_pileup_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_batches, int reset)
+{
+    if (!ctx) { ssn_set_error("ssn_pileup_time: null"); return SSN_ERR_ARG; }
+    if (total_ms) *total_ms = (float)ctx->pileup_ms;
+    if (n_batches) *n_batches = ctx->pileup_n;
+    if (reset) { ctx->pileup_ms = 0; ctx->pileup_n = 0; }
+    return SSN_OK;
+}
+
 extern "C" ssn_status ssn_results_next(ssn_ctx *ctx, const ssn_site **sites, uint32_t *n_sites, ssn_batch **batch)
 {
     if (!ctx || !sites || !n_sites) { ssn_set_error("ssn_results_next: null"); return SSN_ERR_ARG; }
@@ -607,8 +797,9 @@ extern "C" ssn_status ssn_results_next(ssn_ctx *ctx, const ssn_site **sites, uin
         if (b->state == SLOT_SUBMITTED && (!pick || b->seq < pick->seq)) pick = b;
     if (!pick) { ssn_set_error("ssn_results_next: nothing submitted"); return SSN_ERR_STATE; }
     CU(cudaSetDevice(ctx->device));
-    ssn_status st = collect(ctx, pick);
-    if (st != SSN_OK) return st;
+    ssn_status st = SSN_OK;
+    if (pick->reads_pending && (st = finish_reads(ctx, pick)) != SSN_OK) return st;
+    if ((st = collect(ctx, pick)) != SSN_OK) return st;
     pick->state = SLOT_DONE;
     *sites = pick->h_sites; *n_sites = pick->n_sites;
     if (batch) *batch = pick;

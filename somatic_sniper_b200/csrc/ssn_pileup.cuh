@@ -1,0 +1,287 @@
+/*
+ * ssn_pileup.cuh — reads -> pileup columns on the device (sm_100a).
+ *
+ * Builds, from the filtered reads of both samples filed under position windows, the same column batch the host
+ * packer writes (csrc/host/ssn_pack.c; layout of ssn_batch_view in include/ssn.h), entry for entry: a read adds a
+ * read-base at every position of a CIGAR M run, D and N runs skip positions, I and S skip query bases, anything else
+ * advances nothing (get_next_pos / resolve_cigar, src/lib/sniper/sniper_pileup.c:57-104,186-205; QUIRK B6).  A
+ * column exists where both samples hold a read-base and the reference base is callable (somatic_sniper.c:127,156).
+ * Within a column the read-bases keep the order of the reads in the window, tumor before normal.
+ *
+ *   count    one CTA per (window, sample): +1/-1 marks of the M runs in shared memory, block scan -> depth per position
+ *   columns  one CTA per window: live columns, exclusive scans of columns and entries inside the window
+ *   bases    one warp: exclusive scan over the windows, totals, capacity check
+ *   offsets  one thread per position: off[], ref_nt16[], column -> position map, absolute cursors
+ *   fill     one thread per (window, sample, position): gathers the covering reads in file order (binary search on the
+ *            sorted starts, bounded below by the longest reference span of the window) and writes the column
+ *   shape    one thread per 32-column tile: the key-store footprint the scoring kernel's launch needs
+ * No atomics decide an order anywhere, so the batch is bit-identical run to run and to the host packer's.
+ */
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "ssn.h"
+
+namespace pileup {
+
+constexpr uint32_t kWin = SSN_READ_WINDOW;
+constexpr uint32_t kDead = 0xffffffffu;
+constexpr int kThreads = 256;
+constexpr int kRecWords = 5;                 /* sizeof(ssn_read_rec) / 4 */
+constexpr int kSummaryWords = 8;             /* [0] columns [1] entries [2] error bits [3] max tile words [4] max column words */
+constexpr uint32_t kErrUnsorted = 1u, kErrColumns = 2u, kErrEntries = 4u, kErrDepth = 8u;
+
+struct DevReads {
+    const uint32_t *recs;
+    const uint32_t *rec_off;
+    const ssn_read_window *win;
+    const uint8_t *wref;
+    uint32_t n_win;
+    /* work arrays of the slot */
+    uint32_t *A;          /* [n_win][2][kWin]: depth -> entry cursor of the sample at that position (kDead: no column) */
+    uint32_t *P;          /* [n_win][kWin]: column index inside the window */
+    int32_t *rbeg, *rend; /* [n_reads] start / end (from the CIGAR) of every read */
+    uint32_t *wspan;      /* [n_win][2] longest reference span */
+    uint2 *wtot;          /* [n_win] {columns, entries} of the window, then {first column, first entry} */
+    uint32_t *summary;
+    /* the column batch being built */
+    uint32_t *off; uint8_t *bs, *bq, *mq, *ref_nt16;
+    uint32_t *colpos;
+    uint32_t max_columns, max_entries;
+    uint32_t run_len, max_runs;   /* scoring kernel's sort-run geometry (shape kernel) */
+};
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane)
+{
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+
+/* Exclusive scan of kWin values held in shared memory (in place) by a CTA of kThreads threads; returns the total.
+ * Each warp owns a contiguous chunk and walks it 32 values at a time (conflict-free). */
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t *v, uint32_t *wsum)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kWarps = kThreads / 32;
+    constexpr uint32_t chunk = kWin / kWarps;
+    uint32_t sum = 0;
+    for (uint32_t j = 0; j < chunk; j += 32) sum += v[warp * chunk + j + lane];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+    if (lane == 0) wsum[warp] = sum;
+    __syncthreads();
+    uint32_t carry = 0, total = 0;
+    for (int k = 0; k < kWarps; ++k) { if (k < warp) carry += wsum[k]; total += wsum[k]; }
+    for (uint32_t j = 0; j < chunk; j += 32) {
+        const uint32_t x = v[warp * chunk + j + lane];
+        const uint32_t inc = warp_incl_scan(x, lane);
+        v[warp * chunk + j + lane] = carry + inc - x;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    __syncthreads();
+    return total;
+}
+
+__global__ void __launch_bounds__(kThreads) count_kernel(DevReads R)
+{
+    __shared__ uint32_t diff[kWin];
+    __shared__ uint32_t wsum[kThreads / 32];
+    __shared__ uint32_t span_s, err_s;
+    const uint32_t w = blockIdx.x >> 1, s = blockIdx.x & 1;
+    const ssn_read_window W = R.win[w];
+    const uint32_t first = W.rec_first[s], n = W.n_reads[s], lo = W.lo, hi = lo + kWin;
+    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) diff[i] = 0;
+    if (threadIdx.x == 0) { span_s = 0; err_s = 0; }
+    __syncthreads();
+    for (uint32_t r = threadIdx.x; r < n; r += kThreads) {
+        const uint32_t *rec = R.recs + R.rec_off[first + r];
+        const int32_t beg = (int32_t)rec[0];
+        const uint32_t n_cigar = rec[3] & 0xffffu;
+        uint32_t x = (uint32_t)beg;
+        for (uint32_t k = 0; k < n_cigar; ++k) {
+            const uint32_t c = rec[kRecWords + k], op = c & 0xfu, l = c >> 4;
+            if (op == 0u) {
+                const uint32_t a = max(x, lo), b = min(x + l, hi);
+                if (a < b) {                                   /* same marks as count_read (ssn_pack.c) */
+                    atomicAdd(&diff[a - lo], 1u);
+                    if (b < hi) atomicAdd(&diff[b - lo], 0xffffffffu);
+                }
+                x += l;
+            } else if (op == 2u || op == 3u) x += l;
+        }
+        R.rbeg[first + r] = beg;
+        R.rend[first + r] = (int32_t)x;
+        atomicMax(&span_s, x - (uint32_t)beg);
+        if (r > 0 && (int32_t)R.recs[R.rec_off[first + r - 1]] > beg) err_s = 1u;
+    }
+    __syncthreads();
+    /* depth = inclusive scan of the marks = exclusive scan + own mark */
+    uint32_t *A = R.A + ((size_t)w * 2 + s) * kWin;
+    uint32_t own[kWin / kThreads];
+    constexpr uint32_t chunk = kWin / (kThreads / 32);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (uint32_t j = 0; j < chunk / 32; ++j) own[j] = diff[warp * chunk + j * 32 + lane];
+    __syncthreads();
+    block_excl_scan(diff, wsum);
+#pragma unroll
+    for (uint32_t j = 0; j < chunk / 32; ++j) A[warp * chunk + j * 32 + lane] = diff[warp * chunk + j * 32 + lane] + own[j];
+    if (threadIdx.x == 0) {
+        R.wspan[w * 2 + s] = span_s;
+        if (err_s) atomicOr(R.summary + 2, kErrUnsorted);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) columns_kernel(DevReads R)
+{
+    __shared__ uint32_t v[kWin];
+    __shared__ uint32_t wsum[kThreads / 32];
+    const uint32_t w = blockIdx.x;
+    uint32_t *A0 = R.A + (size_t)w * 2 * kWin, *A1 = A0 + kWin;
+    const uint8_t *ref = R.wref + (size_t)w * kWin;
+    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads)
+        v[i] = (A0[i] != 0u && A1[i] != 0u && ref[i] != 15) ? 1u : 0u;
+    __syncthreads();
+    const uint32_t ncol = block_excl_scan(v, wsum);
+    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) {
+        const uint32_t ct = A0[i], cn = A1[i];
+        R.P[(size_t)w * kWin + i] = v[i];
+        v[i] = (ct != 0u && cn != 0u && ref[i] != 15) ? ct + cn : 0u;
+    }
+    __syncthreads();
+    const uint32_t nent = block_excl_scan(v, wsum);
+    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) {
+        const uint32_t ct = A0[i], cn = A1[i];
+        const bool live = ct != 0u && cn != 0u && ref[i] != 15;
+        A0[i] = live ? v[i] : kDead;
+        A1[i] = live ? v[i] + ct : kDead;
+    }
+    if (threadIdx.x == 0) R.wtot[w] = make_uint2(ncol, nent);
+}
+
+__global__ void __launch_bounds__(32) bases_kernel(DevReads R)
+{
+    const int lane = threadIdx.x;
+    uint32_t col = 0;
+    unsigned long long ent = 0;
+    for (uint32_t w0 = 0; w0 < R.n_win; w0 += 32) {
+        const uint32_t w = w0 + lane;
+        const uint2 t = w < R.n_win ? R.wtot[w] : make_uint2(0u, 0u);
+        const uint32_t ci = warp_incl_scan(t.x, lane);
+        unsigned long long ei = t.y;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long u = __shfl_up_sync(0xffffffffu, ei, d);
+            if (lane >= d) ei += u;
+        }
+        if (w < R.n_win) R.wtot[w] = make_uint2(col + ci - t.x, (uint32_t)(ent + ei - t.y));
+        col += __shfl_sync(0xffffffffu, ci, 31);
+        ent += __shfl_sync(0xffffffffu, ei, 31);
+    }
+    if (lane == 0) {
+        uint32_t err = 0;
+        if (col > R.max_columns) err |= kErrColumns;
+        if (ent > (unsigned long long)R.max_entries) err |= kErrEntries;
+        R.summary[0] = col;
+        R.summary[1] = (uint32_t)ent;
+        if (err) atomicOr(R.summary + 2, err);
+        else R.off[2 * (size_t)col] = (uint32_t)ent;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) offsets_kernel(DevReads R)
+{
+    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* w * kWin + i */
+    const uint32_t w = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u);
+    if (g < 16u) R.bq[(size_t)R.summary[1] + g] = 1;                /* the clean-tile check reads up to 16 bytes past the end */
+    if (w >= R.n_win) return;
+    uint32_t *A0 = R.A + (size_t)w * 2 * kWin, *A1 = A0 + kWin;
+    const uint32_t a = A0[i];
+    if (a == kDead) return;
+    const uint2 base = R.wtot[w];
+    const uint32_t col = base.x + R.P[g], eT = base.y + a, eN = base.y + A1[i];
+    R.off[2 * (size_t)col] = eT;
+    R.off[2 * (size_t)col + 1] = eN;
+    R.ref_nt16[col] = R.wref[g];
+    R.colpos[col] = g;
+    A0[i] = eT; A1[i] = eN;
+}
+
+/* one thread per (window, sample, position): the column's read-bases in the order of the window's reads */
+__global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
+{
+    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* (w * 2 + s) * kWin + i */
+    const uint32_t ws = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u), w = ws >> 1, s = ws & 1u;
+    if (w >= R.n_win) return;
+    uint32_t cur = R.A[g];
+    if (cur == kDead) return;
+    const ssn_read_window W = R.win[w];
+    const uint32_t first = W.rec_first[s], n = W.n_reads[s];
+    const long long p = (long long)W.lo + i;
+    const long long span = R.wspan[ws];
+    const int32_t *rb = R.rbeg + first;
+    /* reads [r0, r1): beg in (p - span, p] — every read that can cover p, in file order */
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] <= p) lo = m + 1; else hi = m; }
+    const uint32_t r1 = lo;
+    lo = 0; hi = r1;
+    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] + span <= p) lo = m + 1; else hi = m; }
+    const uint32_t up = (uint32_t)p;
+    for (uint32_t r = lo; r < r1; ++r) {
+        if ((long long)(uint32_t)R.rend[first + r] <= p) continue;
+        const uint32_t *rec = R.recs + R.rec_off[first + r];
+        const uint32_t l_qseq = rec[2], meta = rec[3], n_cigar = meta & 0xffffu;
+        uint32_t x = rec[0], y = 0;
+        bool hit = false;
+        for (uint32_t k = 0; k < n_cigar; ++k) {
+            const uint32_t c = rec[kRecWords + k], op = c & 0xfu, l = c >> 4;
+            if (op == 0u) {
+                if (up - x < l) { y += up - x; hit = true; break; }      /* x <= p here */
+                x += l; y += l;
+            } else if (op == 2u || op == 3u) {
+                if (up - x < l) break;
+                x += l;
+            } else if (op == 1u || op == 4u) y += l;
+        }
+        if (!hit) continue;
+        const uint8_t strand = (uint8_t)(((meta >> 24) & 0xffu) << 4), mapq = (uint8_t)((meta >> 16) & 0xffu);
+        const uint8_t *seq = (const uint8_t*)(rec + kRecWords + n_cigar), *qual = seq + ((l_qseq + 1u) >> 1);
+        uint8_t b = (uint8_t)(15u | strand), q = 0;
+        if (y < l_qseq) {                                                /* else: CIGAR longer than the read */
+            b = (uint8_t)(((seq[y >> 1] >> ((~y & 1u) << 2)) & 0xfu) | strand);
+            q = qual[y];
+        }
+        R.bs[cur] = b; R.bq[cur] = q; R.mq[cur] = mapq;
+        ++cur;
+    }
+}
+
+/* what scan_offsets (ssn_api.cu) computes on the host for packed batches */
+__global__ void __launch_bounds__(kThreads) shape_kernel(DevReads R)
+{
+    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    const uint32_t ncol = R.summary[0];
+    const uint32_t t = (blockIdx.x * kThreads + threadIdx.x) * 32u;
+    if (t >= ncol) return;
+    const uint32_t e = min(ncol, t + 32u);
+    uint32_t words = 0, maxc = 0, err = 0;
+    for (uint32_t c = t; c < e; ++c) {
+        const uint32_t n = R.off[2 * (size_t)c + 2] - R.off[2 * (size_t)c];
+        if (n > R.run_len * R.max_runs) err = kErrDepth;
+        const uint32_t cw = (n / R.run_len) * (R.run_len / 2) + (((n & (R.run_len - 1u)) + 1u) >> 1);
+        words += cw;
+        maxc = max(maxc, cw);
+    }
+    atomicMax(R.summary + 3, words);
+    atomicMax(R.summary + 4, maxc);
+    if (err) atomicOr(R.summary + 2, err);
+}
+
+}  // namespace pileup

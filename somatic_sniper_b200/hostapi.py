@@ -22,7 +22,7 @@ class PackerStats(C.Structure):
 
 
 HOST_SYMBOLS = ["ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
-                "ssn_packer_get_stats", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
+                "ssn_packer_get_stats", "ssn_pack_read_windows", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
                 "ssn_writer_destroy", "ssn_writer_n_formats", "ssn_writer_format_name"]
 
 
@@ -47,6 +47,9 @@ def load_library():
     lib.ssn_packer_get_stats.argtypes = [C.c_void_p, C.POINTER(PackerStats)]
     lib.ssn_packer_get_stats.restype = None
     lib.ssn_host_last_error.restype = C.c_char_p
+    lib.ssn_pack_read_windows.argtypes = [C.POINTER(api.ReadsView), C.c_uint32, C.POINTER(api.BatchView), C.POINTER(C.c_uint32),
+                                          C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+    lib.ssn_pack_read_windows.restype = C.c_int
     lib.ssn_writer_n_formats.restype = C.c_int
     lib.ssn_writer_format_name.argtypes = [C.c_int]
     lib.ssn_writer_format_name.restype = C.c_char_p
@@ -103,3 +106,37 @@ class Packer:
                 return
             yield dict(off=off[:2 * n + 1].copy(), bs=bs[:e].copy(), bq=bq[:e].copy(), mq=mq[:e].copy(), ref_nt16=ref16[:n].copy(),
                        ref_char=refc[:n].copy(), tid=tid[:n].copy(), pos=pos[:n].copy(), ncol=n, n_entries=e)
+
+
+def pack_read_windows(rw, max_columns=None, max_entries=None):
+    """Whole read windows (reads.build_read_windows) through the host packer's count/fill code (ssn_pack_read_windows).
+    Returns a column dict: ncol, n_entries, off, bs, bq, mq, ref_nt16, pos (window << 13 | offset)."""
+    lib = load_library()
+    nw = int(rw["win"].size)
+    max_columns = max_columns or max(1, nw * api.READ_WINDOW)
+    max_entries = max_entries or max(64, int(rw["entries_bound"]))
+    recs = np.ascontiguousarray(rw["recs"], np.uint8)
+    rec_off = np.ascontiguousarray(rw["rec_off"], np.uint32)
+    win = np.ascontiguousarray(rw["win"])
+    wref = np.ascontiguousarray(rw["ref_nt16"], np.uint8)
+    rv = api.ReadsView()
+    rv.recs = recs.ctypes.data_as(C.POINTER(C.c_uint8))
+    rv.rec_off = rec_off.ctypes.data_as(C.POINTER(C.c_uint32))
+    rv.win = win.ctypes.data
+    rv.ref_nt16 = wref.ctypes.data_as(C.POINTER(C.c_uint8))
+    rv.max_rec_bytes, rv.max_reads, rv.max_windows = recs.size, rec_off.size, nw
+    off = np.zeros(2 * max_columns + 1, np.uint32)
+    bs, bq, mq = (np.zeros(max_entries + 64, np.uint8) for _ in range(3))
+    ref = np.zeros(max_columns + 64, np.uint8)
+    pos = np.zeros(max_columns, np.uint32)
+    bv = api.BatchView()
+    bv.off = off.ctypes.data_as(C.POINTER(C.c_uint32))
+    bv.bs, bv.bq, bv.mq, bv.ref_nt16 = (a.ctypes.data_as(C.POINTER(C.c_uint8)) for a in (bs, bq, mq, ref))
+    bv.max_columns, bv.max_entries = max_columns, max_entries
+    ncol, nent = C.c_uint32(), C.c_uint64()
+    st = lib.ssn_pack_read_windows(C.byref(rv), nw, C.byref(bv), pos.ctypes.data_as(C.POINTER(C.c_uint32)), C.byref(ncol), C.byref(nent))
+    if st != 0:
+        raise RuntimeError("ssn_pack_read_windows: %s" % lib.ssn_host_last_error().decode())
+    n, e = int(ncol.value), int(nent.value)
+    return dict(ncol=n, n_entries=e, off=off[:2 * n + 1].copy(), bs=bs[:e].copy(), bq=bq[:e].copy(), mq=mq[:e].copy(),
+                ref_nt16=ref[:n].copy(), pos=pos[:n].copy())
