@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=1_000_000, help="columns of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-e2e-reads", action="store_true")
     ap.add_argument("--backend", default="nccl", help=argparse.SUPPRESS)
     return ap.parse_args()
 
@@ -402,6 +403,73 @@ def run_b200(args):
                "d2h_bytes_per_step": 8 * CHUNKS + 216 * n_sites, "ms_per_step": ems_max / args.steps,
                "batches_per_step": CHUNKS, "device_ms_per_step": dev_ms / args.steps, "host_wall_ms_per_step": host_ms / args.steps}
 
+    # ---- e2e_reads: the filtered reads themselves travel; the device builds the columns, then scores them ----
+    e2e_reads = None
+    if not args.no_e2e and not args.no_e2e_reads:
+        from somatic_sniper_b200 import reads as rd
+        n_win = max(1, int(round(ncol / CHUNKS / api.READ_WINDOW)))
+        length = n_win * api.READ_WINDOW
+        ref = rd.make_reference(shard_seed(rank) + 11, length + 1024)
+        ref_t = ref.copy()
+        ref_t[::5003] = np.where(ref_t[::5003] == 1, 2, 1)          # a tumor-only variant every 5 kb
+        rw = rd.build_read_windows(rd.make_reads(shard_seed(rank) + 12, ref_t, args.depth_t, 150, 0, length, low_mapq_frac=0.02),
+                                   rd.make_reads(shard_seed(rank) + 13, ref, args.depth_n, 150, 0, length, low_mapq_frac=0.02),
+                                   ref, first_window=0, n_windows=n_win)
+        sc = api.Scorer(api.default_params(), device=local, n_slots=CHUNKS, max_columns=length, max_entries=rw["entries_bound"])
+        sc.reads_reserve(rw["recs"].size + 64, rw["rec_off"].size + 1, n_win)
+        held = [sc.acquire() for _ in range(CHUNKS)]
+        for bb in held:                        # the BAM reader's job: records land in pinned memory once
+            rargs = sc.fill_reads(bb, rw)
+        for bb in held:
+            sc.release(bb)
+        live = []
+        for _ in range(CHUNKS):
+            bb = sc.acquire()
+            sc.submit_reads(bb, *rargs)
+            live.append(bb)
+
+        def reads_step():
+            got = 0
+            for i in range(CHUNKS):
+                s, _h = sc.results_next()
+                got += len(s)
+                sc.release(live[i])
+                live[i] = sc.acquire()
+                sc.submit_reads(live[i], *rargs)
+            return got
+
+        for _ in range(max(args.warmup, 3)):
+            r_sites = reads_step()
+        dist_barrier(dist)
+        sc.sync()
+        sc.pileup_time(reset=True)
+        sc.timer_start()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            reads_step()
+        rms = sc.timer_stop()
+        rwall = (time.perf_counter() - t0) * 1e3
+        dist_barrier(dist)
+        for i in range(CHUNKS):
+            sc.results_next()
+        r_pos, r_nent = sc.column_positions(live[0])
+        p_ms, p_n = sc.pileup_time()
+        r_launches = sc.kernel_launches()
+        sc.close()
+        r_cols = int(r_pos.size) * CHUNKS
+        rms_max = dist_max(dist, max(rms, rwall))
+        r_total = dist_sum(dist, r_cols)
+        h2d = CHUNKS * int(rw["recs"].size + 4 * rw["rec_off"].size + 24 * n_win + api.READ_WINDOW * n_win)
+        e2e_reads = {"value": r_total * args.steps / (rms_max * 1e-3), "unit": UNIT, "ms_per_step": rms_max / args.steps,
+                     "columns_per_gpu_per_step": r_cols, "read_bases_per_step": int(r_nent) * CHUNKS, "sites_per_step": int(r_sites),
+                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": CHUNKS * 32 + 4 * r_cols + 216 * int(r_sites) + 32 * CHUNKS,
+                     "batches_per_step": CHUNKS, "windows_per_batch": n_win,
+                     "device_ms_per_step": rms / args.steps, "host_wall_ms_per_step": rwall / args.steps,
+                     "pileup_kernels_ms_per_batch": p_ms / max(p_n, 1),
+                     "input": "filtered reads (ssn_read_rec + cigar + 4-bit bases + qualities, %.2f bytes per read-base) filed under "
+                              "8192-position windows; ssn_batch_submit_reads builds the host packer's column batch on the device "
+                              "(tests/test_pileup.py: byte-identical) and scores it" % (h2d / max(1, int(r_nent) * CHUNKS))}
+
     sampler.stop()
     if rank != 0:
         return
@@ -434,6 +502,8 @@ def run_b200(args):
             }
     if e2e is not None:
         line["e2e"] = e2e
+    if e2e_reads is not None:
+        line["e2e_reads"] = e2e_reads
     if args.gpus == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_single(cols, args.cpu_sample)
     print(json.dumps(line), file=_JSON_OUT, flush=True)

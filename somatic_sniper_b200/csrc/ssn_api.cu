@@ -75,7 +75,7 @@ struct ssn_batch {
     uint32_t n_win;
     uint8_t *h_recs; uint32_t *h_rec_off; ssn_read_window *h_win; uint8_t *h_wref; uint32_t *h_summary, *h_colpos;
     uint8_t *d_recs; uint32_t *d_rec_off; ssn_read_window *d_win; uint8_t *d_wref;
-    uint32_t *d_A, *d_P, *d_wspan, *d_summary, *d_colpos; int32_t *d_rbeg, *d_rend; uint2 *d_wtot;
+    uint32_t *d_A, *d_P, *d_wspan, *d_summary, *d_colpos; int32_t *d_rbeg; uint4 *d_rinfo; uint2 *d_wtot;
     cudaEvent_t piled, pa, pb;
 };
 
@@ -187,7 +187,7 @@ static void slot_free(ssn_batch *b)
     cudaFreeHost(b->h_recs); cudaFreeHost(b->h_rec_off); cudaFreeHost(b->h_win); cudaFreeHost(b->h_wref);
     cudaFreeHost(b->h_summary); cudaFreeHost(b->h_colpos);
     cudaFree(b->d_recs); cudaFree(b->d_rec_off); cudaFree(b->d_win); cudaFree(b->d_wref); cudaFree(b->d_A); cudaFree(b->d_P);
-    cudaFree(b->d_wspan); cudaFree(b->d_summary); cudaFree(b->d_colpos); cudaFree(b->d_rbeg); cudaFree(b->d_rend); cudaFree(b->d_wtot);
+    cudaFree(b->d_wspan); cudaFree(b->d_summary); cudaFree(b->d_colpos); cudaFree(b->d_rbeg); cudaFree(b->d_rinfo); cudaFree(b->d_wtot);
     if (b->piled) cudaEventDestroy(b->piled);
     if (b->pa) cudaEventDestroy(b->pa);
     if (b->pb) cudaEventDestroy(b->pb);
@@ -649,12 +649,13 @@ static ssn_status reads_alloc(ssn_ctx *ctx, ssn_batch *b)
     CU(cudaMalloc(&b->d_wspan, nw * 2 * 4));
     CU(cudaMalloc(&b->d_wtot, nw * sizeof(uint2)));
     CU(cudaMalloc(&b->d_rbeg, nr * 4));
-    CU(cudaMalloc(&b->d_rend, nr * 4));
+    CU(cudaMalloc(&b->d_rinfo, nr * 2 * sizeof(uint4)));
     CU(cudaMalloc(&b->d_summary, pileup::kSummaryWords * 4));
     CU(cudaMalloc(&b->d_colpos, (size_t)b->max_columns * 4));
     CU(cudaEventCreateWithFlags(&b->piled, cudaEventDisableTiming));
     CU(cudaEventCreate(&b->pa));
     CU(cudaEventCreate(&b->pb));
+    CU(cudaFuncSetAttribute(pileup::fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pileup::kFillSmem));
     b->reads_alloc = true;
     return SSN_OK;
 }
@@ -704,7 +705,7 @@ extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_
         CU(cudaMemcpyAsync(b->d_wref, b->h_wref, (size_t)n_windows * SSN_READ_WINDOW, cudaMemcpyHostToDevice, st));
         pileup::DevReads R;
         R.recs = (const uint32_t*)b->d_recs; R.rec_off = b->d_rec_off; R.win = b->d_win; R.wref = b->d_wref; R.n_win = n_windows;
-        R.A = b->d_A; R.P = b->d_P; R.rbeg = b->d_rbeg; R.rend = b->d_rend; R.wspan = b->d_wspan; R.wtot = b->d_wtot; R.summary = b->d_summary;
+        R.A = b->d_A; R.P = b->d_P; R.rbeg = b->d_rbeg; R.rinfo = b->d_rinfo; R.wspan = b->d_wspan; R.wtot = b->d_wtot; R.summary = b->d_summary;
         R.off = b->d_off; R.bs = b->d_bs; R.bq = b->d_bq; R.mq = b->d_mq; R.ref_nt16 = b->d_ref; R.colpos = b->d_colpos;
         R.max_columns = b->max_columns; R.max_entries = (uint32_t)std::min<uint64_t>(b->max_entries, 0xfffffff0ull);
         R.run_len = (uint32_t)kRunLen; R.max_runs = (uint32_t)kMaxRuns;
@@ -714,7 +715,7 @@ extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_
         pileup::columns_kernel<<<n_windows, pileup::kThreads, 0, st>>>(R);
         pileup::bases_kernel<<<1, 32, 0, st>>>(R);
         pileup::offsets_kernel<<<npos / pileup::kThreads, pileup::kThreads, 0, st>>>(R);
-        pileup::fill_kernel<<<2 * (npos / pileup::kThreads), pileup::kThreads, 0, st>>>(R);
+        pileup::fill_kernel<<<npos / pileup::kThreads, pileup::kThreads, pileup::kFillSmem, st>>>(R);
         pileup::shape_kernel<<<(npos / 32 + pileup::kThreads - 1) / pileup::kThreads, pileup::kThreads, 0, st>>>(R);
         CU(cudaGetLastError());
         CU(cudaEventRecord(b->pb, st));

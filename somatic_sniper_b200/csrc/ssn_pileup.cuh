@@ -12,8 +12,10 @@
  *   columns  one CTA per window: live columns, exclusive scans of columns and entries inside the window
  *   bases    one warp: exclusive scan over the windows, totals, capacity check
  *   offsets  one thread per position: off[], ref_nt16[], column -> position map, absolute cursors
- *   fill     one thread per (window, sample, position): gathers the covering reads in file order (binary search on the
- *            sorted starts, bounded below by the longest reference span of the window) and writes the column
+ *   fill     one warp per 32 positions of a window, a lane per position: walks the reads that can cover them in file
+ *            order (binary search on the sorted starts, bounded below by the longest reference span of the window),
+ *            appends each lane's read-bases at its column's cursor in a shared-memory image of the 32 columns, and
+ *            writes that out in 16-byte chunks
  *   shape    one thread per 32-column tile: the key-store footprint the scoring kernel's launch needs
  * No atomics decide an order anywhere, so the batch is bit-identical run to run and to the host packer's.
  */
@@ -41,7 +43,8 @@ struct DevReads {
     /* work arrays of the slot */
     uint32_t *A;          /* [n_win][2][kWin]: depth -> entry cursor of the sample at that position (kDead: no column) */
     uint32_t *P;          /* [n_win][kWin]: column index inside the window */
-    int32_t *rbeg, *rend; /* [n_reads] start / end (from the CIGAR) of every read */
+    int32_t *rbeg;        /* [n_reads] start of every read (binary searches of the fill) */
+    uint4 *rinfo;         /* [n_reads][2] {record word offset, start, l_qseq, n_cigar|mapq<<16|strand<<24}, {cigar[0], end from the CIGAR, -, -} */
     uint32_t *wspan;      /* [n_win][2] longest reference span */
     uint2 *wtot;          /* [n_win] {columns, entries} of the window, then {first column, first entry} */
     uint32_t *summary;
@@ -115,7 +118,8 @@ __global__ void __launch_bounds__(kThreads) count_kernel(DevReads R)
             } else if (op == 2u || op == 3u) x += l;
         }
         R.rbeg[first + r] = beg;
-        R.rend[first + r] = (int32_t)x;
+        R.rinfo[2 * (size_t)(first + r)] = make_uint4(R.rec_off[first + r], (uint32_t)beg, rec[2], rec[3]);
+        R.rinfo[2 * (size_t)(first + r) + 1] = make_uint4(n_cigar ? rec[kRecWords] : 0u, x, 0u, 0u);
         atomicMax(&span_s, x - (uint32_t)beg);
         if (r > 0 && (int32_t)R.recs[R.rec_off[first + r - 1]] > beg) err_s = 1u;
     }
@@ -213,44 +217,55 @@ __global__ void __launch_bounds__(kThreads) offsets_kernel(DevReads R)
     A0[i] = eT; A1[i] = eN;
 }
 
-/* one thread per (window, sample, position): the column's read-bases in the order of the window's reads */
-__global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
+/* One warp per 32 consecutive positions of a window, one lane per position, tumor then normal.  The warp walks the
+ * reads that can cover any of its positions in file order, all lanes on the same read: header and CIGAR loads are
+ * uniform, the base and quality loads of neighbouring positions coalesce, and every lane appends at its own column's
+ * cursor.  The 32 columns are one contiguous stretch of bs/bq/mq: it is assembled in shared memory (scattered byte
+ * stores to global memory run at the L2's partial-sector rate) and written out as whole 16-byte chunks.  A stretch
+ * longer than kStage bytes (about 128 read-bases per column) is written directly. */
+constexpr uint32_t kStage = 4096;
+constexpr size_t kFillSmem = (size_t)(kThreads / 32) * 3 * kStage;
+
+template <bool STAGED>
+__device__ __forceinline__ void fill_sample(const DevReads &R, const ssn_read_window &W, uint32_t ws, uint32_t s, uint32_t up,
+                                            uint32_t lane, bool live, uint32_t cur, uint8_t *sm)
 {
-    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
-    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* (w * 2 + s) * kWin + i */
-    const uint32_t ws = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u), w = ws >> 1, s = ws & 1u;
-    if (w >= R.n_win) return;
-    uint32_t cur = R.A[g];
-    if (cur == kDead) return;
-    const ssn_read_window W = R.win[w];
-    const uint32_t first = W.rec_first[s], n = W.n_reads[s];
-    const long long p = (long long)W.lo + i;
-    const long long span = R.wspan[ws];
+    const uint32_t first = W.rec_first[s], n = W.n_reads[s], up0 = up - lane;
+    const long long p0 = up0, p31 = (long long)up0 + 31, span = R.wspan[ws];
     const int32_t *rb = R.rbeg + first;
-    /* reads [r0, r1): beg in (p - span, p] — every read that can cover p, in file order */
+    /* reads [r0, r1): beg in (p0 - span, p31] — every read that can cover one of the 32 positions, in file order */
     uint32_t lo = 0, hi = n;
-    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] <= p) lo = m + 1; else hi = m; }
+    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] <= p31) lo = m + 1; else hi = m; }
     const uint32_t r1 = lo;
     lo = 0; hi = r1;
-    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] + span <= p) lo = m + 1; else hi = m; }
-    const uint32_t up = (uint32_t)p;
+    while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] + span <= p0) lo = m + 1; else hi = m; }
+    /* per-read facts come from the compact rinfo array, one read ahead of their use: the only dependent loads left in
+     * an iteration are the base and the quality (and the CIGAR words after the first) */
+    const uint4 *info = R.rinfo + 2 * (size_t)first;
+    uint4 n0 = make_uint4(0u, 0u, 0u, 0u), n1 = n0;
+    if (lo < r1) { n0 = info[2 * (size_t)lo]; n1 = info[2 * (size_t)lo + 1]; }
     for (uint32_t r = lo; r < r1; ++r) {
-        if ((long long)(uint32_t)R.rend[first + r] <= p) continue;
-        const uint32_t *rec = R.recs + R.rec_off[first + r];
-        const uint32_t l_qseq = rec[2], meta = rec[3], n_cigar = meta & 0xffffu;
-        uint32_t x = rec[0], y = 0;
-        bool hit = false;
+        const uint4 i0 = n0, i1 = n1;
+        if (r + 1 < r1) { n0 = info[2 * (size_t)(r + 1)]; n1 = info[2 * (size_t)(r + 1) + 1]; }
+        if (i1.y <= up0) continue;                                       /* ends before the warp's first position */
+        const uint32_t *rec = R.recs + i0.x;
+        const uint32_t l_qseq = i0.z, meta = i0.w, n_cigar = meta & 0xffffu;
+        uint32_t x = i0.y, y = 0, c = i1.x;
+        bool hit = false, done = false;
         for (uint32_t k = 0; k < n_cigar; ++k) {
-            const uint32_t c = rec[kRecWords + k], op = c & 0xfu, l = c >> 4;
+            if (k) c = rec[kRecWords + k];
+            const uint32_t op = c & 0xfu, l = c >> 4;
+            if (done) continue;
+            /* up - x < l  <=>  x <= up < x + l (a lane whose position lies before the read never satisfies it) */
             if (op == 0u) {
-                if (up - x < l) { y += up - x; hit = true; break; }      /* x <= p here */
-                x += l; y += l;
+                if (up - x < l) { y += up - x; hit = true; done = true; }
+                else { x += l; y += l; }
             } else if (op == 2u || op == 3u) {
-                if (up - x < l) break;
-                x += l;
+                if (up - x < l) done = true;
+                else x += l;
             } else if (op == 1u || op == 4u) y += l;
         }
-        if (!hit) continue;
+        if (!(hit && live)) continue;
         const uint8_t strand = (uint8_t)(((meta >> 24) & 0xffu) << 4), mapq = (uint8_t)((meta >> 16) & 0xffu);
         const uint8_t *seq = (const uint8_t*)(rec + kRecWords + n_cigar), *qual = seq + ((l_qseq + 1u) >> 1);
         uint8_t b = (uint8_t)(15u | strand), q = 0;
@@ -258,8 +273,50 @@ __global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
             b = (uint8_t)(((seq[y >> 1] >> ((~y & 1u) << 2)) & 0xfu) | strand);
             q = qual[y];
         }
-        R.bs[cur] = b; R.bq[cur] = q; R.mq[cur] = mapq;
+        if (STAGED) { sm[cur] = b; sm[kStage + cur] = q; sm[2 * kStage + cur] = mapq; }
+        else { R.bs[cur] = b; R.bq[cur] = q; R.mq[cur] = mapq; }
         ++cur;
+    }
+}
+
+/* bytes [base, end) of one array from the warp's stage (stage offset = address - (base & ~15)) */
+__device__ __forceinline__ void flush_stage(uint8_t *g, const uint8_t *sm, uint32_t base, uint32_t end, uint32_t lane)
+{
+    const uint32_t al = base & ~15u;
+    const uint32_t a1 = min(end, (base + 15u) & ~15u), m1 = max(a1, end & ~15u);
+    for (uint32_t j = base + lane; j < a1; j += 32u) g[j] = sm[j - al];
+    for (uint32_t j = a1 + 16u * lane; j < m1; j += 512u) *reinterpret_cast<uint4*>(g + j) = *reinterpret_cast<const uint4*>(sm + (j - al));
+    for (uint32_t j = m1 + lane; j < end; j += 32u) g[j] = sm[j - al];
+}
+
+__global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
+{
+    extern __shared__ __align__(16) uint8_t fill_stage[];
+    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* w * kWin + i */
+    const uint32_t w = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u), lane = threadIdx.x & 31u;
+    if (w >= R.n_win) return;
+    const uint32_t eT = R.A[(size_t)w * 2 * kWin + i], eN = R.A[(size_t)w * 2 * kWin + kWin + i];
+    const bool live = eT != kDead;
+    const uint32_t lives = __ballot_sync(0xffffffffu, live);
+    if (!lives) return;
+    const ssn_read_window W = R.win[w];
+    /* the warp's stretch of the entry arrays: first live column's start .. last live column's end */
+    const uint32_t base = __shfl_sync(0xffffffffu, eT, __ffs(lives) - 1);
+    uint32_t end = live ? R.off[2 * (size_t)(R.wtot[w].x + R.P[g]) + 2] : 0u;
+    end = __shfl_sync(0xffffffffu, end, 31 - __clz(lives));
+    const uint32_t al = base & ~15u, up = W.lo + i;
+    uint8_t *sm = fill_stage + (size_t)(threadIdx.x >> 5) * 3 * kStage;
+    if (end - al <= kStage) {
+        fill_sample<true>(R, W, w * 2, 0, up, lane, live, eT - al, sm);
+        fill_sample<true>(R, W, w * 2 + 1, 1, up, lane, live, eN - al, sm);
+        __syncwarp();
+        flush_stage(R.bs, sm, base, end, lane);
+        flush_stage(R.bq, sm + kStage, base, end, lane);
+        flush_stage(R.mq, sm + 2 * kStage, base, end, lane);
+    } else {
+        fill_sample<false>(R, W, w * 2, 0, up, lane, live, eT, nullptr);
+        fill_sample<false>(R, W, w * 2 + 1, 1, up, lane, live, eN, nullptr);
     }
 }
 
