@@ -50,6 +50,13 @@ const char *ssn_packer_target_name(const ssn_packer *p, int which, int32_t tid);
  * at the end of the walk. */
 ssn_status ssn_packer_next(ssn_packer *p, const ssn_batch_view *view, const ssn_colmap *map,
                            uint32_t *n_columns, uint64_t *n_entries);
+/* Device pileup (ssn_batch_submit_reads, include/ssn.h): moves the next joined windows, whole, into the read arrays of a
+ * scorer slot — the records as the BAM reader filed them, their index, the reference slice of every window.  Takes
+ * windows while the read arrays and the slot (max_columns / max_entries, against the windows' upper bounds) can hold
+ * them.  ref_chars (optional, [max_windows][SSN_READ_WINDOW]) receives the raw FASTA characters the writers print.
+ * *n_windows = 0 at the end of the walk.  Do not mix with ssn_packer_next on one packer. */
+ssn_status ssn_packer_next_reads(ssn_packer *p, const ssn_reads_view *rv, uint32_t max_columns, uint64_t max_entries,
+                                 uint8_t *ref_chars, uint32_t *n_windows, uint32_t *n_reads, uint64_t *rec_bytes);
 /* Packs whole read windows — the input of the device pileup, ssn_batch_submit_reads (include/ssn.h) — with the packer's
  * own count/fill code, single-threaded: the CPU side of the device pileup's parity tests.  The records of one window
  * and sample must lie back to back in `recs`.  pos[c] (optional) = window index << 13 | offset inside the window. */

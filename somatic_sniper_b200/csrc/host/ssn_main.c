@@ -76,6 +76,9 @@ static void usage(const char *progname, const ssn_params *p, int mapq)
 typedef struct {
     ssn_batch *batch;
     ssn_colmap map;
+    /* SSN_DEVICE_PILEUP=1: the slot's read arrays and the raw reference characters of its windows */
+    ssn_reads_view rv;
+    uint8_t *ref_chars;
 } slot_meta;
 
 typedef struct {
@@ -112,10 +115,13 @@ static slot_meta *meta_of(gpu_t *g, ssn_batch *b)
     g->meta[g->n_meta].map.tid = (int32_t*)malloc(sizeof(int32_t) * BATCH_COLUMNS);
     g->meta[g->n_meta].map.pos = (uint32_t*)malloc(sizeof(uint32_t) * BATCH_COLUMNS);
     g->meta[g->n_meta].map.ref_char = (uint8_t*)malloc(BATCH_COLUMNS);
+    g->meta[g->n_meta].ref_chars = (uint8_t*)malloc(BATCH_COLUMNS);
     return &g->meta[g->n_meta++];
 }
 
 static uint64_t g_survivors;   /* columns the pre-filter handed to the full model (statistics only) */
+static int g_device_pileup;    /* SSN_DEVICE_PILEUP=1: ship the reads, build the columns on the GPU (ssn_batch_submit_reads) */
+static uint64_t g_dev_columns, g_dev_entries;
 
 /* waits for the oldest batch in flight and writes its sites */
 static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, ssn_packer *pk, ssn_writer *wr, uint64_t *n_sites)
@@ -130,6 +136,21 @@ static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, 
         return -1;
     }
     m = meta_of(g, b);
+    if (g_device_pileup) {
+        const uint32_t *cpos;
+        uint32_t ncol;
+        uint64_t nent;
+        if (ssn_batch_column_positions(b, &cpos, &ncol, &nent) != SSN_OK) {
+            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
+            return -1;
+        }
+        g_dev_columns += ncol; g_dev_entries += nent;
+        for (i = 0; i < n; ++i) {
+            const uint32_t pw = cpos[sites[i].column], w = pw >> SSN_READ_WINDOW_SHIFT, o = pw & (SSN_READ_WINDOW - 1u);
+            const char *name = ssn_packer_target_name(pk, 0, m->rv.win[w].tid);
+            ssn_writer_site(wr, name ? name : "", m->rv.win[w].lo + o, m->ref_chars[pw], &sites[i]);
+        }
+    } else
     for (i = 0; i < n; ++i) {
         const uint32_t c = sites[i].column;
         const char *name = ssn_packer_target_name(pk, 0, m->map.tid[c]);        /* names from the tumor header (QUIRK B9) */
@@ -212,6 +233,7 @@ int main(int argc, char *argv[])
         n_threads = env_int("SSN_THREADS", cores > 3 ? (int)cores - 2 : 1, 0, 256);
     }
     memset(gpus, 0, sizeof(gpus));
+    g_device_pileup = env_int("SSN_DEVICE_PILEUP", 0, 0, 1);
 
     /* same order of stderr lines as main.c:115-131 */
     if (ssn_packer_open(argv[optind], argv[optind + 1], fn_fa, mapq, n_threads, &pk) != SSN_OK) {
@@ -224,6 +246,11 @@ int main(int argc, char *argv[])
         if (ssn_create(&prm, devices[i], (uint32_t)n_slots, BATCH_COLUMNS, BATCH_ENTRIES, &gpus[i].ctx) != SSN_OK) {
             fprintf(stderr, "[bam-somaticsniper] cannot set up GPU %d: %s\n", devices[i], ssn_last_error());
             fprintf(stderr, "[bam-somaticsniper] this build scores on sm_100 GPUs only; there is no CPU path\n");
+            ssn_packer_close(pk);
+            return 1;
+        }
+        if (g_device_pileup && ssn_reads_reserve(gpus[i].ctx, 2 * BATCH_ENTRIES, (uint32_t)(BATCH_ENTRIES / 24), BATCH_COLUMNS >> SSN_READ_WINDOW_SHIFT) != SSN_OK) {
+            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
             ssn_packer_close(pk);
             return 1;
         }
@@ -263,6 +290,24 @@ int main(int argc, char *argv[])
         }
         m = meta_of(g, b);
         if (!m) { fprintf(stderr, "[bam-somaticsniper] slot table overflow\n"); rc = 1; goto done; }
+        if (g_device_pileup) {
+            uint32_t nw = 0, nr = 0;
+            uint64_t nb = 0;
+            if (ssn_batch_reads_view(g->ctx, b, &m->rv) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); rc = 1; goto done; }
+            if (ssn_packer_next_reads(pk, &m->rv, BATCH_COLUMNS, BATCH_ENTRIES, m->ref_chars, &nw, &nr, &nb) != SSN_OK) {
+                fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
+                rc = 1; goto done;
+            }
+            if (nw == 0) { ssn_batch_release(g->ctx, b); break; }
+            if (ssn_batch_submit_reads(g->ctx, b, nw, nr, nb, 0) != SSN_OK) {
+                fprintf(stderr, "[bam-somaticsniper] GPU submit failed: %s\n", ssn_last_error());
+                rc = 1; goto done;
+            }
+            fifo[(f_head + f_count) % (MAX_GPUS * MAX_SLOTS)].gpu = next_gpu;
+            f_count += 1; g->in_flight += 1; n_batches += 1;
+            next_gpu = (next_gpu + 1) % n_gpus;
+            continue;
+        }
         if (ssn_packer_next(pk, &view, &m->map, &ncol, &nent) != SSN_OK) {
             fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
             rc = 1; goto done;
@@ -293,15 +338,16 @@ done:
                 uint64_t launches = 0;
                 const double wall = now_s() - t_start;
                 ssn_packer_get_stats(pk, &st);
+                if (g_device_pileup) { st.columns = g_dev_columns; st.entries = g_dev_entries; }
                 for (i = 0; i < n_gpus; ++i) launches += ssn_kernel_launches(gpus[i].ctx);
                 fprintf(sf, "{\"columns\": %llu, \"read_bases\": %llu, \"batches\": %llu, \"sites\": %llu, \"records_tumor\": %llu, "
                         "\"records_normal\": %llu, \"wall_s\": %.6f, \"setup_s\": %.6f, \"pack_wait_s\": %.6f, \"pack_count_s\": %.6f, "
                         "\"pack_fill_s\": %.6f, \"gpu_wait_s\": %.6f, \"gpus\": %d, \"threads\": %d, \"slots\": %d, \"kernel_launches\": %llu, "
-                        "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"columns_per_s\": %.1f}\n",
+                        "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"device_pileup\": %d, \"columns_per_s\": %.1f}\n",
                         (unsigned long long)st.columns, (unsigned long long)st.entries, (unsigned long long)n_batches,
                         (unsigned long long)n_sites, (unsigned long long)st.records[0], (unsigned long long)st.records[1], wall, t_setup,
                         st.t_wait, st.t_count, st.t_fill, t_gpu_wait, n_gpus, n_threads, n_slots, (unsigned long long)launches,
-                        ssn_prefilter_enabled(gpus[0].ctx), (unsigned long long)g_survivors,
+                        ssn_prefilter_enabled(gpus[0].ctx), (unsigned long long)g_survivors, g_device_pileup,
                         wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
                 fclose(sf);
             }
@@ -311,7 +357,7 @@ done:
     for (i = 0; i < n_gpus; ++i) {
         int k;
         ssn_destroy(gpus[i].ctx);
-        for (k = 0; k < gpus[i].n_meta; ++k) { free(gpus[i].meta[k].map.tid); free(gpus[i].meta[k].map.pos); free(gpus[i].meta[k].map.ref_char); }
+        for (k = 0; k < gpus[i].n_meta; ++k) { free(gpus[i].meta[k].map.tid); free(gpus[i].meta[k].map.pos); free(gpus[i].meta[k].map.ref_char); free(gpus[i].meta[k].ref_chars); }
     }
     ssn_writer_destroy(wr);
     fclose(out);

@@ -414,6 +414,100 @@ ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn
     return SSN_OK;
 }
 
+/* ---- read batches for the device pileup: whole joined windows, records copied as they are ----------------------- */
+
+typedef struct {
+    pair *p;
+    int s;                     /* sample; 2 = the window's reference slice */
+    uint8_t *dst; uint32_t *off; uint32_t off_base;   /* records -> dst, word offsets (off_base + ...) -> off */
+    uint8_t *nt16, *chars;
+} reads_task;
+
+static void reads_copy_task(void *arg, int idx)
+{
+    const reads_task *t = &((const reads_task*)arg)[idx];
+    if (t->s == 2) {
+        const uint32_t lo = t->p->w[0]->widx << SSN_WINDOW_SHIFT;
+        uint32_t i;
+        for (i = 0; i < SSN_WINDOW; ++i) {
+            const uint32_t pos = lo + i;
+            const int rb = (t->p->ref && (int)pos < t->p->ref_len) ? (unsigned char)t->p->ref[pos] : 'N';
+            t->nt16[i] = (uint8_t)ssn_nt16_table(rb);
+            if (t->chars) t->chars[i] = (uint8_t)rb;
+        }
+    } else {
+        const ssn_window *w = t->p->w[t->s];
+        size_t o = 0;
+        uint32_t k = 0;
+        memcpy(t->dst, w->buf, w->len);
+        while (o < w->len) {
+            t->off[k++] = t->off_base + (uint32_t)(o >> 2);
+            o += ((const ssn_read*)(w->buf + o))->bytes;
+        }
+    }
+}
+
+ssn_status ssn_packer_next_reads(ssn_packer *pk, const ssn_reads_view *rv, uint32_t max_columns, uint64_t max_entries,
+                                 uint8_t *ref_chars, uint32_t *n_windows, uint32_t *n_reads, uint64_t *rec_bytes)
+{
+    reads_task tasks[3 * GROUP_MAX];
+    pair *took[GROUP_MAX];
+    uint32_t nw = 0, nr = 0;
+    uint64_t nb = 0, ne = 0;
+    int nt = 0, i;
+    double t0 = now_s(), t1;
+    if (!pk || !rv || !n_windows || !n_reads || !rec_bytes) { set_err("ssn_packer_next_reads: null argument"); return SSN_ERR_ARG; }
+    *n_windows = 0; *n_reads = 0; *rec_bytes = 0;
+    for (;;) {
+        pair *p;
+        uint64_t b, r, e;
+        if (pk->n_pending == 0) {
+            p = next_pair(pk);
+            if (!p) break;
+            attach_ref(pk, p);
+            pk->pending[pk->n_pending++] = p;
+        }
+        p = pk->pending[0];
+        b = (uint64_t)p->w[0]->len + p->w[1]->len;
+        r = (uint64_t)p->w[0]->n_reads + p->w[1]->n_reads;
+        e = p->w[0]->n_bases + p->w[1]->n_bases;
+        if (nw == GROUP_MAX || nw == rv->max_windows || nb + b > rv->max_rec_bytes || nr + r > rv->max_reads ||
+            ne + e > max_entries || (uint64_t)(nw + 1) * SSN_WINDOW > max_columns) {
+            if (nw == 0) {
+                set_err("window %d:%u holds %llu reads / %llu record bytes / %llu read bases; the read batch capacity is %u / %llu / %llu",
+                        p->w[0]->tid, p->w[0]->widx << SSN_WINDOW_SHIFT, (unsigned long long)r, (unsigned long long)b, (unsigned long long)e,
+                        rv->max_reads, (unsigned long long)rv->max_rec_bytes, (unsigned long long)max_entries);
+                return SSN_ERR_OVERFLOW;
+            }
+            break;
+        }
+        {
+            int s;
+            ssn_read_window *W = &rv->win[nw];
+            W->lo = p->w[0]->widx << SSN_WINDOW_SHIFT; W->tid = p->w[0]->tid;
+            for (s = 0; s < 2; ++s) {
+                reads_task *t = &tasks[nt++];
+                W->rec_first[s] = nr; W->n_reads[s] = p->w[s]->n_reads;
+                t->p = p; t->s = s; t->dst = rv->recs + nb; t->off = rv->rec_off + nr; t->off_base = (uint32_t)(nb >> 2);
+                nr += p->w[s]->n_reads; nb += p->w[s]->len;
+            }
+            tasks[nt].p = p; tasks[nt].s = 2; tasks[nt].nt16 = rv->ref_nt16 + (size_t)nw * SSN_WINDOW;
+            tasks[nt].chars = ref_chars ? ref_chars + (size_t)nw * SSN_WINDOW : 0;
+            ++nt;
+        }
+        took[nw++] = p; ne += e;
+        pk->n_pending = 0;
+    }
+    t1 = now_s(); pk->st.t_wait += t1 - t0;
+    if (nw == 0) return SSN_OK;
+    ssn_pool_for(pk->pool, nt, reads_copy_task, tasks);
+    for (i = 0; i < (int)nw; ++i) pair_free(took[i]);
+    pk->st.t_fill += now_s() - t1;
+    pk->st.batches += 1;
+    *n_windows = nw; *n_reads = nr; *rec_bytes = nb;
+    return SSN_OK;
+}
+
 /* ---- whole read windows (the input of the device pileup) through the very same count/fill code ---------------- */
 
 ssn_status ssn_pack_read_windows(const ssn_reads_view *in, uint32_t n_windows, const ssn_batch_view *view,

@@ -22,7 +22,7 @@ class PackerStats(C.Structure):
 
 
 HOST_SYMBOLS = ["ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
-                "ssn_packer_get_stats", "ssn_pack_read_windows", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
+                "ssn_packer_get_stats", "ssn_pack_read_windows", "ssn_packer_next_reads", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
                 "ssn_writer_destroy", "ssn_writer_n_formats", "ssn_writer_format_name"]
 
 

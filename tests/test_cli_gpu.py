@@ -66,6 +66,35 @@ def test_synthetic_pair_matches_live_reference(ct, synthetic_pair, opts, tmp_pat
     assert sum(1 for _ in open(ref)) > 20
 
 
+@pytest.mark.parametrize("run", sorted(RUNS))
+def test_device_pileup_on_integration_data(ct, run, tmp_path):
+    """SSN_DEVICE_PILEUP=1: the reads travel and the GPU builds the columns (csrc/ssn_pileup.cuh); same bytes out."""
+    fa = str(tmp_path / "small.fa")
+    shutil.copy(os.path.join(INTEG, "small.fa"), fa)
+    out = str(tmp_path / "out")
+    r = ct.run_cli(ct.CLI, fa, os.path.join(INTEG, "t-small.bam"), os.path.join(INTEG, "n-small.bam"), out, RUNS[run],
+                   env={"SSN_DEVICE_PILEUP": 1}, stats=str(tmp_path / "stats.json"))
+    assert r["rc"] == 0, r["stderr"]
+    assert ct.comparable(out) == ct.comparable(os.path.join(INTEG, "ref_%s.out" % run))
+    assert r["stats"]["device_pileup"] == 1
+
+
+@pytest.mark.parametrize("opts", [[], ["-J", "-F", "vcf"], ["-q", "1", "-Q", "0", "-L", "-G"]], ids=lambda o: "_".join(o) or "default")
+def test_device_pileup_matches_host_packer_and_reference(ct, synthetic_pair, opts, tmp_path):
+    p = synthetic_pair
+    host, dev, ref = str(tmp_path / "host"), str(tmp_path / "dev"), str(tmp_path / "ref")
+    r0 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], host, opts, stats=str(tmp_path / "s0.json"))
+    r1 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], dev, opts, env={"SSN_DEVICE_PILEUP": 1, "SSN_DEVICES": "0,0"},
+                    stats=str(tmp_path / "s1.json"))
+    assert r0["rc"] == 0 and r1["rc"] == 0, r1["stderr"]
+    assert ct.comparable(dev) == ct.comparable(host)
+    assert r1["stats"]["device_pileup"] == 1 and r1["stats"]["columns"] == r0["stats"]["columns"]
+    assert r1["stats"]["read_bases"] == r0["stats"]["read_bases"] and r1["stats"]["sites"] == r0["stats"]["sites"] > 20
+    if ct.reference_available():
+        ct.run_cli(ct.REF_CLI, p["fasta"], p["tumor"], p["normal"], ref, opts)
+        assert ct.comparable(dev) == ct.comparable(ref)
+
+
 def test_two_scoring_contexts_and_small_slots(ct, synthetic_pair, tmp_path):
     """Region batches alternate between scoring contexts (the multi-GPU path, here two contexts on one device) and the
     ordered merge still reproduces the reference's file."""
