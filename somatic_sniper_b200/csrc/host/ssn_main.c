@@ -254,6 +254,14 @@ int main(int argc, char *argv[])
             ssn_packer_close(pk);
             return 1;
         }
+        if (g_device_pileup) {                       /* the slots' read arrays are allocated on first use: do it here */
+            ssn_batch *held[MAX_SLOTS];
+            ssn_reads_view rv;
+            int k, ok = 1;
+            for (k = 0; k < n_slots; ++k) ok = ok && ssn_batch_acquire(gpus[i].ctx, &held[k]) == SSN_OK && ssn_batch_reads_view(gpus[i].ctx, held[k], &rv) == SSN_OK;
+            if (!ok) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); ssn_packer_close(pk); return 1; }
+            for (k = 0; k < n_slots; ++k) ssn_batch_release(gpus[i].ctx, held[k]);
+        }
     }
     fprintf(stderr, "Preparing to snipe some somatics\n");
     if (use_priors) fprintf(stderr, "Using prior probabilities\n");

@@ -704,15 +704,15 @@ extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_
         CU(cudaMemcpyAsync(b->d_win, b->h_win, (size_t)n_windows * sizeof(ssn_read_window), cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(b->d_wref, b->h_wref, (size_t)n_windows * SSN_READ_WINDOW, cudaMemcpyHostToDevice, st));
         pileup::DevReads R;
-        R.recs = (const uint32_t*)b->d_recs; R.rec_off = b->d_rec_off; R.win = b->d_win; R.wref = b->d_wref; R.n_win = n_windows;
+        R.recs = (const uint32_t*)b->d_recs; R.rec_off = b->d_rec_off; R.win = b->d_win; R.wref = b->d_wref; R.n_win = n_windows; R.n_reads = n_reads; R.rec_words = (uint32_t)(rec_bytes >> 2);
         R.A = b->d_A; R.P = b->d_P; R.rbeg = b->d_rbeg; R.rinfo = b->d_rinfo; R.wspan = b->d_wspan; R.wtot = b->d_wtot; R.summary = b->d_summary;
         R.off = b->d_off; R.bs = b->d_bs; R.bq = b->d_bq; R.mq = b->d_mq; R.ref_nt16 = b->d_ref; R.colpos = b->d_colpos;
         R.max_columns = b->max_columns; R.max_entries = (uint32_t)std::min<uint64_t>(b->max_entries, 0xfffffff0ull);
         R.run_len = (uint32_t)kRunLen; R.max_runs = (uint32_t)kMaxRuns;
         const uint32_t npos = n_windows * SSN_READ_WINDOW;
         CU(cudaEventRecord(b->pa, st));
-        pileup::count_kernel<<<n_windows * 2, pileup::kThreads, 0, st>>>(R);
-        pileup::columns_kernel<<<n_windows, pileup::kThreads, 0, st>>>(R);
+        pileup::count_kernel<<<n_windows * 2, pileup::kScanThreads, 0, st>>>(R);
+        pileup::columns_kernel<<<n_windows, pileup::kScanThreads, 0, st>>>(R);
         pileup::bases_kernel<<<1, 32, 0, st>>>(R);
         pileup::offsets_kernel<<<npos / pileup::kThreads, pileup::kThreads, 0, st>>>(R);
         pileup::fill_kernel<<<npos / pileup::kThreads, pileup::kThreads, pileup::kFillSmem, st>>>(R);
@@ -735,6 +735,7 @@ static ssn_status finish_reads(ssn_ctx *ctx, ssn_batch *b)
     b->reads_pending = false;
     const uint32_t *S = b->h_summary;
     if (S[2]) {
+        if (S[2] & pileup::kErrRecord) { ssn_set_error("read batch: a record or its index entry points outside the record buffer"); return SSN_ERR_ARG; }
         if (S[2] & pileup::kErrUnsorted) { ssn_set_error("read batch: the reads of a window are not sorted by start"); return SSN_ERR_ARG; }
         if (S[2] & (pileup::kErrColumns | pileup::kErrEntries)) {
             ssn_set_error("read batch: %u columns / %u read-bases exceed the slot capacity %u / %llu", S[0], S[1], b->max_columns, (unsigned long long)b->max_entries);

@@ -30,16 +30,18 @@ namespace pileup {
 constexpr uint32_t kWin = SSN_READ_WINDOW;
 constexpr uint32_t kDead = 0xffffffffu;
 constexpr int kThreads = 256;
+constexpr int kScanThreads = 1024;           /* count / columns: one CTA per window (and sample), so make it a big one */
 constexpr int kRecWords = 5;                 /* sizeof(ssn_read_rec) / 4 */
 constexpr int kSummaryWords = 8;             /* [0] columns [1] entries [2] error bits [3] max tile words [4] max column words */
-constexpr uint32_t kErrUnsorted = 1u, kErrColumns = 2u, kErrEntries = 4u, kErrDepth = 8u;
+constexpr uint32_t kErrUnsorted = 1u, kErrColumns = 2u, kErrEntries = 4u, kErrDepth = 8u, kErrRecord = 16u;
+constexpr uint32_t kErrStop = kErrColumns | kErrEntries | kErrRecord;    /* nothing after the count kernel may run */
 
 struct DevReads {
     const uint32_t *recs;
     const uint32_t *rec_off;
     const ssn_read_window *win;
     const uint8_t *wref;
-    uint32_t n_win;
+    uint32_t n_win, n_reads, rec_words;
     /* work arrays of the slot */
     uint32_t *A;          /* [n_win][2][kWin]: depth -> entry cursor of the sample at that position (kDead: no column) */
     uint32_t *P;          /* [n_win][kWin]: column index inside the window */
@@ -65,12 +67,12 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane)
     return v;
 }
 
-/* Exclusive scan of kWin values held in shared memory (in place) by a CTA of kThreads threads; returns the total.
+/* Exclusive scan of kWin values held in shared memory (in place) by a CTA of kScanThreads threads; returns the total.
  * Each warp owns a contiguous chunk and walks it 32 values at a time (conflict-free). */
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t *v, uint32_t *wsum)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    constexpr int kWarps = kThreads / 32;
+    constexpr int kWarps = kScanThreads / 32;
     constexpr uint32_t chunk = kWin / kWarps;
     uint32_t sum = 0;
     for (uint32_t j = 0; j < chunk; j += 32) sum += v[warp * chunk + j + lane];
@@ -90,21 +92,28 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t *v, uint32_t *wsum)
     return total;
 }
 
-__global__ void __launch_bounds__(kThreads) count_kernel(DevReads R)
+__global__ void __launch_bounds__(kScanThreads) count_kernel(DevReads R)
 {
     __shared__ uint32_t diff[kWin];
-    __shared__ uint32_t wsum[kThreads / 32];
+    __shared__ uint32_t wsum[kScanThreads / 32];
     __shared__ uint32_t span_s, err_s;
     const uint32_t w = blockIdx.x >> 1, s = blockIdx.x & 1;
     const ssn_read_window W = R.win[w];
     const uint32_t first = W.rec_first[s], n = W.n_reads[s], lo = W.lo, hi = lo + kWin;
-    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) diff[i] = 0;
+    for (uint32_t i = threadIdx.x; i < kWin; i += kScanThreads) diff[i] = 0;
     if (threadIdx.x == 0) { span_s = 0; err_s = 0; }
     __syncthreads();
-    for (uint32_t r = threadIdx.x; r < n; r += kThreads) {
-        const uint32_t *rec = R.recs + R.rec_off[first + r];
+    for (uint32_t r = threadIdx.x; r < n; r += kScanThreads) {
+        /* the index and the records come from the caller: a record must lie inside the buffer before anything reads it */
+        const uint32_t ro = R.rec_off[first + r];
+        if (ro > R.rec_words || R.rec_words - ro < (uint32_t)kRecWords) { atomicOr(&err_s, 2u); continue; }
+        const uint32_t *rec = R.recs + ro;
         const int32_t beg = (int32_t)rec[0];
         const uint32_t n_cigar = rec[3] & 0xffffu;
+        {
+            const unsigned long long need = (unsigned long long)kRecWords + n_cigar + ((((unsigned long long)rec[2] + 1u) >> 1) + rec[2] + 3u) / 4u;
+            if (need > R.rec_words - ro) { atomicOr(&err_s, 2u); continue; }
+        }
         uint32_t x = (uint32_t)beg;
         for (uint32_t k = 0; k < n_cigar; ++k) {
             const uint32_t c = rec[kRecWords + k], op = c & 0xfu, l = c >> 4;
@@ -121,13 +130,13 @@ __global__ void __launch_bounds__(kThreads) count_kernel(DevReads R)
         R.rinfo[2 * (size_t)(first + r)] = make_uint4(R.rec_off[first + r], (uint32_t)beg, rec[2], rec[3]);
         R.rinfo[2 * (size_t)(first + r) + 1] = make_uint4(n_cigar ? rec[kRecWords] : 0u, x, 0u, 0u);
         atomicMax(&span_s, x - (uint32_t)beg);
-        if (r > 0 && (int32_t)R.recs[R.rec_off[first + r - 1]] > beg) err_s = 1u;
+        if (r > 0) { const uint32_t po = R.rec_off[first + r - 1]; if (po < R.rec_words && (int32_t)R.recs[po] > beg) atomicOr(&err_s, 1u); }
     }
     __syncthreads();
     /* depth = inclusive scan of the marks = exclusive scan + own mark */
     uint32_t *A = R.A + ((size_t)w * 2 + s) * kWin;
-    uint32_t own[kWin / kThreads];
-    constexpr uint32_t chunk = kWin / (kThreads / 32);
+    uint32_t own[kWin / kScanThreads];
+    constexpr uint32_t chunk = kWin / (kScanThreads / 32);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (uint32_t j = 0; j < chunk / 32; ++j) own[j] = diff[warp * chunk + j * 32 + lane];
@@ -137,29 +146,30 @@ __global__ void __launch_bounds__(kThreads) count_kernel(DevReads R)
     for (uint32_t j = 0; j < chunk / 32; ++j) A[warp * chunk + j * 32 + lane] = diff[warp * chunk + j * 32 + lane] + own[j];
     if (threadIdx.x == 0) {
         R.wspan[w * 2 + s] = span_s;
-        if (err_s) atomicOr(R.summary + 2, kErrUnsorted);
+        if (err_s & 1u) atomicOr(R.summary + 2, kErrUnsorted);
+        if (err_s & 2u) atomicOr(R.summary + 2, kErrRecord);
     }
 }
 
-__global__ void __launch_bounds__(kThreads) columns_kernel(DevReads R)
+__global__ void __launch_bounds__(kScanThreads) columns_kernel(DevReads R)
 {
     __shared__ uint32_t v[kWin];
-    __shared__ uint32_t wsum[kThreads / 32];
+    __shared__ uint32_t wsum[kScanThreads / 32];
     const uint32_t w = blockIdx.x;
     uint32_t *A0 = R.A + (size_t)w * 2 * kWin, *A1 = A0 + kWin;
     const uint8_t *ref = R.wref + (size_t)w * kWin;
-    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads)
+    for (uint32_t i = threadIdx.x; i < kWin; i += kScanThreads)
         v[i] = (A0[i] != 0u && A1[i] != 0u && ref[i] != 15) ? 1u : 0u;
     __syncthreads();
     const uint32_t ncol = block_excl_scan(v, wsum);
-    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) {
+    for (uint32_t i = threadIdx.x; i < kWin; i += kScanThreads) {
         const uint32_t ct = A0[i], cn = A1[i];
         R.P[(size_t)w * kWin + i] = v[i];
         v[i] = (ct != 0u && cn != 0u && ref[i] != 15) ? ct + cn : 0u;
     }
     __syncthreads();
     const uint32_t nent = block_excl_scan(v, wsum);
-    for (uint32_t i = threadIdx.x; i < kWin; i += kThreads) {
+    for (uint32_t i = threadIdx.x; i < kWin; i += kScanThreads) {
         const uint32_t ct = A0[i], cn = A1[i];
         const bool live = ct != 0u && cn != 0u && ref[i] != 15;
         A0[i] = live ? v[i] : kDead;
@@ -200,7 +210,7 @@ __global__ void __launch_bounds__(32) bases_kernel(DevReads R)
 
 __global__ void __launch_bounds__(kThreads) offsets_kernel(DevReads R)
 {
-    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    if (R.summary[2] & kErrStop) return;
     const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* w * kWin + i */
     const uint32_t w = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u);
     if (g < 16u) R.bq[(size_t)R.summary[1] + g] = 1;                /* the clean-tile check reads up to 16 bytes past the end */
@@ -224,6 +234,7 @@ __global__ void __launch_bounds__(kThreads) offsets_kernel(DevReads R)
  * stores to global memory run at the L2's partial-sector rate) and written out as whole 16-byte chunks.  A stretch
  * longer than kStage bytes (about 128 read-bases per column) is written directly. */
 constexpr uint32_t kStage = 4096;
+constexpr int kGroup = 4;
 constexpr size_t kFillSmem = (size_t)(kThreads / 32) * 3 * kStage;
 
 template <bool STAGED>
@@ -239,43 +250,63 @@ __device__ __forceinline__ void fill_sample(const DevReads &R, const ssn_read_wi
     const uint32_t r1 = lo;
     lo = 0; hi = r1;
     while (lo < hi) { const uint32_t m = (lo + hi) >> 1; if ((long long)rb[m] + span <= p0) lo = m + 1; else hi = m; }
-    /* per-read facts come from the compact rinfo array, one read ahead of their use: the only dependent loads left in
-     * an iteration are the base and the quality (and the CIGAR words after the first) */
+    /* Reads go in groups of kGroup: all their facts (compact rinfo array) are loaded together, then their CIGARs are
+     * walked, then all base and quality loads are issued, then the lanes append in file order — the loop is bound by
+     * load latency, so the loads of a group overlap instead of queueing behind one another. */
     const uint4 *info = R.rinfo + 2 * (size_t)first;
-    uint4 n0 = make_uint4(0u, 0u, 0u, 0u), n1 = n0;
-    if (lo < r1) { n0 = info[2 * (size_t)lo]; n1 = info[2 * (size_t)lo + 1]; }
-    for (uint32_t r = lo; r < r1; ++r) {
-        const uint4 i0 = n0, i1 = n1;
-        if (r + 1 < r1) { n0 = info[2 * (size_t)(r + 1)]; n1 = info[2 * (size_t)(r + 1) + 1]; }
-        if (i1.y <= up0) continue;                                       /* ends before the warp's first position */
-        const uint32_t *rec = R.recs + i0.x;
-        const uint32_t l_qseq = i0.z, meta = i0.w, n_cigar = meta & 0xffffu;
-        uint32_t x = i0.y, y = 0, c = i1.x;
-        bool hit = false, done = false;
-        for (uint32_t k = 0; k < n_cigar; ++k) {
-            if (k) c = rec[kRecWords + k];
-            const uint32_t op = c & 0xfu, l = c >> 4;
-            if (done) continue;
+    for (uint32_t r = lo; r < r1; r += kGroup) {
+        uint4 i0[kGroup], i1[kGroup];
+#pragma unroll
+        for (int j = 0; j < kGroup; ++j) {
+            const uint32_t rr = min(r + j, r1 - 1u);
+            i0[j] = info[2 * (size_t)rr]; i1[j] = info[2 * (size_t)rr + 1];
+        }
+        uint32_t y[kGroup];
+        bool hit[kGroup];
+#pragma unroll
+        for (int j = 0; j < kGroup; ++j) {
+            const uint32_t n_cigar = i0[j].w & 0xffffu;
+            uint32_t x = i0[j].y, c = i1[j].x;
+            y[j] = 0; hit[j] = false;
             /* up - x < l  <=>  x <= up < x + l (a lane whose position lies before the read never satisfies it) */
-            if (op == 0u) {
-                if (up - x < l) { y += up - x; hit = true; done = true; }
-                else { x += l; y += l; }
-            } else if (op == 2u || op == 3u) {
-                if (up - x < l) done = true;
-                else x += l;
-            } else if (op == 1u || op == 4u) y += l;
+            if (n_cigar == 1u) {
+                if ((c & 0xfu) == 0u && up - x < (c >> 4)) { y[j] = up - x; hit[j] = true; }
+            } else {
+                const uint32_t *rec = R.recs + i0[j].x;
+                bool done = false;
+                for (uint32_t k = 0; k < n_cigar; ++k) {
+                    if (k) c = rec[kRecWords + k];
+                    const uint32_t op = c & 0xfu, l = c >> 4;
+                    if (done) continue;
+                    if (op == 0u) {
+                        if (up - x < l) { y[j] += up - x; hit[j] = true; done = true; }
+                        else { x += l; y[j] += l; }
+                    } else if (op == 2u || op == 3u) {
+                        if (up - x < l) done = true;
+                        else x += l;
+                    } else if (op == 1u || op == 4u) y[j] += l;
+                }
+            }
+            hit[j] = hit[j] && live && r + j < r1;
         }
-        if (!(hit && live)) continue;
-        const uint8_t strand = (uint8_t)(((meta >> 24) & 0xffu) << 4), mapq = (uint8_t)((meta >> 16) & 0xffu);
-        const uint8_t *seq = (const uint8_t*)(rec + kRecWords + n_cigar), *qual = seq + ((l_qseq + 1u) >> 1);
-        uint8_t b = (uint8_t)(15u | strand), q = 0;
-        if (y < l_qseq) {                                                /* else: CIGAR longer than the read */
-            b = (uint8_t)(((seq[y >> 1] >> ((~y & 1u) << 2)) & 0xfu) | strand);
-            q = qual[y];
+        uint8_t sb[kGroup], qq[kGroup];
+#pragma unroll
+        for (int j = 0; j < kGroup; ++j) {
+            const uint32_t n_cigar = i0[j].w & 0xffffu, l_qseq = i0[j].z;
+            const uint8_t *seq = (const uint8_t*)(R.recs + i0[j].x + kRecWords + n_cigar), *qual = seq + ((l_qseq + 1u) >> 1);
+            sb[j] = 0xff; qq[j] = 0;                                      /* CIGAR longer than the read: N, quality 0 */
+            if (hit[j] && y[j] < l_qseq) { sb[j] = seq[y[j] >> 1]; qq[j] = qual[y[j]]; }
         }
-        if (STAGED) { sm[cur] = b; sm[kStage + cur] = q; sm[2 * kStage + cur] = mapq; }
-        else { R.bs[cur] = b; R.bq[cur] = q; R.mq[cur] = mapq; }
-        ++cur;
+#pragma unroll
+        for (int j = 0; j < kGroup; ++j) {
+            if (!hit[j]) continue;
+            const uint32_t meta = i0[j].w;
+            const uint8_t strand = (uint8_t)(((meta >> 24) & 0xffu) << 4), mapq = (uint8_t)((meta >> 16) & 0xffu);
+            const uint8_t b = (uint8_t)(((sb[j] >> ((~y[j] & 1u) << 2)) & 0xfu) | strand);
+            if (STAGED) { sm[cur] = b; sm[kStage + cur] = qq[j]; sm[2 * kStage + cur] = mapq; }
+            else { R.bs[cur] = b; R.bq[cur] = qq[j]; R.mq[cur] = mapq; }
+            ++cur;
+        }
     }
 }
 
@@ -292,7 +323,7 @@ __device__ __forceinline__ void flush_stage(uint8_t *g, const uint8_t *sm, uint3
 __global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
 {
     extern __shared__ __align__(16) uint8_t fill_stage[];
-    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    if (R.summary[2] & kErrStop) return;
     const uint32_t g = blockIdx.x * kThreads + threadIdx.x;        /* w * kWin + i */
     const uint32_t w = g >> SSN_READ_WINDOW_SHIFT, i = g & (kWin - 1u), lane = threadIdx.x & 31u;
     if (w >= R.n_win) return;
@@ -323,7 +354,7 @@ __global__ void __launch_bounds__(kThreads) fill_kernel(DevReads R)
 /* what scan_offsets (ssn_api.cu) computes on the host for packed batches */
 __global__ void __launch_bounds__(kThreads) shape_kernel(DevReads R)
 {
-    if (R.summary[2] & (kErrColumns | kErrEntries)) return;
+    if (R.summary[2] & kErrStop) return;
     const uint32_t ncol = R.summary[0];
     const uint32_t t = (blockIdx.x * kThreads + threadIdx.x) * 32u;
     if (t >= ncol) return;

@@ -112,6 +112,15 @@ def test_device_pileup_errors(built):
     if w[o[0]] != w[o[5]]:
         with pytest.raises(api.SsnError, match="not sorted"):
             device_pileup(api, bad)
+    # an index entry past the buffer, a record whose sequence would run past it
+    bad = dict(rw, rec_off=rw["rec_off"].copy())
+    bad["rec_off"][3] = rw["recs"].size // 4 + 7
+    with pytest.raises(api.SsnError, match="outside the record buffer"):
+        device_pileup(api, bad)
+    bad = dict(rw, recs=rw["recs"].copy())
+    bad["recs"].view("<u4")[rw["rec_off"][-1] + 2] = 1 << 30
+    with pytest.raises(api.SsnError, match="outside the record buffer"):
+        device_pileup(api, bad)
     sc = api.Scorer(n_slots=1)
     b = sc.acquire()
     with pytest.raises(api.SsnError, match="ssn_reads_reserve"):

@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--repeat", type=int, default=3)
     ap.add_argument("--no-reference", action="store_true")
     ap.add_argument("--threads", default=None)
+    ap.add_argument("--device-pileup", action="store_true", help="SSN_DEVICE_PILEUP=1: ship the reads, build the columns on the GPU")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     w = tempfile.mkdtemp(prefix="ssn_bench_")
@@ -26,7 +27,9 @@ def main():
     pair = ct.make_pair(w, contigs, a.depth_t, a.depth_n, seed=1234, n_runs=0, special=True)
     t_sim = time.perf_counter() - t0
     opts = shlex.split(a.args)
-    env = {"SSN_THREADS": a.threads} if a.threads else None
+    env = {"SSN_THREADS": a.threads} if a.threads else {}
+    if a.device_pileup:
+        env["SSN_DEVICE_PILEUP"] = 1
     runs = []
     for i in range(a.repeat):
         mine = os.path.join(w, "mine.out")
