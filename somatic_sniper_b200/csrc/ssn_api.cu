@@ -72,9 +72,12 @@ struct ssn_batch {
     uint32_t n_sites;
     /* read batch: the device builds the columns (ssn_pileup.cuh) */
     bool reads_alloc, reads_pending, from_reads;
+    bool spec;                /* scored speculatively from the device-side column count (submit_reads) */
+    uint32_t spec_col_words;
     uint32_t n_win;
-    uint8_t *h_recs; uint32_t *h_rec_off; ssn_read_window *h_win; uint8_t *h_wref; uint32_t *h_summary, *h_colpos;
-    uint8_t *d_recs; uint32_t *d_rec_off; ssn_read_window *d_win; uint8_t *d_wref;
+    uint8_t *h_recs, *h_index; uint32_t *h_rec_off; ssn_read_window *h_win; uint8_t *h_wref; uint32_t *h_summary, *h_colpos;   /* h_index owns win/wref/rec_off */
+    size_t index_off_bytes;
+    uint8_t *d_recs, *d_index; uint32_t *d_rec_off; ssn_read_window *d_win; uint8_t *d_wref;
     uint32_t *d_A, *d_P, *d_wspan, *d_summary, *d_colpos; int32_t *d_rbeg; uint4 *d_rinfo; uint2 *d_wtot;
     cudaEvent_t piled, pa, pb;
 };
@@ -184,9 +187,9 @@ static void slot_free(ssn_batch *b)
     cudaFreeHost(b->h_ref); cudaFreeHost(b->h_count); cudaFreeHost(b->h_sites); cudaFreeHost(b->h_dump);
     cudaFree(b->d_off); cudaFree(b->d_bs); cudaFree(b->d_bq); cudaFree(b->d_mq); cudaFree(b->d_ref);
     cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump); cudaFree(b->d_survivors);
-    cudaFreeHost(b->h_recs); cudaFreeHost(b->h_rec_off); cudaFreeHost(b->h_win); cudaFreeHost(b->h_wref);
+    cudaFreeHost(b->h_recs); cudaFreeHost(b->h_index);
     cudaFreeHost(b->h_summary); cudaFreeHost(b->h_colpos);
-    cudaFree(b->d_recs); cudaFree(b->d_rec_off); cudaFree(b->d_win); cudaFree(b->d_wref); cudaFree(b->d_A); cudaFree(b->d_P);
+    cudaFree(b->d_recs); cudaFree(b->d_index); cudaFree(b->d_A); cudaFree(b->d_P);
     cudaFree(b->d_wspan); cudaFree(b->d_summary); cudaFree(b->d_colpos); cudaFree(b->d_rbeg); cudaFree(b->d_rinfo); cudaFree(b->d_wtot);
     if (b->piled) cudaEventDestroy(b->piled);
     if (b->pa) cudaEventDestroy(b->pa);
@@ -372,7 +375,7 @@ extern "C" ssn_status ssn_batch_acquire(ssn_ctx *ctx, ssn_batch **out)
     }
     if (!pick) { ssn_set_error("ssn_batch_acquire: all %zu slots are in flight; drain ssn_results_next first", ctx->slots.size()); return SSN_ERR_STATE; }
     pick->state = SLOT_FILLING; pick->ncol = 0; pick->nent = 0; pick->resident = false; pick->n_sites = 0;
-    pick->reads_pending = false; pick->from_reads = false;
+    pick->reads_pending = false; pick->from_reads = false; pick->spec = false;
     *out = pick;
     return SSN_OK;
 }
@@ -527,6 +530,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.scratch = tile_words > words ? ctx->d_scratch : nullptr;
     B.scratch_words_per_warp = (uint32_t)(((size_t)tile_words + 63) / 64 * 64);
     B.smem_words_per_warp = words;
+    B.dev_ncol = b->spec ? b->d_summary : nullptr; B.guard = b->spec ? b->d_summary : nullptr; B.guard_col_words = b->spec_col_words;
     B.collist = listed ? b->d_survivors : nullptr;
     B.list_count = b->d_count + 2;
     { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 4 || w == 8 || w == 16) ? (uint32_t)w : list_width; }
@@ -635,15 +639,16 @@ static ssn_status reads_alloc(ssn_ctx *ctx, ssn_batch *b)
     const size_t nb = ctx->reads_cap_bytes, nr = ctx->reads_cap_reads, nw = ctx->reads_cap_windows;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMallocHost(&b->h_recs, nb));
-    CU(cudaMallocHost(&b->h_rec_off, nr * 4));
-    CU(cudaMallocHost(&b->h_win, nw * sizeof(ssn_read_window)));
-    CU(cudaMallocHost(&b->h_wref, nw * SSN_READ_WINDOW));
+    /* window table, reference slices and record index share one block (one copy per batch): [win][wref][rec_off] */
+    const size_t o_wref = (nw * sizeof(ssn_read_window) + 255) & ~(size_t)255, o_off = o_wref + nw * SSN_READ_WINDOW;
+    b->index_off_bytes = o_off;
+    CU(cudaMallocHost(&b->h_index, o_off + nr * 4));
+    b->h_win = (ssn_read_window*)b->h_index; b->h_wref = b->h_index + o_wref; b->h_rec_off = (uint32_t*)(b->h_index + o_off);
     CU(cudaMallocHost(&b->h_summary, pileup::kSummaryWords * 4));
     CU(cudaMallocHost(&b->h_colpos, (size_t)b->max_columns * 4));
     CU(cudaMalloc(&b->d_recs, nb));
-    CU(cudaMalloc(&b->d_rec_off, nr * 4));
-    CU(cudaMalloc(&b->d_win, nw * sizeof(ssn_read_window)));
-    CU(cudaMalloc(&b->d_wref, nw * SSN_READ_WINDOW));
+    CU(cudaMalloc(&b->d_index, o_off + nr * 4));
+    b->d_win = (ssn_read_window*)b->d_index; b->d_wref = b->d_index + o_wref; b->d_rec_off = (uint32_t*)(b->d_index + o_off);
     CU(cudaMalloc(&b->d_A, nw * 2 * SSN_READ_WINDOW * 4));
     CU(cudaMalloc(&b->d_P, nw * SSN_READ_WINDOW * 4));
     CU(cudaMalloc(&b->d_wspan, nw * 2 * 4));
@@ -700,9 +705,7 @@ extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_
     CU(cudaMemsetAsync(b->d_summary, 0, pileup::kSummaryWords * 4, st));
     if (n_windows) {
         CU(cudaMemcpyAsync(b->d_recs, b->h_recs, rec_bytes, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(b->d_rec_off, b->h_rec_off, (size_t)n_reads * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(b->d_win, b->h_win, (size_t)n_windows * sizeof(ssn_read_window), cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(b->d_wref, b->h_wref, (size_t)n_windows * SSN_READ_WINDOW, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(b->d_index, b->h_index, b->index_off_bytes + (size_t)n_reads * 4, cudaMemcpyHostToDevice, st));
         pileup::DevReads R;
         R.recs = (const uint32_t*)b->d_recs; R.rec_off = b->d_rec_off; R.win = b->d_win; R.wref = b->d_wref; R.n_win = n_windows; R.n_reads = n_reads; R.rec_words = (uint32_t)(rec_bytes >> 2);
         R.A = b->d_A; R.P = b->d_P; R.rbeg = b->d_rbeg; R.rinfo = b->d_rinfo; R.wspan = b->d_wspan; R.wtot = b->d_wtot; R.summary = b->d_summary;
@@ -725,6 +728,23 @@ extern "C" ssn_status ssn_batch_submit_reads(ssn_ctx *ctx, ssn_batch *b, uint32_
     CU(cudaEventRecord(b->piled, st));
     b->reads_pending = true;
     b->state = SLOT_SUBMITTED; b->seq = ctx->next_seq++;
+    /* Product path (pre-filter + survivors, no dump): queue the scoring now, from the column count the device holds.
+     * The launch assumes no column outgrows the shared-memory key store; the kernels check that (and the pileup's
+     * error bits) against the summary and do nothing otherwise — finish_reads then launches with the real shape. */
+    /* Measured on B200: with few slots (the CLI's 3) the early launch hides the scoring behind the next batch's copy
+     * (streaming +10 %); with 8 slots saturating PCIe it costs 6 % of the copy rate, so scoring then waits for
+     * ssn_results_next.  SSN_READS_LAZY_SCORE=0|1 forces either (measurement knob). */
+    static const int lazy_env = getenv("SSN_READS_LAZY_SCORE") ? atoi(getenv("SSN_READS_LAZY_SCORE")) : -1;
+    const bool lazy = lazy_env >= 0 ? lazy_env != 0 : ctx->slots.size() > 4;
+    if (n_windows && !lazy && ctx->pf_on && !(flags & (SSN_SUBMIT_NO_PREFILTER | SSN_SUBMIT_COLUMN_DUMP))) {
+        b->spec = true; b->spec_col_words = ctx->smem_words_default / 32u;
+        b->ncol = (uint32_t)std::min<uint64_t>((uint64_t)n_windows * SSN_READ_WINDOW, b->max_columns);
+        b->max_col_words = b->spec_col_words; b->max_tile_words = 0;
+        ssn_status rc = launch(ctx, b, flags);
+        if (rc != SSN_OK) return rc;
+        CU(cudaMemcpyAsync(b->h_colpos, b->d_colpos, (size_t)b->ncol * 4, cudaMemcpyDeviceToHost, st));
+        if ((rc = copy_out_async(b)) != SSN_OK) return rc;
+    }
     return SSN_OK;
 }
 
@@ -751,6 +771,8 @@ static ssn_status finish_reads(ssn_ctx *ctx, ssn_batch *b)
     }
     b->ncol = S[0]; b->nent = S[1]; b->max_tile_words = S[3]; b->max_col_words = S[4];
     b->resident = true;
+    if (b->spec && S[4] <= b->spec_col_words) return SSN_OK;      /* already scored; the copies back are queued */
+    b->spec = false;
     ssn_status st = launch(ctx, b, b->flags);
     if (st != SSN_OK) return st;
     if (b->ncol) CU(cudaMemcpyAsync(b->h_colpos, b->d_colpos, (size_t)b->ncol * 4, cudaMemcpyDeviceToHost, b->stream));
@@ -800,7 +822,11 @@ extern "C" ssn_status ssn_results_next(ssn_ctx *ctx, const ssn_site **sites, uin
     if (!pick) { ssn_set_error("ssn_results_next: nothing submitted"); return SSN_ERR_STATE; }
     CU(cudaSetDevice(ctx->device));
     ssn_status st = SSN_OK;
-    if (pick->reads_pending && (st = finish_reads(ctx, pick)) != SSN_OK) return st;
+    if (pick->reads_pending && (st = finish_reads(ctx, pick)) != SSN_OK) {
+        pick->state = SLOT_DONE; pick->n_sites = 0;        /* the batch is over: the caller may release it and go on */
+        if (batch) *batch = pick;
+        return st;
+    }
     if ((st = collect(ctx, pick)) != SSN_OK) return st;
     pick->state = SLOT_DONE;
     *sites = pick->h_sites; *n_sites = pick->n_sites;

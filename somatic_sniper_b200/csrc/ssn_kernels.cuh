@@ -112,7 +112,14 @@ struct DevBatch {
     const uint32_t *collist;
     const uint32_t *list_count;
     uint32_t list_width;    /* 0: pick the tile width from the list length; else 4, 8 or 16 */
+    /* batches built on the device (ssn_pileup.cuh) are scored before the host knows their shape: ncol is then an upper
+     * bound and the true count is read here; the kernels do nothing when the pileup's summary reports an error or a
+     * column deeper than the launch assumed (the host then launches again with the real shape) */
+    const uint32_t *dev_ncol;
+    const uint32_t *guard;          /* pileup summary: [2] error bits, [4] key-store words of the deepest column */
+    uint32_t guard_col_words;
 };
+constexpr uint32_t kGuardStop = 2u | 4u | 16u;   /* pileup::kErrStop */
 
 /* -------------------------------------------------------------------------------------------- */
 /* key construction (sniper_maqcns.c:144-156 + the :165 promotion rule folded in)              */
@@ -878,9 +885,11 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
     /* list mode: few columns, gathered from anywhere in the batch.  Narrow tiles (W columns per warp) spread them over
      * every resident warp; the lanes past W idle.  Gathered columns are not contiguous, so they take the generic path. */
     const bool listed = B.collist != nullptr;
-    uint32_t ncols = B.ncol, W = 32u;
+    if (B.guard && ((B.guard[2] & kGuardStop) || B.guard[4] > B.guard_col_words)) return;
+    const uint32_t batch_ncol = B.dev_ncol ? min(*B.dev_ncol, B.ncol) : B.ncol;
+    uint32_t ncols = batch_ncol, W = 32u;
     if (listed) {
-        ncols = min(*B.list_count, B.ncol);
+        ncols = min(*B.list_count, batch_ncol);
         const uint32_t warps = gridDim.x * (uint32_t)kWarpsPerCta, per = (ncols + warps - 1u) / warps;
         W = 4u;
         while (W < per && W < (uint32_t)kListWidth) W <<= 1;

@@ -155,6 +155,7 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
     __shared__ PfShared T;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (B.guard && (B.guard[2] & kGuardStop)) return;                           /* the device pileup refused the batch */
     for (int i = threadIdx.x; i < 257; i += blockDim.x) T.F[i] = P.F[i];
     const uint32_t mbar_s = smem_u32(&T.mbar[warp]);
     if (lane == 0) {
@@ -163,7 +164,8 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
     }
     __syncthreads();
     const uint32_t raw_s = smem_u32(smem_raw + (size_t)warp * kPfStageBytes);
-    const uint32_t ntiles = (B.ncol + 31u) >> 5;
+    const uint32_t ncol = B.dev_ncol ? min(*B.dev_ncol, B.ncol) : B.ncol;      /* device-built batch: the count lives on the device */
+    const uint32_t ntiles = (ncol + 31u) >> 5;
     uint32_t phase = 0;
 
     /* software pipeline over tiles: the tile index for the tile after next is being claimed (atomic in flight) and the
@@ -172,7 +174,7 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
     auto load_hdr = [&](uint32_t t, Hdr &h) {
         const uint32_t c = t * 32u + lane;
         h.o0 = h.o1 = h.o2 = 0u; h.ref16 = 15u;
-        if (t < ntiles && c < B.ncol) {
+        if (t < ntiles && c < ncol) {
             h.o0 = B.off[2 * c]; h.o1 = B.off[2 * c + 1]; h.o2 = B.off[2 * c + 2];
             h.ref16 = B.ref_nt16[c] & 15u;
         }
@@ -186,7 +188,7 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
 
     while (tile < ntiles) {
         const uint32_t col = tile * 32u + lane;
-        const bool live = col < B.ncol;
+        const bool live = col < ncol;
         const uint32_t o0 = cur.o0, o1 = cur.o1, o2 = cur.o2, ref16 = cur.ref16;
         const uint32_t nT = o1 - o0, nN = o2 - o1;
         /* a column can only reach the output with read-bases in both samples and a called reference (somatic_sniper.c:127,156) */

@@ -129,19 +129,21 @@ def test_device_pileup_errors(built):
 
 
 @pytest.mark.gpu
-def test_device_pileup_pipeline_of_batches(built):
-    """Several read batches in flight on their slot streams; results come back in submission order."""
+@pytest.mark.parametrize("n_slots", [3, 6])
+def test_device_pileup_pipeline_of_batches(built, n_slots):
+    """Several read batches in flight on their slot streams; results come back in submission order.  Up to 4 slots the
+    scoring kernels are queued with the pileup (from the device-side column count), beyond that when the batch is drained."""
     from somatic_sniper_b200 import api, hostapi
     batches = []
     for k in range(5):
         ref, t, n = make_case(seed=30 + k, length=6000 + 500 * k, depth_t=20, depth_n=12, complex_cigars=bool(k & 1))
         rw = R.build_read_windows(t, n, ref)
         batches.append((rw, hostapi.pack_read_windows(rw)))
-    sc = api.Scorer(n_slots=3, max_columns=2 * 8192, max_entries=1 << 20)
+    sc = api.Scorer(n_slots=n_slots, max_columns=2 * 8192, max_entries=1 << 20)
     sc.reads_reserve(max(rw["recs"].size for rw, _ in batches) + 64, max(rw["rec_off"].size for rw, _ in batches) + 1, 2)
     pending, done = [], []
     for rw, want in batches:
-        if len(pending) == 3:
+        if len(pending) == min(n_slots, 3):
             sites, _ = sc.results_next()
             b0, want0 = pending.pop(0)
             same_columns(sc.download_columns(b0), want0)
