@@ -70,11 +70,9 @@ __device__ __forceinline__ int pass_quality_class(uint32_t raw_s, uint32_t bytes
     return __any_sync(kFull, (zero & 0x80808080u) != 0u) ? 1 : 0;
 }
 
-/* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.
- * C = tile-uniform number of 4-read-base chunks; R4 = the reference's nt16 code in every byte. */
 struct PfAcc { uint32_t m, n1, S, qref, q1, z; };
 
-/* four read-bases of one sample: BSr/BQr/MQr = the aligned words, keep = live-byte mask (MASKED) */
+/* four read-bases of one sample: BSr/BQr/MQr = one word of each array, keep = live-byte mask (MASKED) */
 template <bool ZEROS, bool MASKED>
 __device__ __forceinline__ void pf_chunk(uint32_t BSr, uint32_t BQr, uint32_t MQr, uint32_t keep, uint32_t R4, PfAcc &A)
 {
@@ -102,33 +100,35 @@ __device__ __forceinline__ void pf_chunk(uint32_t BSr, uint32_t BQr, uint32_t MQ
     A.q1 = __dp4a(q & RV, ones, A.q1);
 }
 
-/* One sample of this lane's column: len staged read-bases starting at byte r of each staged array.  C = tile-uniform
- * number of 4-read-base chunks, Cfull = tile-uniform number of leading chunks that are completely live in every lane
- * that matters (no masking there).  R4 = the reference's nt16 code in every byte. */
+/* One sample of this lane's column: len staged read-bases starting at byte r of each staged array (len = 0 in lanes
+ * outside the pass: mine = false).  The sums do not care where in a word a read-base sits, and the three arrays share
+ * their offsets, so the words are taken as they lie — no re-alignment: the sample's first word and its last ones are
+ * masked, the words that are completely live in every column of the pass are not.  R4 = the reference's nt16 code in
+ * every byte. */
 template <bool ZEROS>
-__device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, int C, int Cfull, uint32_t R4, PfStats &st)
+__device__ __forceinline__ void pf_sample(uint32_t raw_s, uint32_t r, uint32_t len, bool mine, uint32_t R4, PfStats &st)
 {
-    const uint32_t a = raw_s + (r & ~3u), sh = (r & 3u) * 8u;
-    uint32_t ws = lds_u32(a), wq = lds_u32(a + kRawBytes), wm = lds_u32(a + 2 * kRawBytes);
+    const uint32_t a = raw_s + (r & ~3u), h = r & 3u, total = h + len;
+    const int C = (int)__reduce_max_sync(kFull, mine ? (total + 3u) >> 2 : 0u);
+    const int Cfull = ZEROS ? 0 : (int)__reduce_min_sync(kFull, mine ? total >> 2 : 0xffffu);
     PfAcc A = {0u, 0u, 0u, 0u, 0u, 0u};
-    int c = 0;
+    {
+        const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, min(total, 4u) * 8u) & ~__funnelshift_lc(0xffffffffu, 0u, h * 8u);
+        pf_chunk<ZEROS, true>(lds_u32(a), lds_u32(a + kRawBytes), lds_u32(a + 2 * kRawBytes), keep, R4, A);
+    }
+    int c = 1;
     if (!ZEROS) {
 #pragma unroll 2
-        for (; c < Cfull; ++c) {
-            const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
-            pf_chunk<false, false>(__funnelshift_r(ws, ns, sh), __funnelshift_r(wq, nq, sh), __funnelshift_r(wm, nm, sh), 0xffffffffu, R4, A);
-            ws = ns; wq = nq; wm = nm;
-        }
+        for (; c < Cfull; ++c)
+            pf_chunk<false, false>(lds_u32(a + 4 * c), lds_u32(a + kRawBytes + 4 * c), lds_u32(a + 2 * kRawBytes + 4 * c), 0xffffffffu, R4, A);
     }
-    uint32_t bits = len * 8u;                      /* live bits left in this sample */
+    uint32_t bits = total * 8u;                    /* live bits from word c on */
     bits = max(bits, 32u * (uint32_t)c) - 32u * (uint32_t)c;
 #pragma unroll 2
     for (; c < C; ++c) {
-        const uint32_t ns = lds_u32(a + 4 * (c + 1)), nq = lds_u32(a + kRawBytes + 4 * (c + 1)), nm = lds_u32(a + 2 * kRawBytes + 4 * (c + 1));
         const uint32_t keep = __funnelshift_lc(0xffffffffu, 0u, bits);          /* low min(bits,32) bits */
         bits = max(bits, 32u) - 32u;
-        pf_chunk<ZEROS, true>(__funnelshift_r(ws, ns, sh), __funnelshift_r(wq, nq, sh), __funnelshift_r(wm, nm, sh), keep, R4, A);
-        ws = ns; wq = nq; wm = nm;
+        pf_chunk<ZEROS, true>(lds_u32(a + 4 * c), lds_u32(a + kRawBytes + 4 * c), lds_u32(a + 2 * kRawBytes + 4 * c), keep, R4, A);
     }
     st.m = A.m / 255u; st.n1 = A.n1 / 255u; st.z = A.z / 255u;
     st.S = A.S; st.qref = A.qref; st.q1 = A.q1;
@@ -215,7 +215,6 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
                 const uint32_t bytes = (__shfl_sync(kFull, o2, (int)last - 1) - a0 + 15u) & ~15u;
                 if (lane == 0) stage_issue(B, raw_s, mbar_s, a0, bytes);
                 const uint32_t lT = mine ? nT : 0u, lN = mine ? nN : 0u;
-                const uint32_t maxT = __reduce_max_sync(kFull, lT), maxN = __reduce_max_sync(kFull, lN);
                 stage_wait(mbar_s, phase);
                 phase ^= 1u;
                 const int qc = pass_quality_class(raw_s, bytes, lane);
@@ -223,15 +222,14 @@ ssn_prefilter_kernel(const DevPrefilter P, const DevBatch B, uint32_t *survivors
                     const uint32_t r0 = mine ? o0 - a0 : 0u;
                     const uint32_t R4 = ref16 * 0x01010101u;
                     PfStats sT, sN;
-                    /* leading chunks that are fully live in every column of the pass need no masks; the lanes outside
-                     * the pass run them on whatever is staged and their sums are thrown away below */
-                    const int fullT = (int)(__reduce_min_sync(kFull, mine ? nT : 0xffffu) >> 2), fullN = (int)(__reduce_min_sync(kFull, mine ? nN : 0xffffu) >> 2);
+                    /* words that are fully live in every column of the pass need no masks; the lanes outside the pass
+                     * run them on whatever is staged and their sums are thrown away below */
                     if (qc == 0) {
-                        pf_sample<false>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), fullT, R4, sT);
-                        pf_sample<false>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), fullN, R4, sN);
+                        pf_sample<false>(raw_s, r0, lT, mine, R4, sT);
+                        pf_sample<false>(raw_s, r0 + lT, lN, mine, R4, sN);
                     } else {
-                        pf_sample<true>(raw_s, r0, lT, (int)((maxT + 3u) >> 2), 0, R4, sT);
-                        pf_sample<true>(raw_s, r0 + lT, lN, (int)((maxN + 3u) >> 2), 0, R4, sN);
+                        pf_sample<true>(raw_s, r0, lT, mine, R4, sT);
+                        pf_sample<true>(raw_s, r0 + lT, lN, mine, R4, sN);
                     }
                     if (!mine) { sT.m = sT.S = sT.n1 = sT.qref = sT.q1 = sT.z = 0u; sN = sT; }
                     /* both samples' table lookups are issued together (no short-circuit): lT/lN are 0 outside the pass */
