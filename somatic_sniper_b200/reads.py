@@ -35,12 +35,18 @@ def make_reads(seed, ref, depth, read_len=150, start=0, length=None, complex_cig
     length = len(ref) - start if length is None else length
     n = max(1, int(depth * length / read_len))
     beg = np.sort(rng.integers(max(0, start - read_len + 1), start + length, n)).astype(np.int32)
-    kind = rng.integers(0, 10, n) if complex_cigars else np.zeros(n, np.int64)
+    kind = rng.integers(0, 10, n) if complex_cigars is True else np.zeros(n, np.int64)
     a = rng.integers(10, read_len - 20, n)
     cigs, lq = [], np.zeros(n, np.uint32)
     for i in range(n):
         k, L, x = int(kind[i]), read_len, int(a[i])
-        if k == 1:
+        if complex_cigars == "random":
+            # any operator, any order, lengths from 0: what a hostile or merely odd BAM can hold
+            ops = rng.integers(0, 9, int(rng.integers(1, 9)))
+            c = [(int(op), int(rng.integers(0, 41))) for op in ops]
+            k = 7 if rng.random() < 0.3 else -1          # l_qseq unrelated to the CIGAR in 30 % of the reads
+            L = int(rng.integers(0, 120))
+        elif k == 1:
             c = [(OP_S, 5), (OP_M, L - 5)]
         elif k == 2:
             c = [(OP_M, x), (OP_I, 3), (OP_M, L - x - 3)]
@@ -127,6 +133,12 @@ def build_read_windows(tumor, normal, ref, tid=0, first_window=None, n_windows=N
     beg, mapq, strand, lq = f("beg", np.int64), f("mapq", np.int64), f("strand", np.int64), f("l_qseq", np.int64)
     end = np.concatenate(ends)
     ncig = np.concatenate([np.diff(s["cig_off"]) for s in samples]).astype(np.int64)
+    mlen = []                                              # read-bases a read can add: the length of its M runs
+    for s in samples:
+        m = np.where((s["cig"] & 0xf) == OP_M, (s["cig"] >> 4).astype(np.int64), 0)
+        cs = np.concatenate([[0], np.cumsum(m)])
+        mlen.append(cs[s["cig_off"][1:]] - cs[s["cig_off"][:-1]])
+    mlen = np.concatenate(mlen)
     cig_start = np.concatenate([samples[0]["cig_off"][:-1], samples[1]["cig_off"][:-1] + samples[0]["cig"].size])
     cig = np.concatenate([samples[0]["cig"], samples[1]["cig"]])
     packed, poff, plen = [], [], []
@@ -167,7 +179,7 @@ def build_read_windows(tumor, normal, ref, tid=0, first_window=None, n_windows=N
     lo0 = first_window << W_SHIFT
     seg = ref[lo0:lo0 + n_windows * READ_WINDOW]
     wref.reshape(-1)[:seg.size] = seg
-    return dict(recs=recs, rec_off=wo.astype(np.uint32), win=win, ref_nt16=wref, entries_bound=int(lq[g].sum()) + 64)
+    return dict(recs=recs, rec_off=wo.astype(np.uint32), win=win, ref_nt16=wref, entries_bound=int(np.maximum(lq, mlen)[g].sum()) + 64)
 
 
 def pileup_numpy(tumor, normal, ref, first_window, n_windows):

@@ -31,6 +31,8 @@ CASES = {
     "window edge": dict(seed=3, length=2500, depth_t=5, depth_n=5, complex_cigars=True, start=8192 - 1200),
     "second window, quality 0": dict(seed=4, length=2000, depth_t=4, depth_n=7, complex_cigars=True, start=3 * 8192 + 17, q0=0.05),
     "sparse normal": dict(seed=5, length=4000, depth_t=5, depth_n=0.3, complex_cigars=True),
+    "random cigars": dict(seed=6, length=3000, depth_t=12, depth_n=9, complex_cigars="random", start=8192 - 1500),
+    "random cigars, quality 0": dict(seed=7, length=2500, depth_t=9, depth_n=14, complex_cigars="random", q0=0.1),
 }
 
 
