@@ -175,7 +175,14 @@ static void window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar
     memcpy(d, qual, nq);
     w->len += h->bytes;
     w->n_reads += 1;
-    w->n_bases += h->l_qseq;
+    {
+        /* upper bound of the read-bases this record can add to the window: its M runs, which a malformed record may
+         * stretch past the end of the read (such positions become N bases of quality 0) */
+        uint64_t m = 0;
+        uint32_t k, c;
+        for (k = 0; k < h->n_cigar; ++k) { memcpy(&c, cigar + 4 * (size_t)k, 4); if ((c & 0xf) == 0) m += c >> 4; }
+        w->n_bases += m > h->l_qseq ? m : h->l_qseq;
+    }
 }
 
 /* ---- reader thread ----------------------------------------------------------------------------------- */

@@ -33,7 +33,7 @@ typedef struct ssn_window {
     int32_t tid;
     uint32_t widx;             /* positions [widx << SSN_WINDOW_SHIFT, (widx+1) << SSN_WINDOW_SHIFT) */
     uint32_t n_reads;
-    uint64_t n_bases;          /* sum of l_qseq: upper bound of the entries the window can produce */
+    uint64_t n_bases;          /* sum of max(l_qseq, M-run length): upper bound of the entries the window can produce */
     uint8_t *buf;
     size_t len, cap;
     struct ssn_window *next;
