@@ -47,6 +47,9 @@ def load_library():
     lib.ssn_packer_get_stats.argtypes = [C.c_void_p, C.POINTER(PackerStats)]
     lib.ssn_packer_get_stats.restype = None
     lib.ssn_host_last_error.restype = C.c_char_p
+    lib.ssn_packer_next_reads.argtypes = [C.c_void_p, C.POINTER(api.ReadsView), C.c_uint32, C.c_uint64, C.POINTER(C.c_uint8),
+                                          C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+    lib.ssn_packer_next_reads.restype = C.c_int
     lib.ssn_pack_read_windows.argtypes = [C.POINTER(api.ReadsView), C.c_uint32, C.POINTER(api.BatchView), C.POINTER(C.c_uint32),
                                           C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
     lib.ssn_pack_read_windows.restype = C.c_int
@@ -106,6 +109,36 @@ class Packer:
                 return
             yield dict(off=off[:2 * n + 1].copy(), bs=bs[:e].copy(), bq=bq[:e].copy(), mq=mq[:e].copy(), ref_nt16=ref16[:n].copy(),
                        ref_char=refc[:n].copy(), tid=tid[:n].copy(), pos=pos[:n].copy(), ncol=n, n_entries=e)
+
+
+def _packer_read_batches(self, max_rec_bytes=1 << 24, max_reads=1 << 18, max_windows=4):
+    """Iterates read batches (ssn_packer_next_reads): dicts like reads.build_read_windows' plus ref_char[w, 8192], tid, lo."""
+    nw = max_windows
+    while True:
+        recs = np.zeros(max_rec_bytes, np.uint8)
+        rec_off = np.zeros(max_reads, np.uint32)
+        win = np.zeros(nw, api.READ_WINDOW_DTYPE)
+        wref = np.zeros((nw, api.READ_WINDOW), np.uint8)
+        refc = np.zeros((nw, api.READ_WINDOW), np.uint8)
+        rv = api.ReadsView()
+        rv.recs = recs.ctypes.data_as(C.POINTER(C.c_uint8))
+        rv.rec_off = rec_off.ctypes.data_as(C.POINTER(C.c_uint32))
+        rv.win = win.ctypes.data
+        rv.ref_nt16 = wref.ctypes.data_as(C.POINTER(C.c_uint8))
+        rv.max_rec_bytes, rv.max_reads, rv.max_windows = max_rec_bytes, max_reads, nw
+        n_w, n_r, n_b = C.c_uint32(), C.c_uint32(), C.c_uint64()
+        st = self.lib.ssn_packer_next_reads(self.h, C.byref(rv), self.max_columns, self.max_entries,
+                                            refc.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(n_w), C.byref(n_r), C.byref(n_b))
+        if st != 0:
+            raise RuntimeError("ssn_packer_next_reads: %s" % self.lib.ssn_host_last_error().decode())
+        k = int(n_w.value)
+        if k == 0:
+            return
+        yield dict(recs=recs[:int(n_b.value)].copy(), rec_off=rec_off[:int(n_r.value)].copy(), win=win[:k].copy(),
+                   ref_nt16=wref[:k].copy(), ref_char=refc[:k].copy(), entries_bound=self.max_entries)
+
+
+Packer.read_batches = _packer_read_batches
 
 
 def pack_read_windows(rw, max_columns=None, max_entries=None):

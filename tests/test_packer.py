@@ -387,3 +387,38 @@ def test_cli_has_no_cpu_fallback(built, tmp_path):
     shutil.copy(os.path.join(INTEG, "small.fa"), fa)
     p = _cli("-f", fa, os.path.join(INTEG, "t-small.bam"), os.path.join(INTEG, "n-small.bam"), str(tmp_path / "o"))
     assert p.returncode == 1 and b"there is no CPU path" in p.stderr
+
+
+@pytest.mark.parametrize("mapq", [0, 20])
+def test_read_window_route_equals_the_column_route(host, sim, tmp_path, mapq):
+    """ssn_packer_next_reads (what the CLI ships under SSN_DEVICE_PILEUP=1) + the packer's count/fill over those whole
+    windows must give the very columns ssn_packer_next gives: same positions, reference characters and entries in the
+    same order — on the simulated multi-contig pair (indels, clips, N skips, filtered reads, quirk B1)."""
+    from somatic_sniper_b200 import cli_tools
+    contigs = [("chr1", 30000), ("chr2", 12000), ("chrEmpty", 100), ("chr3", 20000)]
+    pair = cli_tools.make_pair(str(tmp_path), contigs, 30, 20, seed=11 + mapq, n_runs=2,
+                               variant_kw=dict(het_every=500, hom_every=2000, som_every=1000, loh_every=5000, gor_every=5000))
+    pk = host.Packer(pair["tumor"], pair["normal"], pair["fasta"], mapq, threads=2, max_columns=1 << 16, max_entries=1 << 23)
+    want = list(pk)
+    pk.close()
+    key = lambda b: (b["tid"].astype(np.int64) << 32) | b["pos"]
+    w_key = np.concatenate([key(b) for b in want])
+    w_refc = np.concatenate([b["ref_char"] for b in want])
+    w_cnt = np.concatenate([np.diff(b["off"].astype(np.int64)) for b in want])
+    w_ent = np.concatenate([np.stack([b["bs"], b["bq"], b["mq"]], 1) for b in want])
+    pk = host.Packer(pair["tumor"], pair["normal"], pair["fasta"], mapq, threads=2, max_columns=1 << 16, max_entries=1 << 23)
+    g_key, g_refc, g_cnt, g_ent, n_batches = [], [], [], [], 0
+    for rb in pk.read_batches(max_windows=3):
+        cols = host.pack_read_windows(rb, max_entries=1 << 23)
+        w, o = cols["pos"] >> 13, cols["pos"] & 8191
+        g_key.append((rb["win"]["tid"][w].astype(np.int64) << 32) | (rb["win"]["lo"][w].astype(np.int64) + o))
+        g_refc.append(rb["ref_char"][w, o])
+        g_cnt.append(np.diff(cols["off"].astype(np.int64)))
+        g_ent.append(np.stack([cols["bs"], cols["bq"], cols["mq"]], 1))
+        n_batches += 1
+    pk.close()
+    assert n_batches >= 3 and len(w_key) > 40000
+    assert np.array_equal(np.concatenate(g_key), w_key)
+    assert np.array_equal(np.concatenate(g_refc), w_refc)
+    assert np.array_equal(np.concatenate(g_cnt), w_cnt)
+    assert np.array_equal(np.concatenate(g_ent), w_ent)
