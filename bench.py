@@ -454,7 +454,6 @@ def run_b200(args):
             sc.results_next()
         r_pos, r_nent = sc.column_positions(live[0])
         p_ms, p_n = sc.pileup_time()
-        r_launches = sc.kernel_launches()
         sc.close()
         r_cols = int(r_pos.size) * CHUNKS
         rms_max = dist_max(dist, max(rms, rwall))
