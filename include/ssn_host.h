@@ -64,6 +64,46 @@ ssn_status ssn_pack_read_windows(const ssn_reads_view *in, uint32_t n_windows, c
                                  uint32_t *pos, uint32_t *n_columns, uint64_t *n_entries);
 void ssn_packer_get_stats(const ssn_packer *p, ssn_packer_stats *out);
 const char *ssn_host_last_error(void);
+/* Device-pileup fall-back.  ssn_packer_next_reads returns SSN_ERR_OVERFLOW (with *n_windows = 0) when the next window
+ * alone is too deep for a read batch; nothing is consumed.  The caller then packs that window into columns:
+ * ssn_packer_one_window(p, 1), ssn_packer_next until ssn_packer_partial(p) is 0, ssn_packer_one_window(p, 0), and goes
+ * back to ssn_packer_next_reads. */
+void ssn_packer_one_window(ssn_packer *p, int on);
+int ssn_packer_partial(const ssn_packer *p);
+
+/* ---- region shards: the genome cut into contiguous intervals, one packer each ---------------------
+ * Replaces the single front-to-back walk of bam_sspileup_file (src/lib/sniper/sniper_pileup.c:226-266) by many walks
+ * over disjoint intervals whose union yields exactly the columns of the one walk: interval edges are multiples of the
+ * packer's window size, every interval's readers seek to their first record by bisection (no index file), start a
+ * look-back early to catch the reads reaching in, and take over the state of the keep rule (:216, QUIRK B1) from the last
+ * passing read in front of them.  Several intervals are read ahead concurrently; callers (one per GPU) take them in genome
+ * order with ssn_shardset_next, drive the returned packer with ssn_packer_next / ssn_packer_next_reads until it is
+ * exhausted, and hand it back with ssn_shardset_done.  Thread-safe.  Inputs that cannot be cut (stdin, a one-interval
+ * genome) come back as a single shard over the front-to-back reader. */
+typedef struct ssn_shardset ssn_shardset;
+typedef struct {
+    int n_threads;              /* host threads to plan for (0: online cores - 2) */
+    uint32_t stride_windows;    /* interval length in windows of 8192 positions (0: from the genome length; SSN_SHARD_WINDOWS) */
+    uint32_t lookback_windows;  /* how far in front of its interval a reader starts (0: 4; SSN_SHARD_LOOKBACK) */
+    int max_reading;            /* intervals whose readers run at once (0: from n_threads; SSN_SHARD_READERS) */
+    int max_open;               /* intervals opened but not yet handed back (0: 2 * max_reading + 2) */
+    int serial;                 /* 1: one interval, front to back */
+} ssn_shard_opts;
+ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, const char *fasta, int min_mapq,
+                             const ssn_shard_opts *opts, ssn_shardset **out);
+void ssn_shardset_close(ssn_shardset *s);
+int32_t ssn_shardset_n_shards(const ssn_shardset *s);
+int32_t ssn_shardset_n_targets(const ssn_shardset *s, int which);
+const char *ssn_shardset_target_name(const ssn_shardset *s, int which, int32_t tid);
+/* interval [ (lo_tid, lo_pos), (hi_tid, hi_pos) ) of a shard; hi_tid = INT32_MAX: to the end */
+ssn_status ssn_shardset_range(const ssn_shardset *s, int32_t index, int32_t *lo_tid, uint32_t *lo_pos, int32_t *hi_tid, uint32_t *hi_pos);
+/* next shard in genome order; *index = -1 after the last one */
+ssn_status ssn_shardset_next(ssn_shardset *s, int32_t *index, ssn_packer **packer);
+ssn_status ssn_shardset_done(ssn_shardset *s, int32_t index);
+/* 1: a read longer than the look-back crossed an interval edge, so a later interval missed it: the results are
+ * incomplete and the caller must run the pair again with opts.serial = 1 (checked after the last ssn_shardset_done) */
+int ssn_shardset_long_span(const ssn_shardset *s);
+void ssn_shardset_get_stats(const ssn_shardset *s, ssn_packer_stats *out);
 
 /* ---- writers: one passing site -> one line, byte-identical to the reference ---------------------------
  * output_classic.c:9-55, output_vcf.c:135-192, output_bed.c:5-19; format names as in output_format.c:9-17 */

@@ -5,13 +5,14 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "ssn_bamseek.h"
 #include "ssn_bgzf.h"
 
 #define QUEUE_MAX_BYTES ((size_t)256 << 20)   /* finished windows waiting for the packer (back-pressure) */
-#define MAX_OPEN 64                           /* windows one read may span at once (beyond: longer reads are clipped to the list) */
 
 struct ssn_bamreader {
     ssn_bgzf *z;
+    ssn_pool *pool;
     ssn_bam_header hdr;
     int flag_mask, mapq_thresh;
     /* byte stream over inflated chunks */
@@ -30,8 +31,16 @@ struct ssn_bamreader {
     int finished, stop;
     uint64_t n_records;
     /* open windows of the current target, ascending widx */
-    ssn_window *open[MAX_OPEN];
-    int n_open;
+    ssn_window **open;
+    int n_open, cap_open;
+    /* region shard (ssn_bamreader_open_range): the reader owns the windows in [lo, hi) */
+    const ssn_bamfile *bf;          /* not owned; NULL = the whole file from its first record */
+    int hdr_borrowed;
+    ssn_bam_range rg;
+    uint64_t lo_key, hi_key;        /* (tid << 32 | first position) of the first owned / first foreign window */
+    int long_span, failed;
+    size_t queue_max;
+    void (*on_finish)(void *); void *on_finish_arg;
 };
 
 /* ---- byte stream -------------------------------------------------------------------------------- */
@@ -120,7 +129,7 @@ void ssn_window_free(ssn_window *w)
 static void queue_push(ssn_bamreader *r, ssn_window *w)
 {
     pthread_mutex_lock(&r->mu);
-    while (!r->stop && r->q_bytes > QUEUE_MAX_BYTES && r->q_head) pthread_cond_wait(&r->not_full, &r->mu);
+    while (!r->stop && r->q_bytes > r->queue_max && r->q_head) pthread_cond_wait(&r->not_full, &r->mu);
     w->next = 0;
     if (r->q_tail) r->q_tail->next = w; else r->q_head = w;
     r->q_tail = w;
@@ -147,7 +156,12 @@ static ssn_window *open_window(ssn_bamreader *r, int32_t tid, uint32_t widx)
     ssn_window *w;
     for (i = 0; i < r->n_open; ++i)
         if (r->open[i]->widx == widx) return r->open[i];
-    if (r->n_open == MAX_OPEN) return 0;
+    if (r->n_open == r->cap_open) {
+        const int cap = r->cap_open ? 2 * r->cap_open : 64;
+        ssn_window **o = (ssn_window**)realloc(r->open, sizeof(*o) * (size_t)cap);
+        if (!o) return 0;
+        r->open = o; r->cap_open = cap;
+    }
     w = (ssn_window*)calloc(1, sizeof(*w));
     if (!w) return 0;
     w->tid = tid; w->widx = widx;
@@ -158,14 +172,17 @@ static ssn_window *open_window(ssn_bamreader *r, int32_t tid, uint32_t widx)
     return w;
 }
 
-static void window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar, const uint8_t *seq, const uint8_t *qual)
+static int window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar, const uint8_t *seq, const uint8_t *qual)
 {
     const size_t nc = (size_t)h->n_cigar * 4, ns = ((size_t)h->l_qseq + 1) >> 1, nq = h->l_qseq;
     uint8_t *d;
     if (w->len + h->bytes > w->cap) {
         size_t cap = w->cap ? w->cap * 2 : ((size_t)1 << 16);
+        uint8_t *nb;
         while (cap < w->len + h->bytes) cap *= 2;
-        w->buf = (uint8_t*)realloc(w->buf, cap);
+        nb = (uint8_t*)realloc(w->buf, cap);
+        if (!nb) return -1;
+        w->buf = nb;
         w->cap = cap;
     }
     d = w->buf + w->len;
@@ -183,15 +200,61 @@ static void window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar
         for (k = 0; k < h->n_cigar; ++k) { memcpy(&c, cigar + 4 * (size_t)k, 4); if ((c & 0xf) == 0) m += c >> 4; }
         w->n_bases += m > h->l_qseq ? m : h->l_qseq;
     }
+    return 0;
 }
 
 /* ---- reader thread ----------------------------------------------------------------------------------- */
+
+static void reader_finish(ssn_bamreader *r)
+{
+    pthread_mutex_lock(&r->mu);
+    r->finished = 1;
+    pthread_cond_broadcast(&r->not_empty);
+    pthread_mutex_unlock(&r->mu);
+    if (r->on_finish) r->on_finish(r->on_finish_arg);
+}
+
+/* Region shard: where to start reading and the keep rule's state there.  The reader starts `lookback` positions in
+ * front of its first window (the reads that begin there may reach into it) at the first record found by bisection, and
+ * takes over the cursor of the reference's walk - the start of the last passing read in front of that record
+ * (sniper_pileup.c:186,215-216) - from a short backward scan. */
+static int range_start(ssn_bamreader *r, int32_t *max_tid, uint32_t *prev_beg)
+{
+    const ssn_bam_range *g = &r->rg;
+    ssn_bam_point pt;
+    int rc;
+    if (g->lo_tid == 0 && g->lo_pos == 0) {                  /* the first shard reads from the top */
+        pt.voff = ssn_bamfile_first_record(r->bf);
+    } else {
+        const uint32_t from = g->lo_pos > g->lookback ? g->lo_pos - g->lookback : 0u;
+        rc = ssn_bamfile_lower_bound(r->bf, g->lo_tid, (int32_t)from, &pt);
+        if (rc < 0) return -1;
+        if (rc == 0) return 0;                                /* nothing at or behind the shard's start */
+        if (ssn_bam_key(pt.tid, pt.pos) >= r->hi_key) return 0;   /* the first such record already belongs to a later shard */
+        {
+            int32_t pt_tid = -1, pt_pos = 0;
+            rc = ssn_bamfile_prev_passing(r->bf, pt.voff, r->flag_mask, r->mapq_thresh, &pt_tid, &pt_pos);
+            if (rc < 0) return -1;
+            if (rc == 1) { *max_tid = pt_tid; *prev_beg = (uint32_t)pt_pos; }
+        }
+    }
+    r->z = ssn_bgzf_open_at(ssn_bamfile_path(r->bf), r->pool, pt.voff >> 16);
+    if (!r->z) return -1;
+    if ((pt.voff & 0xffff) && !stream_take(r, (size_t)(pt.voff & 0xffff))) return 0;
+    return 1;
+}
 
 static void *reader_main(void *v)
 {
     ssn_bamreader *r = (ssn_bamreader*)v;
     int32_t max_tid = -1;
     uint32_t prev_beg = 0;          /* cursor position at the next fetch (0 before the first passing read) */
+    const int ranged = r->bf != 0;
+    if (ranged) {
+        const int st = range_start(r, &max_tid, &prev_beg);
+        if (st < 0) r->failed = 1;
+        if (st <= 0) { reader_finish(r); return 0; }
+    }
     for (;;) {
         const uint8_t *p;
         int32_t block_len, tid, pos;
@@ -204,8 +267,9 @@ static void *reader_main(void *v)
         block_len = (int32_t)le32(p);
         if (block_len < 32) break;
         if (!(p = stream_take(r, (size_t)block_len))) break;
-        r->n_records += 1;
         tid = (int32_t)le32(p); pos = (int32_t)le32(p + 4);
+        if (ranged && ssn_bam_key(tid, pos) >= r->hi_key) break;      /* sorted input: everything from here on is a later shard's */
+        __atomic_add_fetch(&r->n_records, 1, __ATOMIC_RELAXED);
         x2 = le32(p + 8); x3 = le32(p + 12); l_qseq = le32(p + 16);
         mapq = (x2 >> 8) & 0xff; l_qname = x2 & 0xff; flag = x3 >> 16; n_cigar = x3 & 0xffff;
         if ((flag & (uint32_t)r->flag_mask) || (int)mapq < r->mapq_thresh) continue;       /* sniper_pileup.c:208 */
@@ -225,7 +289,7 @@ static void *reader_main(void *v)
         if (tid == max_tid && (uint32_t)pos < prev_beg) {
             /* positions running backwards inside a target: the reference does not notice (its test at :211 is
              * shadowed by tid >= max_tid) and piles such reads from the cursor onwards only; this reader needs
-             * sorted starts, so it stops here like on any other unsorted input */
+             * sorted starts, so it stops here like on any other unsorted input (known deviations) */
             fprintf(stderr, "[bam_pileup_core] the input is not sorted. Abort!\n");
             abort();
         }
@@ -234,49 +298,81 @@ static void *reader_main(void *v)
             max_tid = tid; prev_beg = (uint32_t)pos;
             if (!keep || tid < 0 || pos < 0 || end <= (uint32_t)pos) continue;
         }
+        /* a read that begins in front of the next shard's look-back and reaches into that shard is not seen there */
+        if (ranged && tid == r->rg.hi_tid && end > r->rg.hi_pos && (uint64_t)pos + r->rg.lookback < r->rg.hi_pos) r->long_span = 1;
         h.beg = pos; h.end = (int32_t)end; h.l_qseq = l_qseq; h.n_cigar = (uint16_t)n_cigar;
         h.mapq = (uint8_t)mapq; h.strand = (flag & 16) ? 1 : 0;
         h.bytes = (uint32_t)((sizeof(h) + (size_t)n_cigar * 4 + ((size_t)l_qseq + 1) / 2 + l_qseq + 3) & ~(size_t)3);
         w0 = (uint32_t)pos >> SSN_WINDOW_SHIFT; w1 = (end - 1) >> SSN_WINDOW_SHIFT;
         flush_open(r, tid, w0, 0);
         for (wi = w0; wi <= w1; ++wi) {
-            ssn_window *w = open_window(r, tid, wi);
-            if (!w) {
-                fprintf(stderr, "[ssn_bamread] a read spans more than %d windows of %u positions; the rest of it is ignored\n", MAX_OPEN, SSN_WINDOW);
+            ssn_window *w;
+            if (ranged) {
+                const uint64_t wk = (uint64_t)(uint32_t)tid << 32 | (uint64_t)wi << SSN_WINDOW_SHIFT;
+                if (wk < r->lo_key) continue;
+                if (wk >= r->hi_key) break;
+            }
+            w = open_window(r, tid, wi);
+            if (!w || window_append(w, &h, cigar, seq, qual) != 0) {
+                fprintf(stderr, "[ssn_bamread] out of memory\n");
+                r->failed = 1; r->stop = 1;
                 break;
             }
-            window_append(w, &h, cigar, seq, qual);
         }
     }
     flush_open(r, 0, 0, 1);
-    pthread_mutex_lock(&r->mu);
-    r->finished = 1;
-    pthread_cond_broadcast(&r->not_empty);
-    pthread_mutex_unlock(&r->mu);
+    reader_finish(r);
     return 0;
 }
 
 /* ---- API ------------------------------------------------------------------------------------------------ */
 
-ssn_bamreader *ssn_bamreader_open(const char *path, int flag_mask, int mapq_thresh, ssn_pool *pool, char *err, size_t errlen)
+static ssn_bamreader *reader_new(int flag_mask, int mapq_thresh, ssn_pool *pool, char *err, size_t errlen)
 {
     ssn_bamreader *r = (ssn_bamreader*)calloc(1, sizeof(*r));
     if (!r) { snprintf(err, errlen, "out of memory"); return 0; }
-    r->z = ssn_bgzf_open(path, pool);
-    if (!r->z) { snprintf(err, errlen, "cannot open %s", path); free(r); return 0; }
+    r->pool = pool;
     r->flag_mask = flag_mask < 0 ? SSN_BAM_DEF_MASK : (4 | flag_mask);       /* bam_plbuf_set_mask, sniper_pileup.c:146-150 */
     r->mapq_thresh = mapq_thresh < 0 ? 0 : mapq_thresh;                      /* bam_plbuf_set_mapq_thresh, :139-143 */
+    r->queue_max = QUEUE_MAX_BYTES;
     pthread_mutex_init(&r->mu, 0);
     pthread_cond_init(&r->not_empty, 0);
     pthread_cond_init(&r->not_full, 0);
+    return r;
+}
+
+ssn_bamreader *ssn_bamreader_open(const char *path, int flag_mask, int mapq_thresh, ssn_pool *pool, char *err, size_t errlen)
+{
+    ssn_bamreader *r = reader_new(flag_mask, mapq_thresh, pool, err, errlen);
+    if (!r) return 0;
+    r->z = ssn_bgzf_open(path, pool);
+    if (!r->z) { snprintf(err, errlen, "cannot open %s", path); ssn_bamreader_close(r); return 0; }
     if (read_header(r, err, errlen) != 0) { ssn_bamreader_close(r); return 0; }
     if (pthread_create(&r->th, 0, reader_main, r) != 0) { snprintf(err, errlen, "cannot start the reader thread"); ssn_bamreader_close(r); return 0; }
     r->th_started = 1;
     return r;
 }
 
+ssn_bamreader *ssn_bamreader_open_range(const ssn_bamfile *bf, const ssn_bam_range *range, int flag_mask, int mapq_thresh,
+                                        ssn_pool *pool, void (*on_finish)(void*), void *on_finish_arg, char *err, size_t errlen)
+{
+    ssn_bamreader *r = reader_new(flag_mask, mapq_thresh, pool, err, errlen);
+    if (!r) return 0;
+    r->bf = bf; r->rg = *range;
+    r->hdr = *ssn_bamfile_header(bf); r->hdr_borrowed = 1;
+    r->lo_key = (uint64_t)(uint32_t)range->lo_tid << 32 | range->lo_pos;
+    r->hi_key = range->hi_tid == INT32_MAX ? UINT64_MAX : ((uint64_t)(uint32_t)range->hi_tid << 32 | range->hi_pos);
+    if (range->queue_max_bytes) r->queue_max = range->queue_max_bytes;
+    r->on_finish = on_finish; r->on_finish_arg = on_finish_arg;
+    if (pthread_create(&r->th, 0, reader_main, r) != 0) { snprintf(err, errlen, "cannot start the reader thread"); r->on_finish = 0; ssn_bamreader_close(r); return 0; }
+    r->th_started = 1;
+    return r;
+}
+
 const ssn_bam_header *ssn_bamreader_header(const ssn_bamreader *r) { return &r->hdr; }
-uint64_t ssn_bamreader_records(const ssn_bamreader *r) { return r->n_records; }
+uint64_t ssn_bamreader_records(const ssn_bamreader *r) { return __atomic_load_n(&r->n_records, __ATOMIC_RELAXED); }
+int ssn_bamreader_long_span(const ssn_bamreader *r) { return r->long_span; }
+int ssn_bamreader_failed(const ssn_bamreader *r) { return r->failed; }
 
 ssn_window *ssn_bamreader_pop(ssn_bamreader *r)
 {
@@ -308,8 +404,11 @@ void ssn_bamreader_close(ssn_bamreader *r)
     }
     while (r->q_head) { ssn_window *w = r->q_head; r->q_head = w->next; ssn_window_free(w); }
     for (i = 0; i < r->n_open; ++i) ssn_window_free(r->open[i]);
-    if (r->hdr.target_name) for (i = 0; i < r->hdr.n_targets; ++i) free(r->hdr.target_name[i]);
-    free(r->hdr.target_name); free(r->hdr.target_len); free(r->hdr.text);
+    free(r->open);
+    if (!r->hdr_borrowed) {
+        if (r->hdr.target_name) for (i = 0; i < r->hdr.n_targets; ++i) free(r->hdr.target_name[i]);
+        free(r->hdr.target_name); free(r->hdr.target_len); free(r->hdr.text);
+    }
     free(r->carry);
     ssn_bgzf_close(r->z);
     pthread_mutex_destroy(&r->mu);

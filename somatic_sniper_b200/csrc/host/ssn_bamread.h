@@ -51,6 +51,26 @@ typedef struct ssn_bamreader ssn_bamreader;
 
 /* Opens the file, parses the header (synchronously) and starts the reader thread. */
 ssn_bamreader *ssn_bamreader_open(const char *path, int flag_mask, int mapq_thresh, ssn_pool *pool, char *err, size_t errlen);
+
+/* Region shard: the reader files the windows of [ (lo_tid, lo_pos), (hi_tid, hi_pos) ) only - both multiples of
+ * SSN_WINDOW, hi_tid = INT32_MAX for "to the end" - and stops at the first record at or behind hi.  It starts `lookback`
+ * positions in front of lo (reads beginning there may reach into the shard) with the keep rule's state taken over
+ * from the last passing read before that point, so every keep decision equals the front-to-back walk's
+ * (sniper_pileup.c:216, QUIRK B1 across shard edges).  A kept read that begins more than `lookback` in front of hi and
+ * reaches behind it is invisible to the next shard: ssn_bamreader_long_span() then reports 1 and the caller must fall
+ * back to one shard.  The thread starts at once; the seek happens inside it.  on_finish (optional) is called from the
+ * reader thread when it is done. */
+struct ssn_bamfile;
+typedef struct {
+    int32_t lo_tid; uint32_t lo_pos;
+    int32_t hi_tid; uint32_t hi_pos;
+    uint32_t lookback;
+    size_t queue_max_bytes;        /* 0: default back-pressure limit */
+} ssn_bam_range;
+ssn_bamreader *ssn_bamreader_open_range(const struct ssn_bamfile *bf, const ssn_bam_range *range, int flag_mask, int mapq_thresh,
+                                        ssn_pool *pool, void (*on_finish)(void*), void *on_finish_arg, char *err, size_t errlen);
+int ssn_bamreader_long_span(const ssn_bamreader *r);
+int ssn_bamreader_failed(const ssn_bamreader *r);
 const ssn_bam_header *ssn_bamreader_header(const ssn_bamreader *r);
 /* Next finished window in (tid, widx) order, NULL after the last one.  The caller owns it (ssn_window_free). */
 ssn_window *ssn_bamreader_pop(ssn_bamreader *r);

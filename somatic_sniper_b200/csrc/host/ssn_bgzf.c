@@ -27,24 +27,35 @@ struct ssn_bgzf {
     size_t out_cap;
     blk blocks[MAX_BLOCKS];
     uint64_t consumed;
+    /* per call: up to 512 blocks with a worker pool behind it (parallel inflate); 16 when the caller inflates by itself
+     * (region shards: many readers, one core each — the inflated bytes are framed while they are still in the cache) */
+    int max_blocks;
+    size_t raw_cap;
 };
 
-ssn_bgzf *ssn_bgzf_open(const char *path, ssn_pool *pool)
+ssn_bgzf *ssn_bgzf_open(const char *path, ssn_pool *pool) { return ssn_bgzf_open_at(path, pool, 0); }
+
+ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff)
 {
     ssn_bgzf *z = (ssn_bgzf*)calloc(1, sizeof(*z));
     if (!z) return 0;
-    if (strcmp(path, "-") == 0) { z->fd = 0; z->own_fd = 0; }
-    else {
+    if (strcmp(path, "-") == 0) {
+        if (coff) { free(z); return 0; }
+        z->fd = 0; z->own_fd = 0;
+    } else {
         z->fd = open(path, O_RDONLY);
         z->own_fd = 1;
         if (z->fd < 0) { free(z); return 0; }
+        if (coff && lseek(z->fd, (off_t)coff, SEEK_SET) < 0) { close(z->fd); free(z); return 0; }
 #ifdef POSIX_FADV_SEQUENTIAL
         posix_fadvise(z->fd, 0, 0, POSIX_FADV_SEQUENTIAL);
 #endif
     }
     z->pool = pool;
-    z->raw = (uint8_t*)malloc(RAW_CAP);
-    z->out_cap = (size_t)MAX_BLOCKS * 65536;
+    z->max_blocks = (pool && ssn_pool_threads(pool) > 0) ? MAX_BLOCKS : 16;
+    z->raw_cap = (pool && ssn_pool_threads(pool) > 0) ? RAW_CAP : ((size_t)2 << 20);
+    z->raw = (uint8_t*)malloc(z->raw_cap);
+    z->out_cap = (size_t)z->max_blocks * 65536;
     z->out = (uint8_t*)malloc(z->out_cap);
     if (!z->raw || !z->out) { ssn_bgzf_close(z); return 0; }
     return z;
@@ -66,8 +77,8 @@ static void refill(ssn_bgzf *z)
         z->raw_len -= z->raw_pos;
         z->raw_pos = 0;
     }
-    while (!z->eof_file && z->raw_len < RAW_CAP) {
-        ssize_t r = read(z->fd, z->raw + z->raw_len, RAW_CAP - z->raw_len);
+    while (!z->eof_file && z->raw_len < z->raw_cap) {
+        ssize_t r = read(z->fd, z->raw + z->raw_len, z->raw_cap - z->raw_len);
         if (r < 0) { if (errno == EINTR) continue; z->eof_file = 1; break; }
         if (r == 0) { z->eof_file = 1; break; }
         z->raw_len += (size_t)r;
@@ -125,8 +136,8 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
     inflate_arg a;
     *data = 0; *len = 0;
     if (z->done) return 0;
-    if (z->raw_len - z->raw_pos < (RAW_CAP >> 1)) refill(z);
-    while (n < MAX_BLOCKS) {
+    if (z->raw_len - z->raw_pos < (z->raw_cap >> 1)) refill(z);
+    while (n < z->max_blocks) {
         blk *b = &z->blocks[n];
         int r = parse_block(z->raw + z->raw_pos, z->raw_len - z->raw_pos, b);
         if (r == 0) {

@@ -12,6 +12,8 @@
 typedef struct ssn_bgzf ssn_bgzf;
 
 ssn_bgzf *ssn_bgzf_open(const char *path, ssn_pool *pool);    /* "-" reads stdin; NULL on failure */
+/* the same, starting at the block that begins at file offset coff (region shards; not for stdin) */
+ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff);
 /* Next run of decompressed bytes (a few MB); valid until the next call.  Returns 1 with data, 0 at the end. */
 int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len);
 void ssn_bgzf_close(ssn_bgzf *z);

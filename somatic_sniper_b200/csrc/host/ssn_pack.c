@@ -17,9 +17,11 @@
 #include <time.h>
 
 #include "ssn_bamread.h"
+#include "ssn_bamseek.h"
 #include "ssn_fasta.h"
 #include "ssn_host.h"
 #include "ssn_nt16.h"
+#include "ssn_pack_internal.h"
 #include "ssn_pool.h"
 
 #define GROUP_MAX 16           /* windows pulled per batch at most */
@@ -27,13 +29,14 @@
 
 static __thread char h_err[512] = "";
 const char *ssn_host_last_error(void) { return h_err; }
-static void set_err(const char *fmt, ...)
+void ssn_host_set_error(const char *fmt, ...)
 {
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(h_err, sizeof(h_err), fmt, ap);
     va_end(ap);
 }
+#define set_err ssn_host_set_error
 
 static double now_s(void)
 {
@@ -42,15 +45,104 @@ static double now_s(void)
     return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
 }
 
+/* ---- target sequences: one cache for all packers of a run ----------------------------------------------------
+ * A sequence lives as long as a joined window points at it (reference count) and, idle, until a few newer ones have
+ * pushed it out; packers of different region shards share the cache (one fetch per target, not one per shard). */
+typedef struct ssn_refseq {
+    int32_t tid;
+    char *seq; int len;
+    int refs, loading;
+    struct ssn_refseq *next;
+} ssn_refseq;
+
+struct ssn_refcache {
+    pthread_mutex_t mu;
+    pthread_cond_t cv;
+    ssn_fasta *fa;                 /* owned; NULL: every base reads as 'N' */
+    const ssn_bam_header *names;   /* target names come from the tumor header (QUIRK B9) */
+    ssn_refseq *head;
+};
+
+#define REF_IDLE_MAX 2
+
+ssn_refcache *ssn_refcache_create(const char *fasta, const ssn_bam_header *names)
+{
+    ssn_refcache *rc = (ssn_refcache*)calloc(1, sizeof(*rc));
+    if (!rc) return 0;
+    pthread_mutex_init(&rc->mu, 0);
+    pthread_cond_init(&rc->cv, 0);
+    /* like the reference (main.c:106-108, somatic_sniper.c:112-117) a FASTA that cannot be loaded is not fatal:
+     * every reference base then reads as 'N' and no column is ever emitted */
+    if (fasta) rc->fa = ssn_fasta_load(fasta);
+    rc->names = names;
+    return rc;
+}
+
+void ssn_refcache_destroy(ssn_refcache *rc)
+{
+    if (!rc) return;
+    while (rc->head) { ssn_refseq *e = rc->head; rc->head = e->next; free(e->seq); free(e); }
+    ssn_fasta_destroy(rc->fa);
+    pthread_mutex_destroy(&rc->mu);
+    pthread_cond_destroy(&rc->cv);
+    free(rc);
+}
+
+/* mu held: drops idle sequences beyond REF_IDLE_MAX, lowest target first (targets arrive in ascending order) */
+static void refcache_trim(ssn_refcache *rc)
+{
+    for (;;) {
+        ssn_refseq **pp, **victim = 0;
+        int idle = 0;
+        for (pp = &rc->head; *pp; pp = &(*pp)->next)
+            if ((*pp)->refs == 0 && !(*pp)->loading) { ++idle; if (!victim || (*pp)->tid < (*victim)->tid) victim = pp; }
+        if (idle <= REF_IDLE_MAX) return;
+        { ssn_refseq *e = *victim; *victim = e->next; free(e->seq); free(e); }
+    }
+}
+
+static ssn_refseq *refcache_get(ssn_refcache *rc, int32_t tid)
+{
+    ssn_refseq *e;
+    pthread_mutex_lock(&rc->mu);
+    for (e = rc->head; e; e = e->next) if (e->tid == tid) break;
+    if (e) {
+        e->refs += 1;
+        while (e->loading) pthread_cond_wait(&rc->cv, &rc->mu);
+        pthread_mutex_unlock(&rc->mu);
+        return e;
+    }
+    e = (ssn_refseq*)calloc(1, sizeof(*e));
+    e->tid = tid; e->refs = 1; e->loading = 1;
+    e->next = rc->head; rc->head = e;
+    pthread_mutex_unlock(&rc->mu);
+    if (rc->fa && tid >= 0 && tid < rc->names->n_targets) e->seq = ssn_fasta_fetch(rc->fa, rc->names->target_name[tid], &e->len);
+    if (!e->seq) { e->seq = (char*)calloc(1, 1); e->len = 0; }
+    pthread_mutex_lock(&rc->mu);
+    e->loading = 0;
+    pthread_cond_broadcast(&rc->cv);
+    refcache_trim(rc);
+    pthread_mutex_unlock(&rc->mu);
+    return e;
+}
+
+static void refcache_put(ssn_refcache *rc, ssn_refseq *e)
+{
+    if (!rc || !e) return;
+    pthread_mutex_lock(&rc->mu);
+    e->refs -= 1;
+    refcache_trim(rc);
+    pthread_mutex_unlock(&rc->mu);
+}
+
 /* a joined window: both samples' reads plus the per-position counts */
 typedef struct pair {
     ssn_window *w[2];             /* 0 tumor, 1 normal */
     uint32_t *cnt[2];             /* [SSN_WINDOW] read bases per position */
     uint32_t next_i;              /* first position index not yet emitted */
-    const char *ref; int ref_len; /* target sequence (owned by the packer's cache) */
+    const char *ref; int ref_len; /* target sequence */
+    ssn_refcache *rc; ssn_refseq *rs;   /* where it came from: released with the window */
 } pair;
-
-typedef struct { int32_t tid; char *seq; int len; } ref_slot;
 
 typedef struct {                  /* one fill task */
     pair *p;
@@ -61,11 +153,13 @@ typedef struct {                  /* one fill task */
 
 struct ssn_packer {
     ssn_pool *pool;
+    int own_pool;
     ssn_bamreader *rd[2];
     ssn_window *head[2];          /* next window of each stream (look-ahead of the join) */
     int ended;
-    ssn_fasta *fa;
-    ref_slot refs[4];
+    ssn_refcache *rc;
+    int own_rc;
+    int one_window;               /* ssn_packer_next takes one new window per call (device-pileup fall-back) */
     pair *pending[GROUP_MAX + 1];
     int n_pending;
     ssn_packer_stats st;
@@ -202,6 +296,7 @@ static void fill_task(void *arg, int idx)
 static void pair_free(pair *p)
 {
     if (!p) return;
+    refcache_put(p->rc, p->rs);
     ssn_window_free(p->w[0]); ssn_window_free(p->w[1]);
     free(p->cnt[0]); free(p->cnt[1]);
     free(p);
@@ -238,28 +333,12 @@ static pair *next_pair(ssn_packer *pk)
     return p;
 }
 
-/* target sequence through a tiny cache (tids arrive in ascending order) */
+/* target sequence of the window, shared and reference-counted (released in pair_free) */
 static void attach_ref(ssn_packer *pk, pair *p)
 {
-    const int32_t tid = p->w[0]->tid;
-    const int n = (int)(sizeof(pk->refs) / sizeof(pk->refs[0]));
-    int i, victim = 0;
-    for (i = 0; i < n; ++i)
-        if (pk->refs[i].seq && pk->refs[i].tid == tid) { p->ref = pk->refs[i].seq; p->ref_len = pk->refs[i].len; return; }
-    for (i = 0; i < n; ++i) {
-        if (!pk->refs[i].seq && pk->refs[i].tid == -1) { victim = i; break; }
-        if (pk->refs[i].tid < pk->refs[victim].tid) victim = i;
-    }
-    /* the victim's tid is older than every window still pending (pending tids are >= the batch's first) */
-    free(pk->refs[victim].seq);
-    pk->refs[victim].seq = 0; pk->refs[victim].len = 0; pk->refs[victim].tid = tid;
-    {
-        const ssn_bam_header *h = ssn_bamreader_header(pk->rd[0]);      /* names come from the tumor header, QUIRK B9 */
-        if (pk->fa && tid >= 0 && tid < h->n_targets)
-            pk->refs[victim].seq = ssn_fasta_fetch(pk->fa, h->target_name[tid], &pk->refs[victim].len);
-        if (!pk->refs[victim].seq) { pk->refs[victim].seq = (char*)calloc(1, 1); pk->refs[victim].len = 0; }
-    }
-    p->ref = pk->refs[victim].seq; p->ref_len = pk->refs[victim].len;
+    p->rc = pk->rc;
+    p->rs = refcache_get(pk->rc, p->w[0]->tid);
+    p->ref = p->rs->seq; p->ref_len = p->rs->len;
 }
 
 /* ---- API -------------------------------------------------------------------------------------------------------- */
@@ -269,36 +348,53 @@ ssn_status ssn_packer_open(const char *tumor_bam, const char *normal_bam, const 
 {
     ssn_packer *pk;
     char err[256];
-    int i;
     if (!tumor_bam || !normal_bam || !out) { set_err("ssn_packer_open: null argument"); return SSN_ERR_ARG; }
     pk = (ssn_packer*)calloc(1, sizeof(*pk));
     if (!pk) { set_err("out of memory"); return SSN_ERR_NOMEM; }
-    for (i = 0; i < (int)(sizeof(pk->refs) / sizeof(pk->refs[0])); ++i) pk->refs[i].tid = -1;
-    pk->pool = ssn_pool_create(n_threads);
-    if (fasta) {
-        pk->fa = ssn_fasta_load(fasta);
-        /* like the reference (main.c:106-108, somatic_sniper.c:112-117) a FASTA that cannot be loaded is not fatal:
-         * every reference base then reads as 'N' and no column is ever emitted */
-    }
+    pk->pool = ssn_pool_create(n_threads); pk->own_pool = 1;
     pk->rd[0] = ssn_bamreader_open(tumor_bam, -1, min_mapq, pk->pool, err, sizeof(err));
     if (!pk->rd[0]) { set_err("tumor BAM: %s", err); ssn_packer_close(pk); return SSN_ERR_ARG; }
     pk->rd[1] = ssn_bamreader_open(normal_bam, -1, min_mapq, pk->pool, err, sizeof(err));
     if (!pk->rd[1]) { set_err("normal BAM: %s", err); ssn_packer_close(pk); return SSN_ERR_ARG; }
+    pk->rc = ssn_refcache_create(fasta, ssn_bamreader_header(pk->rd[0])); pk->own_rc = 1;
     *out = pk;
     return SSN_OK;
 }
+
+/* one region shard of a run (ssn_shard.c): pool, target sequences and the two open files belong to the shard set */
+ssn_packer *ssn_packer_create_shard(ssn_pool *pool, ssn_pool *reader_pool, ssn_refcache *rc, const ssn_bamfile *tumor,
+                                    const ssn_bamfile *normal, const ssn_bam_range *range, int min_mapq,
+                                    void (*on_finish)(void*), void *on_finish_arg, char *err, size_t errlen)
+{
+    ssn_packer *pk = (ssn_packer*)calloc(1, sizeof(*pk));
+    if (!pk) { snprintf(err, errlen, "out of memory"); return 0; }
+    pk->pool = pool; pk->rc = rc;
+    pk->rd[0] = ssn_bamreader_open_range(tumor, range, -1, min_mapq, reader_pool, on_finish, on_finish_arg, err, errlen);
+    if (!pk->rd[0]) { ssn_packer_close(pk); return 0; }
+    pk->rd[1] = ssn_bamreader_open_range(normal, range, -1, min_mapq, reader_pool, on_finish, on_finish_arg, err, errlen);
+    if (!pk->rd[1]) { ssn_packer_close(pk); return 0; }
+    return pk;
+}
+
+/* Device-pileup fall-back: a window too deep for a read batch is packed into columns by ssn_packer_next.  With the limit
+ * set, ssn_packer_next works on one window at a time, so that ssn_packer_partial() turns 0 as soon as that window is used
+ * up and the caller can go back to ssn_packer_next_reads. */
+void ssn_packer_one_window(ssn_packer *pk, int on) { pk->one_window = on; }
+int ssn_packer_partial(const ssn_packer *pk) { return pk->n_pending > 0 && pk->pending[0]->next_i > 0; }
+
+int ssn_packer_long_span(const ssn_packer *pk) { return ssn_bamreader_long_span(pk->rd[0]) || ssn_bamreader_long_span(pk->rd[1]); }
+int ssn_packer_failed(const ssn_packer *pk) { return ssn_bamreader_failed(pk->rd[0]) || ssn_bamreader_failed(pk->rd[1]); }
 
 void ssn_packer_close(ssn_packer *pk)
 {
     int i;
     if (!pk) return;
-    for (i = 0; i < pk->n_pending; ++i) pair_free(pk->pending[i]);
-    ssn_window_free(pk->head[0]); ssn_window_free(pk->head[1]);
     if (pk->rd[0]) ssn_bamreader_close(pk->rd[0]);
     if (pk->rd[1]) ssn_bamreader_close(pk->rd[1]);
-    for (i = 0; i < (int)(sizeof(pk->refs) / sizeof(pk->refs[0])); ++i) free(pk->refs[i].seq);
-    ssn_fasta_destroy(pk->fa);
-    ssn_pool_destroy(pk->pool);
+    for (i = 0; i < pk->n_pending; ++i) pair_free(pk->pending[i]);
+    ssn_window_free(pk->head[0]); ssn_window_free(pk->head[1]);
+    if (pk->own_rc) ssn_refcache_destroy(pk->rc);
+    if (pk->own_pool) ssn_pool_destroy(pk->pool);
     free(pk);
 }
 
@@ -338,7 +434,7 @@ ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn
             bound_ent += pk->pending[i]->w[0]->n_bases + pk->pending[i]->w[1]->n_bases;
             bound_col += SSN_WINDOW - pk->pending[i]->next_i;
         }
-        while (pk->n_pending < GROUP_MAX && bound_ent < view->max_entries && bound_col < view->max_columns) {
+        while (pk->n_pending < (pk->one_window ? 1 : GROUP_MAX) && bound_ent < view->max_entries && bound_col < view->max_columns) {
             pair *p = next_pair(pk);
             if (!p) break;
             attach_ref(pk, p);

@@ -67,6 +67,8 @@ struct ssn_batch {
     uint32_t max_tile_words;
     uint32_t max_col_words;   /* key-store words of the deepest column (list-mode tiles gather arbitrary columns) */
     uint32_t *d_survivors;    /* column indices the pre-filter hands to the full model */
+    uint32_t *d_scratch; size_t scratch_words;   /* global key store of this slot's launches (tiles deeper than shared
+                                                   * memory); per slot, because slots score concurrently on their own streams */
     cudaStream_t stream;
     cudaEvent_t done;
     uint32_t n_sites;
@@ -105,8 +107,6 @@ struct ssn_ctx {
     int num_sms, ctas_per_sm_cap;
     size_t smem_optin, smem_static;
     uint32_t smem_words_default;
-    uint32_t *d_scratch; size_t scratch_words;   /* global key store, all warps */
-    uint32_t grid_cap;                          /* largest grid ever launched (scratch sizing) */
     void *d_flush; size_t flush_bytes;
     std::vector<KernelTimer> timers;
     size_t timer_next;
@@ -186,7 +186,7 @@ static void slot_free(ssn_batch *b)
     cudaFreeHost(b->h_off); cudaFreeHost(b->h_bs); cudaFreeHost(b->h_bq); cudaFreeHost(b->h_mq);
     cudaFreeHost(b->h_ref); cudaFreeHost(b->h_count); cudaFreeHost(b->h_sites); cudaFreeHost(b->h_dump);
     cudaFree(b->d_off); cudaFree(b->d_bs); cudaFree(b->d_bq); cudaFree(b->d_mq); cudaFree(b->d_ref);
-    cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump); cudaFree(b->d_survivors);
+    cudaFree(b->d_count); cudaFree(b->d_sites); cudaFree(b->d_dump); cudaFree(b->d_survivors); cudaFree(b->d_scratch);
     cudaFreeHost(b->h_recs); cudaFreeHost(b->h_index);
     cudaFreeHost(b->h_summary); cudaFreeHost(b->h_colpos);
     cudaFree(b->d_recs); cudaFree(b->d_index); cudaFree(b->d_A); cudaFree(b->d_P);
@@ -226,7 +226,7 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     ssn_ctx *ctx = new ssn_ctx();
     ctx->device = device; ctx->params = *p; ctx->next_seq = 1; ctx->launches = 0;
     ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
-    ctx->d_scratch = nullptr; ctx->scratch_words = 0; ctx->grid_cap = 0; ctx->d_flush = nullptr; ctx->flush_bytes = 0;
+    ctx->d_flush = nullptr; ctx->flush_bytes = 0;
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
     ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = ctx->d_pf_vt = nullptr; ctx->pf_on = false;
     memset(&ctx->pf, 0, sizeof(ctx->pf));
@@ -327,7 +327,7 @@ extern "C" void ssn_destroy(ssn_ctx *ctx)
     cudaFree(ctx->d_pf_ab); cudaFree(ctx->d_pf_h); cudaFree(ctx->d_pf_F); cudaFree(ctx->d_pf_vt);
     ssn_prefilter_free(&ctx->pf);
     cudaFree(ctx->d_coef_lhet); cudaFree(ctx->d_fk); cudaFree(ctx->d_prior); cudaFree(ctx->d_jointprior);
-    cudaFree(ctx->d_qadd); cudaFree(ctx->d_scratch); cudaFree(ctx->d_flush);
+    cudaFree(ctx->d_qadd); cudaFree(ctx->d_flush);
     if (ctx->main_stream) cudaStreamDestroy(ctx->main_stream);
     if (ctx->t0) cudaEventDestroy(ctx->t0);
     if (ctx->t1) cudaEventDestroy(ctx->t1);
@@ -516,18 +516,18 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     if (tile_words > words) {
         const size_t per_warp = ((size_t)tile_words + 63) / 64 * 64;
         const size_t need = per_warp * grid * kWarpsPerCta;
-        if (ctx->scratch_words < need) {
-            CU(cudaDeviceSynchronize());
-            cudaFree(ctx->d_scratch); ctx->d_scratch = nullptr; ctx->scratch_words = 0;
-            CU(cudaMalloc(&ctx->d_scratch, need * 4));
-            ctx->scratch_words = need;
+        if (b->scratch_words < need) {
+            CU(cudaStreamSynchronize(b->stream));           /* only this slot's launches ever touch its scratch */
+            cudaFree(b->d_scratch); b->d_scratch = nullptr; b->scratch_words = 0;
+            CU(cudaMalloc(&b->d_scratch, need * 4));
+            b->scratch_words = need;
         }
     }
     DevBatch B;
     B.off = b->d_off; B.bs = b->d_bs; B.bq = b->d_bq; B.mq = b->d_mq; B.ref_nt16 = b->d_ref; B.ncol = b->ncol;
     B.sites = b->d_sites; B.site_count = b->d_count; B.site_cap = b->site_cap;
     B.coldump = dump ? b->d_dump : nullptr;
-    B.scratch = tile_words > words ? ctx->d_scratch : nullptr;
+    B.scratch = tile_words > words ? b->d_scratch : nullptr;
     B.scratch_words_per_warp = (uint32_t)(((size_t)tile_words + 63) / 64 * 64);
     B.smem_words_per_warp = words;
     B.dev_ncol = b->spec ? b->d_summary : nullptr; B.guard = b->spec ? b->d_summary : nullptr; B.guard_col_words = b->spec_col_words;

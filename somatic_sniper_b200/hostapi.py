@@ -21,7 +21,14 @@ class PackerStats(C.Structure):
                 ("t_wait", C.c_double), ("t_count", C.c_double), ("t_fill", C.c_double)]
 
 
-HOST_SYMBOLS = ["ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
+class ShardOpts(C.Structure):
+    _fields_ = [("n_threads", C.c_int), ("stride_windows", C.c_uint32), ("lookback_windows", C.c_uint32), ("max_reading", C.c_int),
+                ("max_open", C.c_int), ("serial", C.c_int)]
+
+
+HOST_SYMBOLS = ["ssn_shardset_open", "ssn_shardset_close", "ssn_shardset_n_shards", "ssn_shardset_n_targets", "ssn_shardset_target_name",
+                "ssn_shardset_range", "ssn_shardset_next", "ssn_shardset_done", "ssn_shardset_long_span", "ssn_shardset_get_stats",
+                "ssn_packer_one_window", "ssn_packer_partial", "ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
                 "ssn_packer_get_stats", "ssn_pack_read_windows", "ssn_packer_next_reads", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
                 "ssn_writer_destroy", "ssn_writer_n_formats", "ssn_writer_format_name"]
 
@@ -30,7 +37,7 @@ def load_library():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = os.path.join(_HERE, "lib", "libssn_host.so")
+    path = os.environ.get("SSN_HOST_LIB") or os.path.join(_HERE, "lib", "libssn_host.so")   # override: sanitizer builds (tools/sanitize_host.sh)
     if not os.path.exists(path):
         raise RuntimeError("libssn_host.so is not built (run python __graft_entry__.py)")
     lib = C.CDLL(path)
@@ -53,6 +60,30 @@ def load_library():
     lib.ssn_pack_read_windows.argtypes = [C.POINTER(api.ReadsView), C.c_uint32, C.POINTER(api.BatchView), C.POINTER(C.c_uint32),
                                           C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
     lib.ssn_pack_read_windows.restype = C.c_int
+    lib.ssn_shardset_open.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(ShardOpts), C.POINTER(C.c_void_p)]
+    lib.ssn_shardset_open.restype = C.c_int
+    lib.ssn_shardset_close.argtypes = [C.c_void_p]
+    lib.ssn_shardset_close.restype = None
+    lib.ssn_shardset_n_shards.argtypes = [C.c_void_p]
+    lib.ssn_shardset_n_shards.restype = C.c_int32
+    lib.ssn_shardset_n_targets.argtypes = [C.c_void_p, C.c_int]
+    lib.ssn_shardset_n_targets.restype = C.c_int32
+    lib.ssn_shardset_target_name.argtypes = [C.c_void_p, C.c_int, C.c_int32]
+    lib.ssn_shardset_target_name.restype = C.c_char_p
+    lib.ssn_shardset_range.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.POINTER(C.c_uint32)]
+    lib.ssn_shardset_range.restype = C.c_int
+    lib.ssn_shardset_next.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_void_p)]
+    lib.ssn_shardset_next.restype = C.c_int
+    lib.ssn_shardset_done.argtypes = [C.c_void_p, C.c_int32]
+    lib.ssn_shardset_done.restype = C.c_int
+    lib.ssn_shardset_long_span.argtypes = [C.c_void_p]
+    lib.ssn_shardset_long_span.restype = C.c_int
+    lib.ssn_shardset_get_stats.argtypes = [C.c_void_p, C.POINTER(PackerStats)]
+    lib.ssn_shardset_get_stats.restype = None
+    lib.ssn_packer_one_window.argtypes = [C.c_void_p, C.c_int]
+    lib.ssn_packer_one_window.restype = None
+    lib.ssn_packer_partial.argtypes = [C.c_void_p]
+    lib.ssn_packer_partial.restype = C.c_int
     lib.ssn_writer_n_formats.restype = C.c_int
     lib.ssn_writer_format_name.argtypes = [C.c_int]
     lib.ssn_writer_format_name.restype = C.c_char_p
@@ -63,9 +94,14 @@ def load_library():
 class Packer:
     """Iterates the SoA batches of a tumor/normal BAM pair (host arrays owned by numpy; no GPU involved)."""
 
-    def __init__(self, tumor, normal, fasta, min_mapq=0, threads=2, max_columns=1 << 16, max_entries=1 << 23):
+    def __init__(self, tumor, normal, fasta, min_mapq=0, threads=2, max_columns=1 << 16, max_entries=1 << 23, handle=None):
         self.lib = load_library()
+        self.max_columns, self.max_entries = max_columns, max_entries
         self.h = C.c_void_p()
+        self.owned = handle is None
+        if handle is not None:          # a region shard's packer (owned by its ShardSet)
+            self.h = handle
+            return
         st = self.lib.ssn_packer_open(os.fsencode(tumor), os.fsencode(normal), os.fsencode(fasta) if fasta else None,
                                       int(min_mapq), int(threads), C.byref(self.h))
         if st != 0:
@@ -73,9 +109,9 @@ class Packer:
         self.max_columns, self.max_entries = max_columns, max_entries
 
     def close(self):
-        if self.h:
+        if self.h and self.owned:
             self.lib.ssn_packer_close(self.h)
-            self.h = C.c_void_p()
+        self.h = C.c_void_p()
 
     def target_names(self, which=0):
         n = self.lib.ssn_packer_n_targets(self.h, which)
@@ -173,3 +209,64 @@ def pack_read_windows(rw, max_columns=None, max_entries=None):
     n, e = int(ncol.value), int(nent.value)
     return dict(ncol=n, n_entries=e, off=off[:2 * n + 1].copy(), bs=bs[:e].copy(), bq=bq[:e].copy(), mq=mq[:e].copy(),
                 ref_nt16=ref[:n].copy(), pos=pos[:n].copy())
+
+
+class ShardSet:
+    """Region shards of a pair (ssn_shardset): iterating yields, shard after shard in genome order, what a Packer over the
+    whole pair yields.  `route` = "columns" (ssn_packer_next) or "reads" (ssn_packer_next_reads)."""
+
+    def __init__(self, tumor, normal, fasta, min_mapq=0, threads=2, stride_windows=0, lookback_windows=0, max_reading=0, max_open=0,
+                 serial=0, max_columns=1 << 16, max_entries=1 << 23):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        o = ShardOpts(int(threads), int(stride_windows), int(lookback_windows), int(max_reading), int(max_open), int(serial))
+        st = self.lib.ssn_shardset_open(os.fsencode(tumor), os.fsencode(normal), os.fsencode(fasta) if fasta else None, int(min_mapq),
+                                        C.byref(o), C.byref(self.h))
+        if st != 0:
+            raise RuntimeError("ssn_shardset_open: %s" % self.lib.ssn_host_last_error().decode())
+        self.max_columns, self.max_entries = max_columns, max_entries
+
+    def close(self):
+        if self.h:
+            self.lib.ssn_shardset_close(self.h)
+            self.h = C.c_void_p()
+
+    def n_shards(self):
+        return int(self.lib.ssn_shardset_n_shards(self.h))
+
+    def ranges(self):
+        out = []
+        for i in range(self.n_shards()):
+            a, b, c, d = C.c_int32(), C.c_uint32(), C.c_int32(), C.c_uint32()
+            assert self.lib.ssn_shardset_range(self.h, i, C.byref(a), C.byref(b), C.byref(c), C.byref(d)) == 0
+            out.append((a.value, b.value, c.value, d.value))
+        return out
+
+    def long_span(self):
+        return bool(self.lib.ssn_shardset_long_span(self.h))
+
+    def stats(self):
+        s = PackerStats()
+        self.lib.ssn_shardset_get_stats(self.h, C.byref(s))
+        return s
+
+    def shards(self):
+        """Yields (index, Packer) in genome order; the packer is handed back when the consumer asks for the next one."""
+        while True:
+            idx, pk = C.c_int32(), C.c_void_p()
+            st = self.lib.ssn_shardset_next(self.h, C.byref(idx), C.byref(pk))
+            if st != 0:
+                raise RuntimeError("ssn_shardset_next: %s" % self.lib.ssn_host_last_error().decode())
+            if idx.value < 0:
+                return
+            try:
+                yield idx.value, Packer(None, None, None, max_columns=self.max_columns, max_entries=self.max_entries, handle=pk)
+            finally:
+                st = self.lib.ssn_shardset_done(self.h, idx.value)
+            if st != 0:
+                raise RuntimeError("ssn_shardset_done: %s" % self.lib.ssn_host_last_error().decode())
+
+    def __iter__(self):
+        for _, pk in self.shards():
+            for b in pk:
+                yield b

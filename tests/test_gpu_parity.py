@@ -118,6 +118,41 @@ def test_deep_panel_columns(mods):
     check_batch(api, Oracle, cols, "default")
 
 
+def test_deep_batches_in_flight_on_several_slots(mods):
+    """Panel-depth batches (key store in the global scratch) on 4 slots whose kernels overlap: every slot owns its
+    scratch, so concurrent launches cannot sort in each other's keys.  Sites and dumps against the oracle."""
+    api, synth, Oracle = mods
+    batches = [synth.make_columns(400, depth_t=1800 + 100 * i, depth_n=1100, seed=80 + i, binned=False, p_som=3e-2, p_het=2e-2)
+               for i in range(8)]
+    cap = max(int(b["n_entries"]) for b in batches) + 64
+    want = [Oracle(min_somatic_qual=0, use_priors=0).score_batch(b["off"], b["bs"], b["bq"], b["mq"], b["ref_char"], want_glf=True)
+            for b in batches]
+    for flags in (api.SUBMIT_NO_PREFILTER | api.SUBMIT_COLUMN_DUMP, 0):
+        for rounds in range(2):
+            sc = api.Scorer(ssn_params("nopriors_q0"), device=0, n_slots=4, max_columns=512, max_entries=cap)
+            got, fifo = [], []
+            want_dump = bool(flags & api.SUBMIT_COLUMN_DUMP)
+
+            def drain():
+                s, _ = sc.results_next()
+                b = fifo.pop(0)
+                got.append((s, b.column_dump() if want_dump else None))
+
+            for cols in batches:
+                if len(fifo) == 4:
+                    drain()
+                b = sc.acquire(); b.fill(cols); sc.submit(b, flags); fifo.append(b)
+            while fifo:
+                drain()
+            sc.close()
+            for (s, d), w, cols in zip(got, want, batches):
+                assert np.array_equal(s["column"].astype(np.int64), w["emit_col"].astype(np.int64))
+                assert np.array_equal(api.sites_to_records(s, cols["ref_char"]), w["recs"])
+                if d is not None:
+                    assert np.array_equal(d[:, :28], w["glf"])
+    assert sum(len(w["emit_col"]) for w in want) > 10
+
+
 def test_empty_and_single(mods):
     api, synth, Oracle = mods
     sc = api.Scorer(ssn_params("default"), n_slots=2, max_columns=64, max_entries=4096)
