@@ -32,6 +32,21 @@ def make_pair(workdir, contigs, depth_t=60.0, depth_n=30.0, seed=7, n_runs=1, le
     return dict(fasta=fa, tumor=t, normal=n, reads_tumor=nt, reads_normal=nn, columns=sum(l for _, l in contigs))
 
 
+SIMBAM = os.path.join(_HERE, "bin", "ssn-simbam")
+
+
+def make_pair_fast(workdir, contigs, depth_t=60.0, depth_n=30.0, seed=7, level=1, threads=None):
+    """The same kind of pair from the multi-threaded C generator (tools/simbam_fast.c): for inputs a Python loop cannot
+    produce in reasonable time.  Returns the paths and read counts."""
+    os.makedirs(workdir, exist_ok=True)
+    threads = threads or max(1, (os.cpu_count() or 2) - 1)
+    p = subprocess.run([SIMBAM, workdir, str(seed), str(depth_t), str(depth_n), str(level), str(threads)] +
+                       ["%s:%d" % c for c in contigs], stdout=subprocess.PIPE, check=True)
+    r = json.loads(p.stdout.decode())
+    return dict(fasta=os.path.join(workdir, "ref.fa"), tumor=os.path.join(workdir, "tumor.bam"), normal=os.path.join(workdir, "normal.bam"),
+                reads_tumor=r["reads_tumor"], reads_normal=r["reads_normal"], columns=sum(l for _, l in contigs))
+
+
 def run_cli(exe, fasta, tumor, normal, out, args=(), env=None, stats=None, timeout=3600):
     e = dict(os.environ)
     if env:

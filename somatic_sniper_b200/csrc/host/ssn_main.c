@@ -8,15 +8,24 @@
  *   bam_sspileup_file(..., glf_somatic, ...) (:146)     ssn_packer_next -> ssn_batch_submit -> ssn_results_next
  *   output_formatter (:141-145, somatic_sniper.c:264)   ssn_writer_*
  *
+ *   one front-to-back walk on one thread                region shards (ssn_shardset_*): the genome is cut into intervals,
+ *                                                       several are read ahead at once, one feeder thread per GPU takes them
+ *                                                       in genome order, the main thread writes their output in that order
+ *
  * Not in the reference (environment only, the command line is unchanged):
- *   SSN_GPUS     number of GPUs to spread batches over (default 1; batch k goes to GPU k mod N)
+ *   SSN_GPUS     number of GPUs (default 1); every GPU gets a feeder thread and takes the next region shard when it is free
  *   SSN_DEVICES  comma-separated device ordinals, one scoring context each (overrides SSN_GPUS; an ordinal may repeat)
- *   SSN_THREADS  worker threads for inflate + packing (default: online cores - 2, at least 1)
+ *   SSN_THREADS  host threads to plan for: readers, inflate, packing (default: online cores - 2, at least 1)
  *   SSN_SLOTS    batches in flight per GPU (default 3)
+ *   SSN_DEVICE_PILEUP  1 (default): ship the filtered reads, build the columns on the GPU; 0: pack columns on the host
+ *   SSN_SERIAL   1: one interval, front to back (what a pair that cannot be cut gets anyway)
+ *   SSN_SHARD_WINDOWS / SSN_SHARD_LOOKBACK / SSN_SHARD_READERS  interval length and look-back in windows of 8192
+ *                positions, intervals read at once (ssn_host.h)
  *   SSN_STATS    file that receives one JSON line of run statistics
  * There is no CPU scoring path: without a usable sm_100 device the program fails.
  */
 #include <ctype.h>
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -26,11 +35,11 @@
 #include "ssn.h"
 #include "ssn_host.h"
 
-#define SSN_CLI_VERSION "b200-r1"
+#define SSN_CLI_VERSION "b200-r2"
 #define MAX_GPUS 16
 #define MAX_SLOTS 8
 #define BATCH_COLUMNS (16u << 13)            /* 16 packer windows */
-#define BATCH_ENTRIES ((uint64_t)24 << 20)
+#define BATCH_ENTRIES ((uint64_t)32 << 20)      /* one window of 8192 positions up to ~4000x (tumor + normal) */
 
 static const char *default_normal_id = "NORMAL";
 static const char *default_tumor_id = "TUMOR";
@@ -76,18 +85,51 @@ static void usage(const char *progname, const ssn_params *p, int mapq)
 typedef struct {
     ssn_batch *batch;
     ssn_colmap map;
-    /* SSN_DEVICE_PILEUP=1: the slot's read arrays and the raw reference characters of its windows */
+    /* device pileup: the slot's read arrays and the raw reference characters of its windows */
     ssn_reads_view rv;
     uint8_t *ref_chars;
+    int from_reads;
+    int32_t shard;
 } slot_meta;
 
+/* output of one region shard: lines are formatted into memory by the feeder that scored it and written by main in
+ * shard order */
 typedef struct {
+    char *buf; size_t len;
+    FILE *fp;
+    ssn_writer *wr;
+    int in_flight, exhausted, complete;
+} shard_out;
+
+typedef struct run run_t;
+
+typedef struct {
+    run_t *run;
+    int index, device;
     ssn_ctx *ctx;
     slot_meta meta[MAX_SLOTS];
     int n_meta, in_flight;
+    slot_meta *fifo[MAX_SLOTS];
+    int f_head, f_count;
+    pthread_t th;
+    int th_started, setup_rc;
+    /* statistics */
+    uint64_t n_sites, n_batches, survivors, dev_columns, dev_entries, col_batches;
+    double t_gpu_wait, t_setup;
 } gpu_t;
 
-typedef struct { int gpu; } flight;
+struct run {
+    ssn_params prm;
+    int n_gpus, n_slots, n_threads, device_pileup;
+    const char *format;
+    gpu_t gpus[MAX_GPUS];
+    ssn_shardset *set;
+    shard_out *outs;
+    int32_t n_shards;
+    pthread_mutex_t mu;
+    pthread_cond_t cv;
+    int error, gpus_ready, go;
+};
 
 static double now_s(void)
 {
@@ -105,38 +147,63 @@ static int env_int(const char *name, int dflt, int lo, int hi)
     return v;
 }
 
+static void run_fail(run_t *R)
+{
+    pthread_mutex_lock(&R->mu);
+    R->error = 1;
+    pthread_cond_broadcast(&R->cv);
+    pthread_mutex_unlock(&R->mu);
+}
+
 static slot_meta *meta_of(gpu_t *g, ssn_batch *b)
 {
     int i;
     for (i = 0; i < g->n_meta; ++i)
         if (g->meta[i].batch == b) return &g->meta[i];
     if (g->n_meta == MAX_SLOTS) return 0;
+    memset(&g->meta[g->n_meta], 0, sizeof(slot_meta));
     g->meta[g->n_meta].batch = b;
-    g->meta[g->n_meta].map.tid = (int32_t*)malloc(sizeof(int32_t) * BATCH_COLUMNS);
-    g->meta[g->n_meta].map.pos = (uint32_t*)malloc(sizeof(uint32_t) * BATCH_COLUMNS);
-    g->meta[g->n_meta].map.ref_char = (uint8_t*)malloc(BATCH_COLUMNS);
     g->meta[g->n_meta].ref_chars = (uint8_t*)malloc(BATCH_COLUMNS);
     return &g->meta[g->n_meta++];
 }
 
-static uint64_t g_survivors;   /* columns the pre-filter handed to the full model (statistics only) */
-static int g_device_pileup;    /* SSN_DEVICE_PILEUP=1: ship the reads, build the columns on the GPU (ssn_batch_submit_reads) */
-static uint64_t g_dev_columns, g_dev_entries;
-
-/* waits for the oldest batch in flight and writes its sites */
-static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, ssn_packer *pk, ssn_writer *wr, uint64_t *n_sites)
+static int meta_colmap(slot_meta *m)
 {
-    gpu_t *g = &gpus[fifo[*head].gpu];
+    if (m->map.tid) return 0;
+    m->map.tid = (int32_t*)malloc(sizeof(int32_t) * BATCH_COLUMNS);
+    m->map.pos = (uint32_t*)malloc(sizeof(uint32_t) * BATCH_COLUMNS);
+    m->map.ref_char = (uint8_t*)malloc(BATCH_COLUMNS);
+    return m->map.tid && m->map.pos && m->map.ref_char ? 0 : -1;
+}
+
+static void shard_complete(run_t *R, int32_t k)
+{
+    shard_out *o = &R->outs[k];
+    ssn_writer_destroy(o->wr); o->wr = 0;
+    fclose(o->fp); o->fp = 0;               /* finalises buf / len */
+    pthread_mutex_lock(&R->mu);
+    o->complete = 1;
+    pthread_cond_broadcast(&R->cv);
+    pthread_mutex_unlock(&R->mu);
+}
+
+/* waits for the GPU's oldest batch in flight and formats its sites into its shard's buffer */
+static int drain_one(gpu_t *g)
+{
+    run_t *R = g->run;
     const ssn_site *sites;
     uint32_t n, i;
     ssn_batch *b;
-    slot_meta *m;
+    slot_meta *m = g->fifo[g->f_head];
+    shard_out *o = &R->outs[m->shard];
+    const double t0 = now_s();
     if (ssn_results_next(g->ctx, &sites, &n, &b) != SSN_OK) {
         fprintf(stderr, "[bam-somaticsniper] GPU scoring failed: %s\n", ssn_last_error());
         return -1;
     }
-    m = meta_of(g, b);
-    if (g_device_pileup) {
+    g->t_gpu_wait += now_s() - t0;
+    if (b != m->batch) { fprintf(stderr, "[bam-somaticsniper] batches came back out of order\n"); return -1; }
+    if (m->from_reads) {
         const uint32_t *cpos;
         uint32_t ncol;
         uint64_t nent;
@@ -144,124 +211,331 @@ static int drain_one(gpu_t *gpus, flight *fifo, int *head, int *count, int cap, 
             fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
             return -1;
         }
-        g_dev_columns += ncol; g_dev_entries += nent;
+        g->dev_columns += ncol; g->dev_entries += nent;
         for (i = 0; i < n; ++i) {
-            const uint32_t pw = cpos[sites[i].column], w = pw >> SSN_READ_WINDOW_SHIFT, o = pw & (SSN_READ_WINDOW - 1u);
-            const char *name = ssn_packer_target_name(pk, 0, m->rv.win[w].tid);
-            ssn_writer_site(wr, name ? name : "", m->rv.win[w].lo + o, m->ref_chars[pw], &sites[i]);
+            const uint32_t pw = cpos[sites[i].column], w = pw >> SSN_READ_WINDOW_SHIFT, off = pw & (SSN_READ_WINDOW - 1u);
+            const char *name = ssn_shardset_target_name(R->set, 0, m->rv.win[w].tid);   /* names from the tumor header (QUIRK B9) */
+            ssn_writer_site(o->wr, name ? name : "", m->rv.win[w].lo + off, m->ref_chars[pw], &sites[i]);
         }
     } else
     for (i = 0; i < n; ++i) {
         const uint32_t c = sites[i].column;
-        const char *name = ssn_packer_target_name(pk, 0, m->map.tid[c]);        /* names from the tumor header (QUIRK B9) */
-        ssn_writer_site(wr, name ? name : "", m->map.pos[c], m->map.ref_char[c], &sites[i]);
+        const char *name = ssn_shardset_target_name(R->set, 0, m->map.tid[c]);
+        ssn_writer_site(o->wr, name ? name : "", m->map.pos[c], m->map.ref_char[c], &sites[i]);
     }
-    *n_sites += n;
+    g->n_sites += n;
     {
         uint32_t surv = 0;
-        if (ssn_batch_survivors(b, &surv) == SSN_OK) g_survivors += surv;
+        if (ssn_batch_survivors(b, &surv) == SSN_OK) g->survivors += surv;
     }
     g->in_flight -= 1;
-    *head = (*head + 1) % cap;
-    *count -= 1;
+    g->f_head = (g->f_head + 1) % MAX_SLOTS;
+    g->f_count -= 1;
+    if (--o->in_flight == 0 && o->exhausted) shard_complete(R, m->shard);
     return 0;
+}
+
+static void push_flight(gpu_t *g, slot_meta *m, int32_t shard, int from_reads)
+{
+    m->shard = shard; m->from_reads = from_reads;
+    g->fifo[(g->f_head + g->f_count) % MAX_SLOTS] = m;
+    g->f_count += 1; g->in_flight += 1; g->n_batches += 1;
+    g->run->outs[shard].in_flight += 1;
+}
+
+/* one region shard through this GPU: batches are submitted while earlier ones (of this or the previous shard) score */
+static int feed_shard(gpu_t *g, int32_t k, ssn_packer *pk)
+{
+    run_t *R = g->run;
+    int columns_mode = !R->device_pileup;       /* or: inside a window too deep for a read batch */
+    for (;;) {
+        ssn_batch *b;
+        slot_meta *m;
+        while (g->in_flight == R->n_slots)
+            if (drain_one(g) != 0) return -1;
+        if (ssn_batch_acquire(g->ctx, &b) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); return -1; }
+        m = meta_of(g, b);
+        if (!m) { fprintf(stderr, "[bam-somaticsniper] slot table overflow\n"); return -1; }
+        if (!columns_mode) {
+            uint32_t nw = 0, nr = 0;
+            uint64_t nb = 0;
+            ssn_status st;
+            if (ssn_batch_reads_view(g->ctx, b, &m->rv) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); return -1; }
+            st = ssn_packer_next_reads(pk, &m->rv, BATCH_COLUMNS, BATCH_ENTRIES, m->ref_chars, &nw, &nr, &nb);
+            if (st == SSN_ERR_OVERFLOW) {
+                /* this window alone is too deep for a read batch: the host packs it into columns (any depth), then the
+                 * reads route resumes */
+                columns_mode = 1;
+                ssn_packer_one_window(pk, 1);
+            } else if (st != SSN_OK) {
+                fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
+                return -1;
+            } else {
+                if (nw == 0) { ssn_batch_release(g->ctx, b); return 0; }
+                if (ssn_batch_submit_reads(g->ctx, b, nw, nr, nb, 0) != SSN_OK) {
+                    fprintf(stderr, "[bam-somaticsniper] GPU submit failed: %s\n", ssn_last_error());
+                    return -1;
+                }
+                push_flight(g, m, k, 1);
+                continue;
+            }
+        }
+        {
+            ssn_batch_view view;
+            uint32_t ncol = 0;
+            uint64_t nent = 0;
+            if (ssn_batch_view_get(b, &view) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); return -1; }
+            if (meta_colmap(m) != 0) { fprintf(stderr, "[bam-somaticsniper] out of memory\n"); return -1; }
+            if (ssn_packer_next(pk, &view, &m->map, &ncol, &nent) != SSN_OK) {
+                fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
+                return -1;
+            }
+            if (ncol == 0) { ssn_batch_release(g->ctx, b); return 0; }
+            if (ssn_batch_set_size(b, ncol, nent) != SSN_OK || ssn_batch_submit(g->ctx, b, 0) != SSN_OK) {
+                fprintf(stderr, "[bam-somaticsniper] GPU submit failed: %s\n", ssn_last_error());
+                return -1;
+            }
+            push_flight(g, m, k, 0);
+            g->col_batches += 1;
+            if (R->device_pileup && !ssn_packer_partial(pk)) { columns_mode = 0; ssn_packer_one_window(pk, 0); }
+        }
+    }
+}
+
+static int gpu_setup(gpu_t *g)
+{
+    run_t *R = g->run;
+    const double t0 = now_s();
+    if (ssn_create(&R->prm, g->device, (uint32_t)R->n_slots, BATCH_COLUMNS, BATCH_ENTRIES, &g->ctx) != SSN_OK) {
+        fprintf(stderr, "[bam-somaticsniper] cannot set up GPU %d: %s\n", g->device, ssn_last_error());
+        fprintf(stderr, "[bam-somaticsniper] this build scores on sm_100 GPUs only; there is no CPU path\n");
+        return -1;
+    }
+    if (R->device_pileup) {
+        ssn_batch *held[MAX_SLOTS];
+        ssn_reads_view rv;
+        int k, ok = 1;
+        if (ssn_reads_reserve(g->ctx, 2 * BATCH_ENTRIES, (uint32_t)(BATCH_ENTRIES / 24), BATCH_COLUMNS >> SSN_READ_WINDOW_SHIFT) != SSN_OK) {
+            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
+            return -1;
+        }
+        /* the slots' read arrays are allocated on first use: do it here, not inside the stream */
+        for (k = 0; k < R->n_slots; ++k) ok = ok && ssn_batch_acquire(g->ctx, &held[k]) == SSN_OK && ssn_batch_reads_view(g->ctx, held[k], &rv) == SSN_OK;
+        if (!ok) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); return -1; }
+        for (k = 0; k < R->n_slots; ++k) ssn_batch_release(g->ctx, held[k]);
+    }
+    g->t_setup = now_s() - t0;
+    return 0;
+}
+
+/* feeder thread of one GPU: sets the context up, then takes region shards in genome order until none is left */
+static void *gpu_main(void *arg)
+{
+    gpu_t *g = (gpu_t*)arg;
+    run_t *R = g->run;
+    if (!g->ctx) g->setup_rc = gpu_setup(g);
+    pthread_mutex_lock(&R->mu);
+    R->gpus_ready += 1;
+    if (g->setup_rc != 0) R->error = 1;
+    pthread_cond_broadcast(&R->cv);
+    while (!R->go && !R->error) pthread_cond_wait(&R->cv, &R->mu);
+    pthread_mutex_unlock(&R->mu);
+    if (g->setup_rc != 0) return 0;
+    for (;;) {
+        int32_t k = -1;
+        ssn_packer *pk = 0;
+        shard_out *o;
+        int rc;
+        if (R->error) break;
+        if (ssn_shardset_next(R->set, &k, &pk) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error()); run_fail(R); break; }
+        if (k < 0) break;
+        o = &R->outs[k];
+        o->fp = open_memstream(&o->buf, &o->len);
+        o->wr = o->fp ? ssn_writer_create(R->format, o->fp) : 0;
+        if (!o->wr) { fprintf(stderr, "[bam-somaticsniper] out of memory\n"); ssn_shardset_done(R->set, k); run_fail(R); break; }
+        rc = feed_shard(g, k, pk);
+        if (ssn_shardset_done(R->set, k) != SSN_OK && rc == 0) {
+            /* the seek could not place this interval: main runs the pair again as one interval */
+            pthread_mutex_lock(&R->mu); R->error |= 2; pthread_cond_broadcast(&R->cv); pthread_mutex_unlock(&R->mu);
+            break;
+        }
+        if (rc != 0) { run_fail(R); break; }
+        o->exhausted = 1;
+        if (o->in_flight == 0) shard_complete(R, k);
+    }
+    while (g->f_count > 0 && !(R->error & 1))
+        if (drain_one(g) != 0) { run_fail(R); break; }
+    return 0;
+}
+
+static int start_feeders(run_t *R)
+{
+    int i;
+    R->error = 0; R->gpus_ready = 0; R->go = 0;
+    for (i = 0; i < R->n_gpus; ++i) {
+        gpu_t *g = &R->gpus[i];
+        g->f_head = g->f_count = g->in_flight = 0; g->th_started = 0;
+        if (pthread_create(&g->th, 0, gpu_main, g) != 0) {
+            fprintf(stderr, "[bam-somaticsniper] cannot start a feeder thread\n");
+            pthread_mutex_lock(&R->mu); R->error = 1; R->gpus_ready += 1; pthread_cond_broadcast(&R->cv); pthread_mutex_unlock(&R->mu);
+            continue;
+        }
+        g->th_started = 1;
+    }
+    /* contexts are set up in parallel (model tables, device and pinned memory) */
+    pthread_mutex_lock(&R->mu);
+    while (R->gpus_ready < R->n_gpus) pthread_cond_wait(&R->cv, &R->mu);
+    i = R->error;
+    pthread_mutex_unlock(&R->mu);
+    return i ? -1 : 0;
+}
+
+static void join_feeders(run_t *R)
+{
+    int i;
+    pthread_mutex_lock(&R->mu);
+    R->go = 1;
+    pthread_cond_broadcast(&R->cv);
+    pthread_mutex_unlock(&R->mu);
+    for (i = 0; i < R->n_gpus; ++i)
+        if (R->gpus[i].th_started) { pthread_join(R->gpus[i].th, 0); R->gpus[i].th_started = 0; }
+}
+
+/* Releases the feeders and writes the shards' output in genome order as they complete.
+ * 0: done; 1: failed; 2: the pair has to be walked as one interval (a read longer than the look-back crossed an interval
+ * edge, or the seek could not place an interval): the caller runs it again with serial = 1. */
+static int stream_pass(run_t *R, FILE *out)
+{
+    int32_t k;
+    int err = 0;
+    pthread_mutex_lock(&R->mu);
+    R->go = 1;
+    pthread_cond_broadcast(&R->cv);
+    for (k = 0; k < R->n_shards; ++k) {
+        shard_out *o = &R->outs[k];
+        while (!o->complete && !R->error) pthread_cond_wait(&R->cv, &R->mu);
+        if (R->error) break;
+        pthread_mutex_unlock(&R->mu);
+        if (o->len) fwrite(o->buf, 1, o->len, out);
+        free(o->buf); o->buf = 0; o->len = 0;
+        pthread_mutex_lock(&R->mu);
+    }
+    err = R->error;
+    pthread_mutex_unlock(&R->mu);
+    join_feeders(R);
+    err |= R->error;
+    if (err & 1) return 1;
+    if ((err & 2) || ssn_shardset_long_span(R->set)) return 2;
+    return 0;
+}
+
+static void free_outs(run_t *R)
+{
+    int32_t k;
+    for (k = 0; k < R->n_shards && R->outs; ++k) {
+        shard_out *o = &R->outs[k];
+        if (o->wr) ssn_writer_destroy(o->wr);
+        if (o->fp) fclose(o->fp);
+        free(o->buf);
+    }
+    free(R->outs); R->outs = 0;
+}
+
+static int open_set(run_t *R, const char *tumor, const char *normal, const char *fasta, int mapq, int serial)
+{
+    ssn_shard_opts so;
+    memset(&so, 0, sizeof(so));
+    so.n_threads = R->n_threads; so.serial = serial;
+    if (ssn_shardset_open(tumor, normal, fasta, mapq, &so, &R->set) != SSN_OK) {
+        fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
+        return -1;
+    }
+    R->n_shards = ssn_shardset_n_shards(R->set);
+    R->outs = (shard_out*)calloc((size_t)R->n_shards, sizeof(shard_out));
+    return R->outs ? 0 : -1;
 }
 
 int main(int argc, char *argv[])
 {
-    int c, use_priors = 1, mapq = 0, n_gpus, n_slots, n_threads, i, rc = 0, devices[MAX_GPUS];
+    int c, use_priors = 1, mapq = 0, i, rc = 0, passes = 1;
     const char *normal_id = default_normal_id, *tumor_id = default_tumor_id, *fn_fa = 0, *format = default_format;
-    ssn_params prm;
-    ssn_packer *pk = 0;
+    static run_t R;
     ssn_writer *wr;
     FILE *out;
-    gpu_t gpus[MAX_GPUS];
-    flight fifo[MAX_GPUS * MAX_SLOTS];
-    int f_head = 0, f_count = 0, next_gpu = 0;
-    uint64_t n_sites = 0, n_batches = 0;
-    double t_start = now_s(), t_setup, t_gpu_wait = 0;
+    ssn_packer_stats st;
+    int32_t n_shards_first;
+    double t_start = now_s(), t_setup;
 
-    ssn_params_default(&prm);
+    memset(&R, 0, sizeof(R));
+    memset(&st, 0, sizeof(st));
+    ssn_params_default(&R.prm);
     while ((c = getopt(argc, argv, "n:t:vf:T:N:r:I:q:Q:pLGJs:F:")) >= 0) {
         switch (c) {
         case 'f': fn_fa = optarg; break;
-        case 'T': prm.theta = (float)atof(optarg); break;
-        case 'N': prm.n_hap = atoi(optarg); break;
-        case 'r': prm.het_rate = (float)atof(optarg); break;
+        case 'T': R.prm.theta = (float)atof(optarg); break;
+        case 'N': R.prm.n_hap = atoi(optarg); break;
+        case 'r': R.prm.het_rate = (float)atof(optarg); break;
         case 'q': mapq = atoi(optarg); break;
-        case 'Q': prm.min_somatic_qual = atoi(optarg); break;
+        case 'Q': R.prm.min_somatic_qual = atoi(optarg); break;
         case 'F': format = optarg; break;
         case 'p': use_priors = 0; break;
-        case 'J': prm.use_joint_priors = 1; break;
-        case 's': prm.somatic_mutation_rate = atof(optarg); prm.use_joint_priors = 1; break;
+        case 'J': R.prm.use_joint_priors = 1; break;
+        case 's': R.prm.somatic_mutation_rate = atof(optarg); R.prm.use_joint_priors = 1; break;
         case 'v': version_info(); exit(0); break;
         case 't': tumor_id = optarg; break;
         case 'n': normal_id = optarg; break;
-        case 'L': prm.include_loh = 0; break;
-        case 'G': prm.include_gor = 0; break;
+        case 'L': R.prm.include_loh = 0; break;
+        case 'G': R.prm.include_gor = 0; break;
         default: fprintf(stderr, "Unrecognizd option '-%c'.\n", c); return 1;
         }
     }
-    prm.use_priors = use_priors;
-    if (optind == argc) { usage(argv[0], &prm, mapq); return 1; }
+    R.prm.use_priors = use_priors;
+    if (optind == argc) { usage(argv[0], &R.prm, mapq); return 1; }
     if (!fn_fa) {
         fprintf(stderr, "You MUST specify a reference sequence. It isn't optional.\n");
         exit(1);
     }
     if (argc - optind < 3) {
         /* the reference reads argv past its end here; ask for the missing arguments instead */
-        usage(argv[0], &prm, mapq);
+        usage(argv[0], &R.prm, mapq);
         return 1;
     }
-    n_gpus = env_int("SSN_GPUS", 1, 1, MAX_GPUS);
-    for (i = 0; i < MAX_GPUS; ++i) devices[i] = i;
+    R.n_gpus = env_int("SSN_GPUS", 1, 1, MAX_GPUS);
+    for (i = 0; i < MAX_GPUS; ++i) R.gpus[i].device = i;
     {
         const char *dv = getenv("SSN_DEVICES");
         if (dv && *dv) {
-            n_gpus = 0;
-            while (*dv && n_gpus < MAX_GPUS) {
-                devices[n_gpus++] = atoi(dv);
+            R.n_gpus = 0;
+            while (*dv && R.n_gpus < MAX_GPUS) {
+                R.gpus[R.n_gpus++].device = atoi(dv);
                 while (*dv && *dv != ',') ++dv;
                 if (*dv == ',') ++dv;
             }
-            if (n_gpus == 0) n_gpus = 1;
+            if (R.n_gpus == 0) R.n_gpus = 1;
         }
     }
-    n_slots = env_int("SSN_SLOTS", 3, 1, MAX_SLOTS);
+    for (i = 0; i < R.n_gpus; ++i) { R.gpus[i].run = &R; R.gpus[i].index = i; }
+    R.n_slots = env_int("SSN_SLOTS", 3, 1, MAX_SLOTS);
     {
         long cores = sysconf(_SC_NPROCESSORS_ONLN);
-        n_threads = env_int("SSN_THREADS", cores > 3 ? (int)cores - 2 : 1, 0, 256);
+        R.n_threads = env_int("SSN_THREADS", cores > 3 ? (int)cores - 2 : 1, 0, 256);
     }
-    memset(gpus, 0, sizeof(gpus));
-    g_device_pileup = env_int("SSN_DEVICE_PILEUP", 0, 0, 1);
+    R.device_pileup = env_int("SSN_DEVICE_PILEUP", 1, 0, 1);
+    R.format = format;
+    pthread_mutex_init(&R.mu, 0);
+    pthread_cond_init(&R.cv, 0);
 
-    /* same order of stderr lines as main.c:115-131 */
-    if (ssn_packer_open(argv[optind], argv[optind + 1], fn_fa, mapq, n_threads, &pk) != SSN_OK) {
-        fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
+    /* The readers of the first region shards start inside open_set and read ahead while the GPU contexts are built.
+     * Same order of stderr lines as main.c:115-131. */
+    if (open_set(&R, argv[optind], argv[optind + 1], fn_fa, mapq, env_int("SSN_SERIAL", 0, 0, 1)) != 0) return 1;
+    n_shards_first = R.n_shards;
+    if (R.prm.use_joint_priors)
+        fprintf(stderr, "Using priors accounting for somatic mutation rate. Prior probability of a somatic mutation is %f\n", R.prm.somatic_mutation_rate);
+    if (start_feeders(&R) != 0) {
+        join_feeders(&R);
+        free_outs(&R);
+        ssn_shardset_close(R.set);
         return 1;
-    }
-    if (prm.use_joint_priors)
-        fprintf(stderr, "Using priors accounting for somatic mutation rate. Prior probability of a somatic mutation is %f\n", prm.somatic_mutation_rate);
-    for (i = 0; i < n_gpus; ++i) {
-        if (ssn_create(&prm, devices[i], (uint32_t)n_slots, BATCH_COLUMNS, BATCH_ENTRIES, &gpus[i].ctx) != SSN_OK) {
-            fprintf(stderr, "[bam-somaticsniper] cannot set up GPU %d: %s\n", devices[i], ssn_last_error());
-            fprintf(stderr, "[bam-somaticsniper] this build scores on sm_100 GPUs only; there is no CPU path\n");
-            ssn_packer_close(pk);
-            return 1;
-        }
-        if (g_device_pileup && ssn_reads_reserve(gpus[i].ctx, 2 * BATCH_ENTRIES, (uint32_t)(BATCH_ENTRIES / 24), BATCH_COLUMNS >> SSN_READ_WINDOW_SHIFT) != SSN_OK) {
-            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
-            ssn_packer_close(pk);
-            return 1;
-        }
-        if (g_device_pileup) {                       /* the slots' read arrays are allocated on first use: do it here */
-            ssn_batch *held[MAX_SLOTS];
-            ssn_reads_view rv;
-            int k, ok = 1;
-            for (k = 0; k < n_slots; ++k) ok = ok && ssn_batch_acquire(gpus[i].ctx, &held[k]) == SSN_OK && ssn_batch_reads_view(gpus[i].ctx, held[k], &rv) == SSN_OK;
-            if (!ok) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); ssn_packer_close(pk); return 1; }
-            for (k = 0; k < n_slots; ++k) ssn_batch_release(gpus[i].ctx, held[k]);
-        }
     }
     fprintf(stderr, "Preparing to snipe some somatics\n");
     if (use_priors) fprintf(stderr, "Using prior probabilities\n");
@@ -280,92 +554,63 @@ int main(int argc, char *argv[])
     ssn_writer_header(wr, fn_fa, normal_id, tumor_id);
     t_setup = now_s() - t_start;
 
-    for (;;) {
-        gpu_t *g = &gpus[next_gpu];
-        ssn_batch *b;
-        ssn_batch_view view;
-        slot_meta *m;
-        uint32_t ncol = 0;
-        uint64_t nent = 0;
-        double t0;
-        t0 = now_s();
-        while (g->in_flight == n_slots)
-            if (drain_one(gpus, fifo, &f_head, &f_count, MAX_GPUS * MAX_SLOTS, pk, wr, &n_sites) != 0) { rc = 1; goto done; }
-        t_gpu_wait += now_s() - t0;
-        if (ssn_batch_acquire(g->ctx, &b) != SSN_OK || ssn_batch_view_get(b, &view) != SSN_OK) {
-            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error());
-            rc = 1; goto done;
-        }
-        m = meta_of(g, b);
-        if (!m) { fprintf(stderr, "[bam-somaticsniper] slot table overflow\n"); rc = 1; goto done; }
-        if (g_device_pileup) {
-            uint32_t nw = 0, nr = 0;
-            uint64_t nb = 0;
-            if (ssn_batch_reads_view(g->ctx, b, &m->rv) != SSN_OK) { fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_last_error()); rc = 1; goto done; }
-            if (ssn_packer_next_reads(pk, &m->rv, BATCH_COLUMNS, BATCH_ENTRIES, m->ref_chars, &nw, &nr, &nb) != SSN_OK) {
-                fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
-                rc = 1; goto done;
-            }
-            if (nw == 0) { ssn_batch_release(g->ctx, b); break; }
-            if (ssn_batch_submit_reads(g->ctx, b, nw, nr, nb, 0) != SSN_OK) {
-                fprintf(stderr, "[bam-somaticsniper] GPU submit failed: %s\n", ssn_last_error());
-                rc = 1; goto done;
-            }
-            fifo[(f_head + f_count) % (MAX_GPUS * MAX_SLOTS)].gpu = next_gpu;
-            f_count += 1; g->in_flight += 1; n_batches += 1;
-            next_gpu = (next_gpu + 1) % n_gpus;
-            continue;
-        }
-        if (ssn_packer_next(pk, &view, &m->map, &ncol, &nent) != SSN_OK) {
-            fprintf(stderr, "[bam-somaticsniper] %s\n", ssn_host_last_error());
-            rc = 1; goto done;
-        }
-        if (ncol == 0) { ssn_batch_release(g->ctx, b); break; }
-        if (ssn_batch_set_size(b, ncol, nent) != SSN_OK || ssn_batch_submit(g->ctx, b, 0) != SSN_OK) {
-            fprintf(stderr, "[bam-somaticsniper] GPU submit failed: %s\n", ssn_last_error());
-            rc = 1; goto done;
-        }
-        fifo[(f_head + f_count) % (MAX_GPUS * MAX_SLOTS)].gpu = next_gpu;
-        f_count += 1; g->in_flight += 1; n_batches += 1;
-        next_gpu = (next_gpu + 1) % n_gpus;
+    rc = stream_pass(&R, out);
+    ssn_shardset_get_stats(R.set, &st);
+    if (rc == 2) {
+        /* second pass, one interval front to back: exact for any input the reference accepts */
+        fprintf(stderr, "[bam-somaticsniper] a read longer than the shards' look-back crosses an interval edge; walking the pair as one interval\n");
+        free_outs(&R);
+        ssn_shardset_close(R.set); R.set = 0;
+        fflush(out);
+        if (ftruncate(fileno(out), 0) != 0 || fseek(out, 0, SEEK_SET) != 0) { fprintf(stderr, "[bam-somaticsniper] cannot rewind the output file\n"); return 1; }
+        ssn_writer_header(wr, fn_fa, normal_id, tumor_id);
+        for (i = 0; i < R.n_gpus; ++i) { gpu_t *g = &R.gpus[i]; g->n_sites = g->n_batches = g->survivors = g->dev_columns = g->dev_entries = g->col_batches = 0; }
+        passes = 2;
+        if (open_set(&R, argv[optind], argv[optind + 1], fn_fa, mapq, 1) != 0) return 1;
+        if (start_feeders(&R) != 0) { join_feeders(&R); return 1; }
+        rc = stream_pass(&R, out);
+        ssn_shardset_get_stats(R.set, &st);
+        if (rc == 2) rc = 1;
     }
-    {
-        double t0 = now_s();
-        while (f_count > 0)
-            if (drain_one(gpus, fifo, &f_head, &f_count, MAX_GPUS * MAX_SLOTS, pk, wr, &n_sites) != 0) { rc = 1; goto done; }
-        t_gpu_wait += now_s() - t0;
-    }
-done:
     fflush(out);
     {
         const char *sp = getenv("SSN_STATS");
         if (sp && *sp) {
             FILE *sf = fopen(sp, "w");
             if (sf) {
-                ssn_packer_stats st;
-                uint64_t launches = 0;
+                uint64_t launches = 0, n_sites = 0, n_batches = 0, survivors = 0, dcol = 0, dent = 0, colb = 0;
+                double t_gpu_wait = 0, t_ctx = 0;
                 const double wall = now_s() - t_start;
-                ssn_packer_get_stats(pk, &st);
-                if (g_device_pileup) { st.columns = g_dev_columns; st.entries = g_dev_entries; }
-                for (i = 0; i < n_gpus; ++i) launches += ssn_kernel_launches(gpus[i].ctx);
+                for (i = 0; i < R.n_gpus; ++i) {
+                    const gpu_t *g = &R.gpus[i];
+                    if (g->ctx) launches += ssn_kernel_launches(g->ctx);
+                    n_sites += g->n_sites; n_batches += g->n_batches; survivors += g->survivors; dcol += g->dev_columns; dent += g->dev_entries;
+                    colb += g->col_batches; t_gpu_wait += g->t_gpu_wait;
+                    if (g->t_setup > t_ctx) t_ctx = g->t_setup;
+                }
+                /* columns / read bases: the device counts what it built, the host packer what it packed */
+                st.columns += dcol; st.entries += dent;
                 fprintf(sf, "{\"columns\": %llu, \"read_bases\": %llu, \"batches\": %llu, \"sites\": %llu, \"records_tumor\": %llu, "
-                        "\"records_normal\": %llu, \"wall_s\": %.6f, \"setup_s\": %.6f, \"pack_wait_s\": %.6f, \"pack_count_s\": %.6f, "
+                        "\"records_normal\": %llu, \"wall_s\": %.6f, \"setup_s\": %.6f, \"gpu_setup_s\": %.6f, \"pack_wait_s\": %.6f, \"pack_count_s\": %.6f, "
                         "\"pack_fill_s\": %.6f, \"gpu_wait_s\": %.6f, \"gpus\": %d, \"threads\": %d, \"slots\": %d, \"kernel_launches\": %llu, "
-                        "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"device_pileup\": %d, \"columns_per_s\": %.1f}\n",
+                        "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"device_pileup\": %d, \"column_route_batches\": %llu, \"shards\": %d, "
+                        "\"passes\": %d, \"columns_per_s\": %.1f}\n",
                         (unsigned long long)st.columns, (unsigned long long)st.entries, (unsigned long long)n_batches,
-                        (unsigned long long)n_sites, (unsigned long long)st.records[0], (unsigned long long)st.records[1], wall, t_setup,
-                        st.t_wait, st.t_count, st.t_fill, t_gpu_wait, n_gpus, n_threads, n_slots, (unsigned long long)launches,
-                        ssn_prefilter_enabled(gpus[0].ctx), (unsigned long long)g_survivors, g_device_pileup,
-                        wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
+                        (unsigned long long)n_sites, (unsigned long long)st.records[0], (unsigned long long)st.records[1], wall, t_setup, t_ctx,
+                        st.t_wait, st.t_count, st.t_fill, t_gpu_wait, R.n_gpus, R.n_threads, R.n_slots, (unsigned long long)launches,
+                        R.gpus[0].ctx ? ssn_prefilter_enabled(R.gpus[0].ctx) : 0, (unsigned long long)survivors, R.device_pileup,
+                        (unsigned long long)colb, (int)n_shards_first, passes, wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
                 fclose(sf);
             }
         }
     }
-    ssn_packer_close(pk);
-    for (i = 0; i < n_gpus; ++i) {
+    free_outs(&R);
+    ssn_shardset_close(R.set);
+    for (i = 0; i < R.n_gpus; ++i) {
         int k;
-        ssn_destroy(gpus[i].ctx);
-        for (k = 0; k < gpus[i].n_meta; ++k) { free(gpus[i].meta[k].map.tid); free(gpus[i].meta[k].map.pos); free(gpus[i].meta[k].map.ref_char); free(gpus[i].meta[k].ref_chars); }
+        gpu_t *g = &R.gpus[i];
+        if (g->ctx) ssn_destroy(g->ctx);
+        for (k = 0; k < g->n_meta; ++k) { free(g->meta[k].map.tid); free(g->meta[k].map.pos); free(g->meta[k].map.ref_char); free(g->meta[k].ref_chars); }
     }
     ssn_writer_destroy(wr);
     fclose(out);

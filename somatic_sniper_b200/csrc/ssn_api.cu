@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <ctime>
+#include <thread>
 #include <vector>
 
 #include "ssn_internal.h"
@@ -158,11 +159,8 @@ static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, u
 {
     b->ctx = ctx; b->state = SLOT_FREE; b->max_columns = max_columns; b->max_entries = max_entries;
     const size_t ent = (size_t)max_entries + 64;
-    CU(cudaMallocHost(&b->h_off, sizeof(uint32_t) * (2 * (size_t)max_columns + 1)));
-    CU(cudaMallocHost(&b->h_bs, ent));
-    CU(cudaMallocHost(&b->h_bq, ent));
-    CU(cudaMallocHost(&b->h_mq, ent));
-    CU(cudaMallocHost(&b->h_ref, (size_t)max_columns + 64));
+    /* the pinned column arrays are allocated when a caller first asks for them (host_columns): a run that ships reads
+     * (ssn_batch_submit_reads) never does */
     CU(cudaMallocHost(&b->h_count, kCountWords * sizeof(uint32_t)));
     CU(cudaMalloc(&b->d_off, sizeof(uint32_t) * (2 * (size_t)max_columns + 1)));
     CU(cudaMalloc(&b->d_bs, ent));
@@ -177,6 +175,20 @@ static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, u
     CU(cudaMallocHost(&b->h_sites, sizeof(ssn_site) * (size_t)b->h_sites_cap));
     CU(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+    return SSN_OK;
+}
+
+/* pinned host arrays of the column batch (ssn_batch_view), on first use */
+static ssn_status host_columns(ssn_batch *b)
+{
+    if (b->h_off) return SSN_OK;
+    const size_t ent = (size_t)b->max_entries + 64;
+    CU(cudaSetDevice(b->ctx->device));
+    CU(cudaMallocHost(&b->h_off, sizeof(uint32_t) * (2 * (size_t)b->max_columns + 1)));
+    CU(cudaMallocHost(&b->h_bs, ent));
+    CU(cudaMallocHost(&b->h_bq, ent));
+    CU(cudaMallocHost(&b->h_mq, ent));
+    CU(cudaMallocHost(&b->h_ref, (size_t)b->max_columns + 64));
     return SSN_OK;
 }
 
@@ -214,31 +226,97 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
 #define SSN_TRACE(what) do { if (trace) { double n_ = wall_now(); fprintf(stderr, "[ssn_create] %-28s %.3f s\n", what, n_ - tt); tt = n_; } } while (0)
     if (!p || !out || n_slots == 0 || max_columns == 0) { ssn_set_error("ssn_create: bad argument"); return SSN_ERR_ARG; }
     if (max_entries >= (1ull << 32) - 64) { ssn_set_error("ssn_create: max_entries must stay below 2^32"); return SSN_ERR_ARG; }
-    int ndev = 0;
-    CU(cudaGetDeviceCount(&ndev));
-    if (device < 0 || device >= ndev) { ssn_set_error("ssn_create: no CUDA device %d (found %d)", device, ndev); return SSN_ERR_CUDA; }
-    CU(cudaSetDevice(device));
-    cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, device));
-    SSN_TRACE("device query (context)");
-    if (prop.major < 10) { ssn_set_error("ssn_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return SSN_ERR_CUDA; }
-
     ssn_ctx *ctx = new ssn_ctx();
     ctx->device = device; ctx->params = *p; ctx->next_seq = 1; ctx->launches = 0;
-    ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
     ctx->d_flush = nullptr; ctx->flush_bytes = 0;
     ctx->timer_next = 0; ctx->kernel_ms = 0; ctx->kernel_n = 0; ctx->l2_window_bytes = 0;
     ctx->prefilter_ms = 0; ctx->score_ms = 0; ctx->d_pf_ab = ctx->d_pf_h = ctx->d_pf_F = ctx->d_pf_vt = nullptr; ctx->pf_on = false;
     memset(&ctx->pf, 0, sizeof(ctx->pf));
+    memset(&ctx->tab, 0, sizeof(ctx->tab));
     ctx->survivor_frac = 1.0; ctx->last_slot = -1;
+    /* the model tables (x87 long double, ~0.5 s of host arithmetic) are built on a thread of their own while this one
+     * creates the CUDA context, the streams and the batch slots */
+    int tables_rc = 0, pf_rc = 0;
+    std::thread table_thread([&]() {
+        tables_rc = ssn_tables_build(p, &ctx->tab);
+        if (tables_rc == 0) pf_rc = ssn_prefilter_build(&ctx->tab, (int)(ctx->tab.q_r + 0.5), &ctx->pf);
+    });
+    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } table_joiner{table_thread};
+    auto fail_early = [&](ssn_status st) {       /* before any device object exists */
+        table_thread.join();
+        ssn_prefilter_free(&ctx->pf);
+        if (tables_rc == 0) ssn_tables_free(&ctx->tab);
+        delete ctx;
+        return st;
+    };
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess) { ssn_set_error("ssn_create: no usable CUDA driver/device (%s)", cudaGetErrorString(cudaGetLastError())); return fail_early(SSN_ERR_CUDA); }
+    if (device < 0 || device >= ndev) { ssn_set_error("ssn_create: no CUDA device %d (found %d)", device, ndev); return fail_early(SSN_ERR_CUDA); }
+    if (cudaSetDevice(device) != cudaSuccess) { ssn_set_error("ssn_create: cudaSetDevice(%d) failed", device); return fail_early(SSN_ERR_CUDA); }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { ssn_set_error("ssn_create: cudaGetDeviceProperties failed"); return fail_early(SSN_ERR_CUDA); }
+    SSN_TRACE("device query");
+    if (prop.major < 10) { ssn_set_error("ssn_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); return fail_early(SSN_ERR_CUDA); }
+    ctx->num_sms = prop.multiProcessorCount; ctx->smem_optin = prop.sharedMemPerBlockOptin;
     const char *env = getenv("SSN_SMEM_WORDS");
     ctx->smem_words_default = env ? (uint32_t)atoi(env) : (uint32_t)kFastWords * 32u;
     ctx->smem_words_default = (ctx->smem_words_default + 31u) / 32u * 32u;
-    if (ssn_tables_build(p, &ctx->tab) != 0) { ssn_set_error("ssn_create: table construction failed (n_hap=%d)", p->n_hap); delete ctx; return SSN_ERR_ARG; }
 
-    SSN_TRACE("host tables");
+    CU(cudaFree(0));
+    SSN_TRACE("CUDA context");
+    CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&ctx->t0));
+    CU(cudaEventCreate(&ctx->t1));
+    cudaFuncAttributes fa;
+    CU(cudaFuncGetAttributes(&fa, ssn_score_kernel<true>));
+    ctx->smem_static = fa.sharedSizeBytes;
+    const int max_dyn = (int)(ctx->smem_optin - ctx->smem_static);
+    CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+    CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+    CU(cudaFuncSetAttribute(ssn_prefilter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pf_smem_bytes()));
     const size_t coef_n = (size_t)64 * 65536, lhet_n = 65536;
     CU(cudaMalloc(&ctx->d_coef_lhet, sizeof(double) * (coef_n + lhet_n)));
+
+    /* keep coef+lhet resident in L2: persisting carve-out + per-stream access-policy window */
+    size_t want = sizeof(double) * (coef_n + lhet_n);
+    size_t persist = std::min<size_t>(want, (size_t)prop.persistingL2CacheMaxSize);
+    if (getenv("SSN_NO_L2_WINDOW")) persist = 0;               /* measurement knob: the tables compete for L2 like any other line */
+    if (persist > 0 && prop.accessPolicyMaxWindowSize > 0) {
+        CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist));
+        ctx->l2_window_bytes = std::min<size_t>(want, (size_t)prop.accessPolicyMaxWindowSize);
+    }
+    SSN_TRACE("kernel attributes, L2 limit");
+    for (uint32_t i = 0; i < n_slots; ++i) {
+        ssn_batch *b = new ssn_batch();
+        memset((void*)b, 0, sizeof(*b));
+        b->index = (int)i;
+        ctx->slots.push_back(b);
+        ssn_status st = slot_alloc(ctx, b, max_columns, max_entries);
+        if (st != SSN_OK) { table_thread.join(); ssn_destroy(ctx); return st; }
+        if (ctx->l2_window_bytes) {
+            cudaStreamAttrValue attr;
+            memset(&attr, 0, sizeof(attr));
+            attr.accessPolicyWindow.base_ptr = ctx->d_coef_lhet;
+            attr.accessPolicyWindow.num_bytes = ctx->l2_window_bytes;
+            attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)ctx->l2_window_bytes);
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            CU(cudaStreamSetAttribute(b->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+        }
+    }
+    SSN_TRACE("batch slots");
+    ctx->timers.resize(64);
+    for (auto &t : ctx->timers) {
+        CU(cudaEventCreate(&t.a));
+        CU(cudaEventCreate(&t.m));
+        CU(cudaEventCreate(&t.b));
+        t.pending = false; t.filtered = false;
+    }
+
+    table_thread.join();
+    SSN_TRACE("wait for the host tables");
+    if (tables_rc != 0) { ssn_set_error("ssn_create: table construction failed (n_hap=%d)", p->n_hap); ssn_destroy(ctx); return SSN_ERR_ARG; }
+    if (pf_rc != 0) { ssn_set_error("ssn_create: out of memory (pre-filter tables)"); ssn_destroy(ctx); return SSN_ERR_NOMEM; }
     CU(cudaMemcpy(ctx->d_coef_lhet, ctx->tab.coef, sizeof(double) * coef_n, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(ctx->d_coef_lhet + coef_n, ctx->tab.lhet, sizeof(double) * lhet_n, cudaMemcpyHostToDevice));
     CU(cudaMalloc(&ctx->d_fk, sizeof(double) * 256));
@@ -256,7 +334,6 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     M.cap_mapq = p->cap_mapq; M.min_somatic_qual = p->min_somatic_qual;
     M.include_loh = p->include_loh; M.include_gor = p->include_gor; M.use_joint = p->use_joint_priors;
 
-    if (ssn_prefilter_build(&ctx->tab, M.q_r_int, &ctx->pf) != 0) { ssn_set_error("ssn_create: out of memory (pre-filter tables)"); ssn_destroy(ctx); return SSN_ERR_NOMEM; }
     ctx->pf_on = ctx->pf.enabled && getenv("SSN_NO_PREFILTER") == nullptr;
     CU(cudaMalloc(&ctx->d_pf_ab, sizeof(float) * 4 * SSN_PF_N * SSN_PF_N));
     CU(cudaMemcpy(ctx->d_pf_ab, ctx->pf.ab, sizeof(float) * 4 * SSN_PF_N * SSN_PF_N, cudaMemcpyHostToDevice));
@@ -268,51 +345,6 @@ extern "C" ssn_status ssn_create(const ssn_params *p, int device, uint32_t n_slo
     CU(cudaMemcpy(ctx->d_pf_vt, ctx->pf.vt, sizeof(float) * SSN_PF_N * SSN_PF_VK * SSN_PF_VS, cudaMemcpyHostToDevice));
     ctx->dpf.ab = reinterpret_cast<const float4*>(ctx->d_pf_ab); ctx->dpf.h = ctx->d_pf_h; ctx->dpf.F = ctx->d_pf_F; ctx->dpf.vt = ctx->d_pf_vt;
     SSN_TRACE("table upload");
-    CU(cudaStreamCreateWithFlags(&ctx->main_stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&ctx->t0));
-    CU(cudaEventCreate(&ctx->t1));
-    cudaFuncAttributes fa;
-    CU(cudaFuncGetAttributes(&fa, ssn_score_kernel<true>));
-    ctx->smem_static = fa.sharedSizeBytes;
-    const int max_dyn = (int)(ctx->smem_optin - ctx->smem_static);
-    CU(cudaFuncSetAttribute(ssn_score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
-    CU(cudaFuncSetAttribute(ssn_score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
-    CU(cudaFuncSetAttribute(ssn_prefilter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pf_smem_bytes()));
-
-    /* keep coef+lhet resident in L2: persisting carve-out + per-stream access-policy window */
-    size_t want = sizeof(double) * (coef_n + lhet_n);
-    size_t persist = std::min<size_t>(want, (size_t)prop.persistingL2CacheMaxSize);
-    if (persist > 0 && prop.accessPolicyMaxWindowSize > 0) {
-        CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist));
-        ctx->l2_window_bytes = std::min<size_t>(want, (size_t)prop.accessPolicyMaxWindowSize);
-    }
-    SSN_TRACE("kernel attributes, L2 limit");
-    for (uint32_t i = 0; i < n_slots; ++i) {
-        ssn_batch *b = new ssn_batch();
-        memset((void*)b, 0, sizeof(*b));
-        b->index = (int)i;
-        ctx->slots.push_back(b);
-        ssn_status st = slot_alloc(ctx, b, max_columns, max_entries);
-        if (st != SSN_OK) { ssn_destroy(ctx); return st; }
-        if (ctx->l2_window_bytes) {
-            cudaStreamAttrValue attr;
-            memset(&attr, 0, sizeof(attr));
-            attr.accessPolicyWindow.base_ptr = ctx->d_coef_lhet;
-            attr.accessPolicyWindow.num_bytes = ctx->l2_window_bytes;
-            attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)ctx->l2_window_bytes);
-            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-            CU(cudaStreamSetAttribute(b->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
-        }
-    }
-    SSN_TRACE("batch slots (pinned + device)");
-    ctx->timers.resize(64);
-    for (auto &t : ctx->timers) {
-        CU(cudaEventCreate(&t.a));
-        CU(cudaEventCreate(&t.m));
-        CU(cudaEventCreate(&t.b));
-        t.pending = false; t.filtered = false;
-    }
     *out = ctx;
     return SSN_OK;
 }
@@ -391,6 +423,8 @@ extern "C" ssn_status ssn_batch_release(ssn_ctx *ctx, ssn_batch *b)
 extern "C" ssn_status ssn_batch_view_get(ssn_batch *b, ssn_batch_view *out)
 {
     if (!b || !out) { ssn_set_error("ssn_batch_view_get: null"); return SSN_ERR_ARG; }
+    ssn_status hs = host_columns(b);
+    if (hs != SSN_OK) return hs;
     out->off = b->h_off; out->bs = b->h_bs; out->bq = b->h_bq; out->mq = b->h_mq; out->ref_nt16 = b->h_ref;
     out->max_columns = b->max_columns; out->max_entries = b->max_entries;
     return SSN_OK;
@@ -610,6 +644,7 @@ extern "C" ssn_status ssn_batch_submit(ssn_ctx *ctx, ssn_batch *b, uint32_t flag
 {
     if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_submit: bad batch"); return SSN_ERR_ARG; }
     if (b->state != SLOT_FILLING) { ssn_set_error("ssn_batch_submit: batch was not acquired"); return SSN_ERR_STATE; }
+    if (!b->h_off) { ssn_set_error("ssn_batch_submit: the batch was never filled (ssn_batch_view_get)"); return SSN_ERR_STATE; }
     CU(cudaSetDevice(ctx->device));
     ssn_status st = scan_offsets(b);
     if (st != SSN_OK) return st;
@@ -793,6 +828,8 @@ extern "C" ssn_status ssn_batch_download_columns(ssn_ctx *ctx, ssn_batch *b)
     if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_download_columns: bad batch"); return SSN_ERR_ARG; }
     if (!b->from_reads || b->reads_pending || !b->resident) { ssn_set_error("ssn_batch_download_columns: not a finished read batch"); return SSN_ERR_STATE; }
     CU(cudaSetDevice(ctx->device));
+    ssn_status hs = host_columns(b);
+    if (hs != SSN_OK) return hs;
     CU(cudaMemcpyAsync(b->h_off, b->d_off, sizeof(uint32_t) * (2 * (size_t)b->ncol + 1), cudaMemcpyDeviceToHost, b->stream));
     if (b->nent) {
         CU(cudaMemcpyAsync(b->h_bs, b->d_bs, b->nent, cudaMemcpyDeviceToHost, b->stream));
@@ -848,6 +885,7 @@ extern "C" ssn_status ssn_batch_upload(ssn_ctx *ctx, ssn_batch *b)
 {
     if (!ctx || !b || b->ctx != ctx) { ssn_set_error("ssn_batch_upload: bad batch"); return SSN_ERR_ARG; }
     if (b->state != SLOT_FILLING) { ssn_set_error("ssn_batch_upload: batch was not acquired"); return SSN_ERR_STATE; }
+    if (!b->h_off) { ssn_set_error("ssn_batch_upload: the batch was never filled (ssn_batch_view_get)"); return SSN_ERR_STATE; }
     CU(cudaSetDevice(ctx->device));
     ssn_status st = scan_offsets(b);
     if (st != SSN_OK) return st;

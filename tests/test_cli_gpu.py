@@ -83,12 +83,12 @@ def test_device_pileup_on_integration_data(ct, run, tmp_path):
 def test_device_pileup_matches_host_packer_and_reference(ct, synthetic_pair, opts, tmp_path):
     p = synthetic_pair
     host, dev, ref = str(tmp_path / "host"), str(tmp_path / "dev"), str(tmp_path / "ref")
-    r0 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], host, opts, stats=str(tmp_path / "s0.json"))
+    r0 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], host, opts, env={"SSN_DEVICE_PILEUP": 0}, stats=str(tmp_path / "s0.json"))
     r1 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], dev, opts, env={"SSN_DEVICE_PILEUP": 1, "SSN_DEVICES": "0,0"},
                     stats=str(tmp_path / "s1.json"))
     assert r0["rc"] == 0 and r1["rc"] == 0, r1["stderr"]
     assert ct.comparable(dev) == ct.comparable(host)
-    assert r1["stats"]["device_pileup"] == 1 and r1["stats"]["columns"] == r0["stats"]["columns"]
+    assert r0["stats"]["device_pileup"] == 0 and r1["stats"]["device_pileup"] == 1 and r1["stats"]["columns"] == r0["stats"]["columns"]
     assert r1["stats"]["read_bases"] == r0["stats"]["read_bases"] and r1["stats"]["sites"] == r0["stats"]["sites"] > 20
     if ct.reference_available():
         ct.run_cli(ct.REF_CLI, p["fasta"], p["tumor"], p["normal"], ref, opts)
@@ -103,7 +103,7 @@ def test_two_scoring_contexts_and_small_slots(ct, synthetic_pair, tmp_path):
     p = synthetic_pair
     mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
     r1 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], mine, ["-F", "vcf", "-Q", "0"],
-                    env={"SSN_DEVICES": "0,0", "SSN_SLOTS": 1, "SSN_THREADS": 3}, stats=str(tmp_path / "stats.json"))
+                    env={"SSN_DEVICES": "0,0", "SSN_SLOTS": 1, "SSN_THREADS": 3, "SSN_DEVICE_PILEUP": 0, "SSN_SHARD_WINDOWS": 3}, stats=str(tmp_path / "stats.json"))
     r2 = ct.run_cli(ct.REF_CLI, p["fasta"], p["tumor"], p["normal"], ref, ["-F", "vcf", "-Q", "0"])
     assert r1["rc"] == 0, r1["stderr"]
     assert ct.comparable(mine) == ct.comparable(ref)
@@ -123,3 +123,139 @@ def test_stdin_tumor_and_bad_format(ct, synthetic_pair, tmp_path):
         assert ct.comparable(out) == ct.comparable(ref)
     r = subprocess.run([ct.CLI, "-f", p["fasta"], "-F", "gff", p["tumor"], p["normal"], out], stderr=subprocess.PIPE)
     assert r.returncode == 1 and b"unknown output format: 'gff'. Abort!" in r.stderr
+
+
+# ---- region shards through the whole program ---------------------------------------------------
+
+@pytest.mark.parametrize("env,opts", [
+    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1}, []),
+    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0"}, ["-F", "vcf", "-Q", "0"]),
+    ({"SSN_SHARD_WINDOWS": 1, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0,0", "SSN_THREADS": 3, "SSN_SLOTS": 2}, ["-J", "-F", "vcf"]),
+    ({"SSN_SHARD_WINDOWS": 3, "SSN_SHARD_LOOKBACK": 2, "SSN_DEVICE_PILEUP": 0, "SSN_DEVICES": "0,0"}, ["-q", "1", "-Q", "0", "-L", "-G"]),
+], ids=["1ctx", "2ctx_vcf", "3ctx_joint", "2ctx_host_columns"])
+def test_region_shards_match_the_single_process_reference(ct, synthetic_pair, env, opts, tmp_path):
+    """The 4-contig pair cut into >= 8 intervals, scored on 1-3 contexts (one feeder thread each, shards taken in genome
+    order, output merged in order): byte-identical to the unmodified reference binary's single front-to-back walk."""
+    if not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    p = synthetic_pair
+    mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
+    r1 = ct.run_cli(ct.CLI, p["fasta"], p["tumor"], p["normal"], mine, opts, env=env, stats=str(tmp_path / "stats.json"))
+    r2 = ct.run_cli(ct.REF_CLI, p["fasta"], p["tumor"], p["normal"], ref, opts)
+    assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+    assert ct.comparable(mine) == ct.comparable(ref)
+    st = r1["stats"]
+    assert st["shards"] >= 8 and st["passes"] == 1 and st["gpus"] == len(str(env.get("SSN_DEVICES", "0")).split(","))
+    assert sum(1 for _ in open(ref)) > 20
+
+
+def test_keep_rule_on_a_shard_edge_through_the_cli(ct, tmp_path):
+    """QUIRK B1 (sniper_pileup.c:216) with the target change exactly on an interval edge: the reference binary drops
+    chr2's first read (its end 10 is not beyond chr1's last passing read start 10), and so must the sharded run."""
+    import numpy as np
+    from somatic_sniper_b200 import simbam as sim
+    from test_packer import _simple_reads, _write_pair
+    contigs = [("chr1", 8192), ("chr2", 20000)]
+    ref = [("chr1", np.frombuffer(b"ACGT" * 2048, np.uint8)), ("chr2", np.frombuffer(b"TGCA" * 5000, np.uint8))]
+    outs = {}
+    for last_start in (9, 10):
+        d = tmp_path / str(last_start)
+        d.mkdir()
+        def mk(alt):
+            return (_simple_reads(0, [0, 5, last_start]) + _simple_reads(0, [40], flag=0x400)
+                    + _simple_reads(1, [0], length=10, base=alt) + _simple_reads(1, [0, 0, 4], length=10, base=alt)
+                    + _simple_reads(1, [8190, 8200, 16380], length=30))
+        t, n, fa = _write_pair(sim, str(d), contigs, ref, mk("C"), mk("T"))
+        mine, want = str(d / "mine"), str(d / "ref")
+        r1 = ct.run_cli(ct.CLI, fa, t, n, mine, ["-Q", "0"], env={"SSN_SHARD_WINDOWS": 1, "SSN_SHARD_LOOKBACK": 1}, stats=str(d / "s.json"))
+        assert r1["rc"] == 0, r1["stderr"]
+        assert r1["stats"]["shards"] == 4
+        if ct.reference_available():
+            ct.run_cli(ct.REF_CLI, fa, t, n, want, ["-Q", "0"])
+            assert ct.comparable(mine) == ct.comparable(want)
+        outs[last_start] = open(mine).read()
+    # the dropped read changes the tumor depth at chr2:1 (column 8 of the classic format is not depth; compare whole lines)
+    assert outs[9] != outs[10] and "chr2\t1\t" in outs[9]
+
+
+def test_long_read_across_an_interval_edge_falls_back_to_one_walk(ct, tmp_path):
+    """A read with a 20 kb N skip begins further in front of an interval edge than the look-back and reaches behind it: the
+    sharded pass notices, the program walks the pair again as one interval, and the output equals the reference's."""
+    import numpy as np
+    from somatic_sniper_b200 import simbam as sim
+    from test_packer import _simple_reads, _write_pair
+    contigs = [("chr1", 60000)]
+    ref = [("chr1", np.frombuffer(b"ACGT" * 15000, np.uint8))]
+    def mk(alt):
+        long_read = [(0, 100, 60, 0, "10M20000N10M", alt * 20, [30] * 20)]
+        return (_simple_reads(0, [50, 90]) + long_read + _simple_reads(0, [200, 8300], length=30)
+                + _simple_reads(0, [20100, 20105, 20108], length=30, base=alt) + _simple_reads(0, [30000], length=30))
+    t, n, fa = _write_pair(sim, str(tmp_path), contigs, ref, mk("G"), mk("A"))
+    mine, want = str(tmp_path / "mine"), str(tmp_path / "ref")
+    r1 = ct.run_cli(ct.CLI, fa, t, n, mine, ["-Q", "0", "-F", "vcf"], env={"SSN_SHARD_WINDOWS": 1, "SSN_SHARD_LOOKBACK": 1}, stats=str(tmp_path / "s.json"))
+    assert r1["rc"] == 0, r1["stderr"]
+    assert r1["stats"]["passes"] == 2 and "one interval" in r1["stderr"]
+    if ct.reference_available():
+        ct.run_cli(ct.REF_CLI, fa, t, n, want, ["-Q", "0", "-F", "vcf"])
+        assert ct.comparable(mine) == ct.comparable(want)
+        assert sum(1 for l in open(want) if not l.startswith("#")) >= 1
+
+
+def test_window_too_deep_for_a_read_batch_takes_the_column_route(ct, tmp_path):
+    """Windows whose reads exceed a read batch (~4600x over 8192 positions; a slot holds 32 Mi read-bases) are packed into
+    columns by the host, and the reads route resumes behind them (the contig's last, partial window fits)."""
+    if not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    pair = ct.make_pair_fast(str(tmp_path), [("chr1", 20000)], 3000, 1600, seed=5)
+    mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
+    r1 = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine, ["-Q", "30"], stats=str(tmp_path / "s.json"))
+    r2 = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, ["-Q", "30"])
+    assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+    assert ct.comparable(mine) == ct.comparable(ref)
+    st = r1["stats"]
+    assert st["column_route_batches"] >= 2 and st["batches"] > st["column_route_batches"] and st["device_pileup"] == 1
+
+
+# ---- BASELINE.json configs 2-4 against the live reference binary ---------------------------------------------------
+
+def test_config2_one_megabase_classic(ct, tmp_path):
+    """configs[1]: synthetic 1 Mb region, normal 30x / tumor 60x, -q 1 -Q 15, classic output."""
+    if not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    pair = ct.make_pair_fast(str(tmp_path), [("chr1", 1000000)], 60, 30, seed=1234, level=6)
+    mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
+    opts = ["-q", "1", "-Q", "15", "-F", "classic"]
+    r1 = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine, opts, stats=str(tmp_path / "s.json"))
+    r2 = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, opts)
+    assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+    assert ct.comparable(mine) == ct.comparable(ref)
+    assert r1["stats"]["columns"] > 990000 and sum(1 for _ in open(ref)) > 100
+
+
+def test_config3_joint_vcf_on_several_megabases(ct, tmp_path):
+    """configs[2] at 6 Mb (the 50 Mb run lives in profiles/): -J -s 0.01 -T 0.85 -F vcf, two contigs, region shards on."""
+    if not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    pair = ct.make_pair_fast(str(tmp_path), [("chr1", 4000000), ("chr2", 2000000)], 60, 30, seed=77)
+    mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
+    opts = ["-J", "-s", "0.01", "-T", "0.85", "-F", "vcf"]
+    r1 = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine, opts, env={"SSN_DEVICES": "0,0"}, stats=str(tmp_path / "s.json"))
+    r2 = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, opts)
+    assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+    assert ct.comparable(mine) == ct.comparable(ref)
+    assert r1["stats"]["shards"] >= 4 and r1["stats"]["columns"] > 5900000
+    assert sum(1 for l in open(ref) if not l.startswith("#")) > 300
+
+
+def test_config4_targeted_panel_depth(ct, tmp_path):
+    """configs[3]: targeted panel at 2000x / 1000x (per-column sort and dependency model under depth): 8 targets x 5 kb."""
+    if not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    pair = ct.make_pair_fast(str(tmp_path), [("t%02d" % i, 5000) for i in range(8)], 2000, 1000, seed=9)
+    mine, ref = str(tmp_path / "mine"), str(tmp_path / "ref")
+    for opts in ([], ["-J", "-F", "vcf", "-Q", "40"]):
+        r1 = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine, opts, stats=str(tmp_path / "s.json"))
+        r2 = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, opts)
+        assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+        assert ct.comparable(mine) == ct.comparable(ref)
+    assert r1["stats"]["read_bases"] > 8 * 4000 * 2900

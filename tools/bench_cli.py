@@ -1,60 +1,137 @@
 #!/usr/bin/env python
-"""BAM-level end-to-end timing (BASELINE.json configs[1]-style): this repo's bam-somaticsniper (BGZF inflate -> packer ->
-H2D -> kernel -> writers) against the unmodified reference binary (oracle/_ref, single process) on the same synthetic
-tumor/normal pair, with a byte comparison of the two output files.
-    python tools/bench_cli.py --len 1000000 [--depth-t 60 --depth-n 30] [--args "-J -F vcf"] [--out gpurun_out/cli_bench.json]"""
-import argparse, json, os, shlex, sys, tempfile, time
+"""BAM-level end-to-end timing: this repo's bam-somaticsniper (region shards -> BGZF inflate -> read batches -> H2D -> device
+pileup -> pre-filter/scoring kernels -> writers) against the unmodified reference binary (oracle/_ref) on the same synthetic
+tumor/normal pair, with a byte comparison of the output files.
+
+    python tools/bench_cli.py --len 1000000                               # one contig, Python simulator, single reference process
+    python tools/bench_cli.py --fast --contigs 16 --len 8000000 --gpus 1,2,4,8 --reference split
+        # BASELINE.json configs[4] tiling: 16 contigs x 8 Mb = 128 Mb of 30x/60x; the CPU baseline is the reference binary
+        # region-split by contig over all host cores (the reference has no region option, so every
+        # process gets a BAM pair holding one contig's reads).  Parity there is judged on everything but the first 1000
+        # positions of each later contig: the single front-to-back walk drops the first read of every later contig (QUIRK
+        # B1), a split run cannot."""
+import argparse, concurrent.futures, json, os, shlex, shutil, subprocess, sys, tempfile, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from somatic_sniper_b200 import cli_tools as ct
+
+
+def _lines_outside_b1(path, first_contig):
+    keep = []
+    with open(path, "rb") as f:
+        for l in f:
+            if l.startswith(b"#"):
+                if not (l.startswith(b"##fileDate") or l.startswith(b"##reference=")):
+                    keep.append(l)
+                continue
+            c = l.split(b"\t", 3)
+            if c[0] != first_contig and c[1].isdigit() and int(c[1]) <= 1000:
+                continue
+            keep.append(l)
+    return keep
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--len", type=int, default=1_000_000)
+    ap.add_argument("--contigs", type=int, default=1)
     ap.add_argument("--depth-t", type=float, default=60.0)
     ap.add_argument("--depth-n", type=float, default=30.0)
-    ap.add_argument("--targets", type=int, default=0, help="panel mode: this many 5 kb targets instead of one contig")
+    ap.add_argument("--targets", type=int, default=0, help="panel mode: this many 5 kb targets instead of contigs")
+    ap.add_argument("--fast", action="store_true", help="tools/simbam_fast.c instead of the Python simulator")
+    ap.add_argument("--level", type=int, default=1, help="zlib level of the generated BAMs (--fast)")
     ap.add_argument("--args", default="")
-    ap.add_argument("--repeat", type=int, default=3)
-    ap.add_argument("--no-reference", action="store_true")
+    ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--gpus", default="1")
+    ap.add_argument("--reference", choices=["none", "single", "split"], default="single")
     ap.add_argument("--threads", default=None)
-    ap.add_argument("--device-pileup", action="store_true", help="SSN_DEVICE_PILEUP=1: ship the reads, build the columns on the GPU")
+    ap.add_argument("--env", default="", help="extra environment for this repo's CLI, e.g. 'SSN_DEVICE_PILEUP=0 SSN_SLOTS=4'")
+    ap.add_argument("--workdir", default=None)
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
-    w = tempfile.mkdtemp(prefix="ssn_bench_")
+    w = a.workdir or tempfile.mkdtemp(prefix="ssn_bench_")
+    os.makedirs(w, exist_ok=True)
     t0 = time.perf_counter()
-    contigs = [("chr1", a.len)] if not a.targets else [("t%03d" % i, 5000) for i in range(a.targets)]
-    pair = ct.make_pair(w, contigs, a.depth_t, a.depth_n, seed=1234, n_runs=0, special=True)
+    if a.targets:
+        contigs = [("t%03d" % i, 5000) for i in range(a.targets)]
+    else:
+        contigs = [("chr%d" % (i + 1), a.len) for i in range(a.contigs)]
+    if a.fast:
+        if a.reference == "split":
+            os.environ["SSN_SIMBAM_SPLIT"] = "1"
+        pair = ct.make_pair_fast(w, contigs, a.depth_t, a.depth_n, seed=1234, level=a.level)
+    else:
+        pair = ct.make_pair(w, contigs, a.depth_t, a.depth_n, seed=1234, n_runs=0, special=True)
     t_sim = time.perf_counter() - t0
     opts = shlex.split(a.args)
     env = {"SSN_THREADS": a.threads} if a.threads else {}
-    if a.device_pileup:
-        env["SSN_DEVICE_PILEUP"] = 1
-    runs = []
-    for i in range(a.repeat):
-        mine = os.path.join(w, "mine.out")
-        r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine, opts, env=env, stats=os.path.join(w, "stats.json"))
-        assert r["rc"] == 0, r["stderr"]
-        runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
-    best = min(runs, key=lambda x: x["wall_s"])
-    st = best["stats"]
-    res = dict(workload="synthetic %d bp, tumor %gx / normal %gx, 2x150 reads, args '%s'" % (pair["columns"], a.depth_t, a.depth_n, a.args),
+    for kv in a.env.split():
+        k, v = kv.split("=", 1)
+        env[k] = v
+    res = dict(workload="synthetic %d contig(s) x %d bp = %d positions, tumor %gx / normal %gx, 150 bp reads, args '%s'" % (
+                   len(contigs), contigs[0][1], pair["columns"], a.depth_t, a.depth_n, a.args),
+               generator="tools/simbam_fast.c, zlib level %d" % a.level if a.fast else "somatic_sniper_b200/simbam.py, zlib level 6",
                reads=[pair["reads_tumor"], pair["reads_normal"]], bam_bytes=[os.path.getsize(pair["tumor"]), os.path.getsize(pair["normal"])],
-               simulate_s=t_sim, b200=dict(wall_s=best["wall_s"], setup_s=st["setup_s"], stream_s=st["wall_s"] - st["setup_s"], columns=st["columns"],
-                                           columns_per_s_stream=st["columns_per_s"], columns_per_s_wall=st["columns"] / best["wall_s"],
-                                           all_walls=[x["wall_s"] for x in runs], stats=st))
-    if not a.no_reference and ct.reference_available():
+               simulate_s=t_sim, host_cores=os.cpu_count(), runs={})
+    mine = os.path.join(w, "mine.out")
+    for g in [int(x) for x in a.gpus.split(",")]:
+        runs = []
+        for i in range(a.repeat):
+            e = dict(env)
+            e["SSN_GPUS"] = g
+            r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine + ".%d" % g, opts, env=e, stats=os.path.join(w, "stats.json"))
+            assert r["rc"] == 0, r["stderr"]
+            runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
+        best = min(runs, key=lambda x: x["wall_s"])
+        st = best["stats"]
+        res["runs"]["gpus_%d" % g] = dict(wall_s=best["wall_s"], setup_s=st["setup_s"], stream_s=st["wall_s"] - st["setup_s"], columns=st["columns"],
+                                          columns_per_s_stream=st["columns_per_s"], columns_per_s_wall=st["columns"] / best["wall_s"],
+                                          all_walls=[x["wall_s"] for x in runs], stats=st)
+        if g != int(a.gpus.split(",")[0]):
+            res["runs"]["gpus_%d" % g]["identical_to_first_gpu_count"] = ct.comparable(mine + ".%d" % g) == ct.comparable(mine + ".%s" % a.gpus.split(",")[0])
+    first = mine + ".%s" % a.gpus.split(",")[0]
+    ncols = res["runs"]["gpus_%s" % a.gpus.split(",")[0]]["columns"]
+    if a.reference == "single" and ct.reference_available():
         ref = os.path.join(w, "ref.out")
         r = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, opts)
-        same = ct.comparable(ref) == ct.comparable(os.path.join(w, "mine.out"))
-        res["reference"] = dict(wall_s=r["wall_s"], columns_per_s_wall=st["columns"] / r["wall_s"], processes=1, rc=r["rc"])
-        res["identical_output"] = bool(same)
+        res["reference"] = dict(kind="single process", wall_s=r["wall_s"], columns_per_s_wall=ncols / r["wall_s"], processes=1, rc=r["rc"])
+        res["identical_output"] = bool(ct.comparable(ref) == ct.comparable(first))
         res["output_lines"] = sum(1 for _ in open(ref, "rb"))
-        res["speedup_wall"] = r["wall_s"] / best["wall_s"]
+    elif a.reference == "split" and ct.reference_available():
+        cores = os.cpu_count() or 1
+
+        def one(i):
+            o = os.path.join(w, "ref.%d.out" % i)
+            r = ct.run_cli(ct.REF_CLI, pair["fasta"], os.path.join(w, "tumor.%d.bam" % i), os.path.join(w, "normal.%d.bam" % i), o, opts)
+            return r["rc"], r["wall_s"]
+        t0 = time.perf_counter()
+        with concurrent.futures.ThreadPoolExecutor(cores) as ex:
+            rs = list(ex.map(one, range(len(contigs))))
+        wall = time.perf_counter() - t0
+        ref = os.path.join(w, "ref.out")
+        with open(ref, "wb") as f:
+            for i in range(len(contigs)):
+                with open(os.path.join(w, "ref.%d.out" % i), "rb") as g_:
+                    for l in g_:
+                        if i == 0 or not l.startswith(b"#"):
+                            f.write(l)
+        fc = contigs[0][0].encode()
+        a_, b_ = _lines_outside_b1(ref, fc), _lines_outside_b1(first, fc)
+        res["reference"] = dict(kind="region-split by contig, %d processes on %d cores" % (len(contigs), cores), wall_s=wall,
+                                columns_per_s_wall=ncols / wall, processes=len(contigs), cores=cores, rc=max(r[0] for r in rs),
+                                slowest_process_s=max(r[1] for r in rs), sum_process_s=sum(r[1] for r in rs))
+        res["identical_output"] = bool(a_ == b_)
+        res["identical_output_scope"] = "every line except positions <= 1000 of contigs 2..N (QUIRK B1 differs between one walk and a split run)"
+        res["output_lines"] = len(a_)
+        res["lines_in_b1_zones"] = [sum(1 for _ in open(ref, "rb")) - len(a_), sum(1 for _ in open(first, "rb")) - len(b_)]
+    if "reference" in res:
+        g0 = res["runs"]["gpus_%s" % a.gpus.split(",")[0]]
+        res["speedup_wall"] = res["reference"]["wall_s"] / g0["wall_s"]
     print(json.dumps(res), flush=True)
     if a.out:
         with open(a.out, "w") as f:
             json.dump(res, f, indent=1)
+    if not a.workdir:
+        shutil.rmtree(w, ignore_errors=True)
 
 
 if __name__ == "__main__":
