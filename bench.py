@@ -42,6 +42,15 @@ STREAMS = 8                     # value: resident batches in flight (slot stream
 WORKLOAD = "synthetic 1 Mb region, normal 30x / tumor 60x, -Q 15 independent priors (BASELINE configs[1])"
 
 
+REPEATS = 5                     # the K-step timed region of `value` is repeated; the median is reported, the spread beside it
+
+
+def workload_config(ncol, depth_t, depth_n, alg_bytes):
+    """`config` is the workload and nothing else, identical in both arms (the driver compares them)."""
+    return {"workload": WORKLOAD, "columns_per_gpu_per_step": int(ncol), "depth_tumor": depth_t, "depth_normal": depth_n,
+            "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (alg_bytes / 1e6)}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -55,6 +64,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-e2e-reads", action="store_true")
+    ap.add_argument("--no-e2e-bam", action="store_true")
+    ap.add_argument("--no-panel", action="store_true")
+    ap.add_argument("--bam-contigs", type=int, default=4)
+    ap.add_argument("--bam-len", type=int, default=8_000_000)
     ap.add_argument("--backend", default="nccl", help=argparse.SUPPRESS)
     return ap.parse_args()
 
@@ -254,8 +267,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64/f32+int", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "columns_per_step": sample_cols, "depth_tumor": args.depth_t,
-                       "depth_normal": args.depth_n},
+            "config": workload_config(sample_cols, args.depth_t, args.depth_n, synth.algorithmic_bytes(cols)),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -263,6 +275,43 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------
+
+def bam_level(args):
+    """bam-somaticsniper (this repo's CLI, SSN_GPUS = N) on a synthetic 30x/60x BAM pair: columns/s from the program's own
+    statistics (streaming = wall minus set-up).  The pair is generated once per box under /tmp and reused by later runs."""
+    import tempfile
+    from somatic_sniper_b200 import cli_tools as ct
+    if not (os.path.exists(ct.CLI) and os.path.exists(ct.SIMBAM)):
+        return {"unavailable": "bam-somaticsniper / ssn-simbam are not built"}
+    contigs = [("chr%d" % (i + 1), args.bam_len) for i in range(args.bam_contigs)]
+    d = os.path.join(tempfile.gettempdir(), "ssn_bench_bam_%dx%d_%g_%g" % (args.bam_contigs, args.bam_len, args.depth_t, args.depth_n))
+    t0 = time.perf_counter()
+    marker = os.path.join(d, "pair.json")
+    if os.path.exists(marker):
+        with open(marker) as f:
+            pair = json.load(f)
+    else:
+        pair = ct.make_pair_fast(d, contigs, args.depth_t, args.depth_n, seed=1234, level=1)
+        with open(marker, "w") as f:
+            json.dump(pair, f)
+    t_gen = time.perf_counter() - t0
+    out = os.path.join(d, "out.%d" % args.gpus)
+    runs = []
+    for _ in range(3):
+        r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], out, [], env={"SSN_GPUS": args.gpus}, stats=os.path.join(d, "stats.json"))
+        if r["rc"] != 0:
+            return {"unavailable": "bam-somaticsniper failed: %s" % r["stderr"][-300:]}
+        runs.append((r["wall_s"], r["stats"]))
+    wall, st = min(runs, key=lambda x: x[0])
+    bam_bytes = os.path.getsize(pair["tumor"]) + os.path.getsize(pair["normal"])
+    return {"value": st["columns_per_s"], "unit": UNIT, "columns": st["columns"], "read_bases": st["read_bases"], "sites": st["sites"],
+            "wall_s": wall, "setup_s": st["setup_s"], "stream_s": st["wall_s"] - st["setup_s"], "columns_per_s_wall": st["columns"] / wall,
+            "all_walls_s": [w for w, _ in runs], "bam_bytes": bam_bytes, "shards": st["shards"], "threads": st["threads"],
+            "host_cores": os.cpu_count(), "gpus": args.gpus, "pack_wait_s": st["pack_wait_s"], "gpu_wait_s": st["gpu_wait_s"],
+            "generate_s": t_gen,
+            "workload": "%d contigs x %d bp, tumor %gx / normal %gx, 150 bp reads, BGZF level 1 (tools/simbam_fast.c); classic output, "
+                        "default options; file cache warm" % (args.bam_contigs, args.bam_len, args.depth_t, args.depth_n)}
+
 
 def run_b200(args):
     from somatic_sniper_b200 import api, synth
@@ -325,15 +374,18 @@ def run_b200(args):
     for r in resident:
         assert sc.fetch(r).tobytes() == sites_ref.tobytes()
     sc.kernel_time(reset=True)
-    l0 = sc.kernel_launches()
-    dist_barrier(dist)
-    sc.sync()
-    sc.timer_start()
-    for i in range(args.steps):
-        sc.score_resident(resident[i % STREAMS])
-    ms = sc.timer_stop()
-    dist_barrier(dist)
-    launches = sc.kernel_launches() - l0
+    rep_ms = []
+    for _ in range(REPEATS):            # each repeat: exactly K steps between barrier + sync on both sides
+        l0 = sc.kernel_launches()
+        dist_barrier(dist)
+        sc.sync()
+        sc.timer_start()
+        for i in range(args.steps):
+            sc.score_resident(resident[i % STREAMS])
+        rep_ms.append(dist_max(dist, sc.timer_stop()))
+        dist_barrier(dist)
+        launches = sc.kernel_launches() - l0
+    ms = float(np.median(rep_ms))
     ov_pf_ms, ov_score_ms, ov_kn = sc.kernel_time_split(reset=True)
     for r in resident:
         sc.release(r)
@@ -469,19 +521,65 @@ def run_b200(args):
                               "8192-position windows; ssn_batch_submit_reads builds the host packer's column batch on the device "
                               "(tests/test_pileup.py: byte-identical) and scores it" % (h2d / max(1, int(r_nent) * CHUNKS))}
 
+    # ---- panel: BASELINE configs[3] depth (1500x / 1500x), resident, the product path and every-column path ----
+    panel = None
+    if not args.no_panel:
+        pcols = synth.make_columns(16384, depth_t=1500, depth_n=1500, seed=shard_seed(rank) + 500)
+        p_alg = synth.algorithmic_bytes(pcols)
+        sc = api.Scorer(api.default_params(), device=local, n_slots=1, max_columns=pcols["ncol"], max_entries=int(pcols["n_entries"]) + 64)
+        pb = sc.acquire()
+        pb.fill(pcols)
+        sc.upload(pb)
+        res = {}
+        for name, flags in (("product", 0), ("every_column", api.SUBMIT_NO_PREFILTER)):
+            for _ in range(3):
+                sc.score_resident(pb, flags)
+            sc.sync()
+            sites_p = sc.fetch(pb)
+            sc.kernel_time(reset=True)
+            dist_barrier(dist)
+            sc.timer_start()
+            for _ in range(max(3, args.steps // 2)):
+                sc.score_resident(pb, flags)
+            p_ms = sc.timer_stop() / max(3, args.steps // 2)
+            dist_barrier(dist)
+            ppf, psc, pkn = sc.kernel_time_split(reset=True)
+            res[name] = (p_ms, ppf / max(pkn, 1), psc / max(pkn, 1), sites_p)
+        assert res["product"][3].tobytes() == res["every_column"][3].tobytes()
+        sc.close()
+        pm = dist_max(dist, res["product"][0])
+        ptot = dist_sum(dist, float(pcols["ncol"]))
+        panel = {"value": ptot / (pm * 1e-3), "unit": UNIT, "ms_per_step": pm,
+                 "workload": "synthetic targeted panel, 16384 columns at 1500x / 1500x (BASELINE configs[3] depth), %d read-bases, resident" % int(pcols["n_entries"]),
+                 "sites_per_step": int(len(res["product"][3])),
+                 "kernels_ms": {"ssn_prefilter_kernel": res["product"][1], "ssn_score_kernel<false>": res["product"][2]},
+                 "every_column_ms_per_step": res["every_column"][0],
+                 "roofline": {"bound": "hbm", "achieved": p_alg / (pm * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                              "frac": p_alg / (pm * 1e-3) / 1e9 / peak, "traffic": None, "kernel": "ssn_score_kernel<false> (deep columns)",
+                              "algorithmic_bytes_per_launch": p_alg, "ceiling_columns_per_s": peak * 1e9 / (p_alg / pcols["ncol"])},
+                 "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (p_alg / 1e6)}
+
+    # ---- e2e_bam: the whole program on BAM files (region shards -> inflate -> reads -> device pileup -> kernels -> writer) ----
+    e2e_bam = None
+    if not args.no_e2e_bam:
+        dist_barrier(dist)
+        if rank == 0:
+            e2e_bam = bam_level(args)
+        dist_barrier(dist)
+
     sampler.stop()
     if rank != 0:
         return
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64/f32+int", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "columns_per_gpu_per_step": ncol, "read_bases_per_step": nent,
-                       "depth_tumor": args.depth_t, "depth_normal": args.depth_n, "sites_per_step": n_sites,
-                       "prefilter": "exact hom-reference pre-filter on; %d of %d columns go on to the full model" % (survivors, ncol)
-                                    if filtered else "off",
-                       "resident_batches_in_flight": STREAMS,
-                       "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (alg_bytes / 1e6),
-                       "parallelism": "region shards, %d GPU(s), no collective" % args.gpus},
+            "config": workload_config(ncol, args.depth_t, args.depth_n, alg_bytes),
+            "run": {"read_bases_per_step": nent, "sites_per_step": n_sites,
+                    "prefilter": "exact hom-reference pre-filter on; %d of %d columns go on to the full model" % (survivors, ncol)
+                                 if filtered else "off",
+                    "resident_batches_in_flight": STREAMS, "parallelism": "region shards, %d GPU(s), no collective" % args.gpus,
+                    "timed_region_repeats": REPEATS, "ms_per_step_each_repeat": [m / args.steps for m in rep_ms],
+                    "value_spread": (max(rep_ms) - min(rep_ms)) / ms},
             "clocks": sampler.summary(),
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -503,6 +601,10 @@ def run_b200(args):
         line["e2e"] = e2e
     if e2e_reads is not None:
         line["e2e_reads"] = e2e_reads
+    if panel is not None:
+        line["panel"] = panel
+    if e2e_bam is not None:
+        line["e2e_bam"] = e2e_bam
     if args.gpus == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_single(cols, args.cpu_sample)
     print(json.dumps(line), file=_JSON_OUT, flush=True)

@@ -1,4 +1,5 @@
 #include "ssn_bamseek.h"
+#include "ssn_inflate.h"
 
 #include <errno.h>
 #include <fcntl.h>
@@ -58,6 +59,7 @@ static __thread int t_zs_ready = 0;
 
 static int inflate_raw(const uint8_t *src, uint32_t clen, uint8_t *dst, uint32_t ulen)
 {
+    if (ssn_inflate_raw(src, clen, dst, ulen) == 0) return 0;      /* every caller's buffer extends past the block's footer */
     if (!t_zs_ready) {
         memset(&t_zs, 0, sizeof(t_zs));
         if (inflateInit2(&t_zs, -15) != Z_OK) return -1;
@@ -271,7 +273,7 @@ static int chain_ok(const ssn_bam_header *h, const uint8_t *U, size_t L, size_t 
 int ssn_bamfile_probe(const ssn_bamfile *f, uint64_t coff, ssn_bam_point *out)
 {
     const size_t RAWCAP = (size_t)(LOOK_BLOCKS + 3) * 65536 + 4096;
-    uint8_t *raw = (uint8_t*)malloc(RAWCAP), *U = (uint8_t*)malloc((size_t)LOOK_BLOCKS * 65536);
+    uint8_t *raw = (uint8_t*)calloc(1, RAWCAP + SSN_INFLATE_SLACK), *U = (uint8_t*)malloc((size_t)LOOK_BLOCKS * 65536);
     int rc = 0;
     if (!raw || !U) { free(raw); free(U); return -1; }
     while (coff < f->size) {

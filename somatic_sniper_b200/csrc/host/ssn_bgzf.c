@@ -1,4 +1,5 @@
 #include "ssn_bgzf.h"
+#include "ssn_inflate.h"
 
 #include <errno.h>
 #include <fcntl.h>
@@ -54,7 +55,7 @@ ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff)
     z->pool = pool;
     z->max_blocks = (pool && ssn_pool_threads(pool) > 0) ? MAX_BLOCKS : 16;
     z->raw_cap = (pool && ssn_pool_threads(pool) > 0) ? RAW_CAP : ((size_t)2 << 20);
-    z->raw = (uint8_t*)malloc(z->raw_cap);
+    z->raw = (uint8_t*)calloc(1, z->raw_cap + SSN_INFLATE_SLACK);
     z->out_cap = (size_t)z->max_blocks * 65536;
     z->out = (uint8_t*)malloc(z->out_cap);
     if (!z->raw || !z->out) { ssn_bgzf_close(z); return 0; }
@@ -118,6 +119,10 @@ static void inflate_one(void *arg, int i)
     ssn_bgzf *z = ((inflate_arg*)arg)->z;
     blk *b = &z->blocks[i];
     int st;
+    static int use_zlib = -1;
+    if (use_zlib < 0) use_zlib = getenv("SSN_ZLIB_INFLATE") != 0;          /* measurement / fall-back knob */
+    if (!use_zlib && ssn_inflate_raw(b->cdata, b->clen, z->out + b->uoff, b->ulen) == 0) return;
+    /* zlib reads every stream the reference reads; the fast decoder gave up on this one (or is switched off) */
     if (!t_zs_ready) {
         memset(&t_zs, 0, sizeof(t_zs));
         if (inflateInit2(&t_zs, -15) != Z_OK) { b->bad = 1; return; }

@@ -446,7 +446,8 @@ ssn_status ssn_packer_next(ssn_packer *pk, const ssn_batch_view *view, const ssn
     t1 = now_s(); pk->st.t_wait += t1 - t0;
     if (pk->n_pending == 0) return SSN_OK;
 
-    /* 2. count the new windows */
+    /* 2. count the new windows (a window ssn_packer_next_reads looked at and left behind was never counted) */
+    while (fresh0 > 0 && !pk->pending[fresh0 - 1]->cnt[0]) --fresh0;
     if (pk->n_pending > fresh0) ssn_pool_for(pk->pool, pk->n_pending - fresh0, count_task, pk->pending + fresh0);
     t0 = now_s(); pk->st.t_count += t0 - t1;
 

@@ -121,8 +121,15 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
         for (t = 0; t < h->n_targets; ++t) genome += h->target_len[t];
         if (o.stride_windows) stride = (uint64_t)o.stride_windows << SSN_WINDOW_SHIFT;
         else {
+            /* An interval should (a) leave every reader pair several intervals to take and (b) hold about 48 MB of
+             * records in its larger file, so that its windows fit the reader's queue and read-ahead never stalls on
+             * back-pressure (records inflate to roughly 3.5 x their share of the file). */
+            const uint64_t big = ssn_bamfile_size(set->bf[0]) > ssn_bamfile_size(set->bf[1]) ? ssn_bamfile_size(set->bf[0]) : ssn_bamfile_size(set->bf[1]);
+            const double per_pos = genome ? 3.5 * (double)big / (double)genome : 0.0;
+            uint64_t by_bytes = per_pos > 0.0 ? (uint64_t)(((double)((uint64_t)48 << 20)) / per_pos) : genome;
             stride = genome / (4u * (uint64_t)o.max_reading + 1u);
-            if (stride < ((uint64_t)32 << SSN_WINDOW_SHIFT)) stride = (uint64_t)32 << SSN_WINDOW_SHIFT;
+            if (stride > by_bytes) stride = by_bytes;
+            if (stride < ((uint64_t)8 << SSN_WINDOW_SHIFT)) stride = (uint64_t)8 << SSN_WINDOW_SHIFT;
             if (stride > ((uint64_t)1024 << SSN_WINDOW_SHIFT)) stride = (uint64_t)1024 << SSN_WINDOW_SHIFT;
             stride &= ~(uint64_t)(SSN_WINDOW - 1u);
         }
@@ -152,7 +159,7 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
                 s->rg.hi_tid = i + 1 < n ? cuts[i + 1].lo_tid : INT32_MAX;
                 s->rg.hi_pos = i + 1 < n ? cuts[i + 1].lo_pos : 0;
                 s->rg.lookback = o.lookback_windows << SSN_WINDOW_SHIFT;
-                s->rg.queue_max_bytes = (size_t)96 << 20;
+                s->rg.queue_max_bytes = (size_t)192 << 20;
             }
             set->max_reading = o.max_reading; set->max_open = o.max_open;
             /* the readers inflate by themselves (one core each); the pool serves the packers' count / fill / copy tasks */

@@ -252,3 +252,49 @@ def test_many_small_targets_share_the_sequence_cache(host, sim, tmp_path):
     n = sum(host.pack_read_windows(rb)["ncol"] for rb in pk.read_batches(max_windows=16))
     pk.close()
     assert n == len(got)
+
+
+def test_mixed_routes_windows_too_deep_for_a_read_batch(host, big_pair):
+    """The CLI's fall-back: ssn_packer_next_reads refuses a window that alone exceeds the read batch (SSN_ERR_OVERFLOW,
+    nothing consumed), ssn_packer_next packs exactly that window into columns (one-window mode), then the reads route
+    resumes.  With a capacity between the shallow and the deep windows of the pair both routes alternate; the union of the
+    columns equals the column route's."""
+    from somatic_sniper_b200 import api
+    p = big_pair
+    lib = host.load_library()
+    pk = host.Packer(p["tumor"], p["normal"], p["fasta"], 0, threads=2)
+    want = _packed_columns(list(pk))
+    pk.close()
+    cap_entries = 8192 * 38 * 150 // 150          # windows at full depth (24x + 14x) exceed it; ragged ones at contig ends fit
+    pk = host.Packer(p["tumor"], p["normal"], p["fasta"], 0, threads=2, max_columns=1 << 14, max_entries=cap_entries)
+    got, n_reads_batches, n_col_batches = [], 0, 0
+    it_reads = pk.read_batches(max_rec_bytes=1 << 24, max_reads=1 << 18, max_windows=2)
+    cols_mode = False
+    while True:
+        if not cols_mode:
+            try:
+                rb = next(it_reads)
+            except StopIteration:
+                break
+            except RuntimeError as e:
+                assert "capacity" in str(e)
+                cols_mode = True
+                lib.ssn_packer_one_window(pk.h, 1)
+                it_reads = pk.read_batches(max_rec_bytes=1 << 24, max_reads=1 << 18, max_windows=2)
+                continue
+            b = host.pack_read_windows(rb)
+            # positions come back as window << 13 | offset: rebuild tid / pos / ref_char for the comparison
+            w, o = b["pos"] >> 13, b["pos"] & 8191
+            b["tid"] = rb["win"]["tid"][w]; b["pos"] = rb["win"]["lo"][w] + o; b["ref_char"] = rb["ref_char"][w, o]
+            got += _packed_columns([b]); n_reads_batches += 1
+            continue
+        b = next(iter(pk), None)
+        if b is None:
+            break
+        got += _packed_columns([b]); n_col_batches += 1
+        if not lib.ssn_packer_partial(pk.h):
+            cols_mode = False
+            lib.ssn_packer_one_window(pk.h, 0)
+    pk.close()
+    assert n_reads_batches >= 2 and n_col_batches >= 10
+    assert got == want
