@@ -33,6 +33,7 @@ struct ssn_bamreader {
     /* open windows of the current target, ascending widx */
     ssn_window **open;
     int n_open, cap_open;
+    size_t hint_bytes; uint32_t hint_reads;      /* capacity of the last finished window (+12 %) */
     /* region shard (ssn_bamreader_open_range): the reader owns the windows in [lo, hi) */
     const ssn_bamfile *bf;          /* not owned; NULL = the whole file from its first record */
     int hdr_borrowed;
@@ -123,6 +124,7 @@ void ssn_window_free(ssn_window *w)
 {
     if (!w) return;
     free(w->buf);
+    free(w->rec_word);
     free(w);
 }
 
@@ -131,6 +133,7 @@ static void queue_push(ssn_bamreader *r, ssn_window *w)
     pthread_mutex_lock(&r->mu);
     while (!r->stop && r->q_bytes > r->queue_max && r->q_head) pthread_cond_wait(&r->not_full, &r->mu);
     w->next = 0;
+    r->hint_bytes = w->len + (w->len >> 3) + 4096; r->hint_reads = w->n_reads + (w->n_reads >> 3) + 64;
     if (r->q_tail) r->q_tail->next = w; else r->q_head = w;
     r->q_tail = w;
     r->q_bytes += w->len;
@@ -165,6 +168,14 @@ static ssn_window *open_window(ssn_bamreader *r, int32_t tid, uint32_t widx)
     w = (ssn_window*)calloc(1, sizeof(*w));
     if (!w) return 0;
     w->tid = tid; w->widx = widx;
+    if (r->hint_bytes) {
+        /* neighbouring windows are about as deep: one allocation instead of a doubling chain (every large realloc is a
+         * system call, and with many readers those contend) */
+        w->buf = (uint8_t*)malloc(r->hint_bytes);
+        w->rec_word = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)r->hint_reads);
+        if (w->buf && w->rec_word) { w->cap = r->hint_bytes; w->cap_reads = r->hint_reads; }
+        else { free(w->buf); free(w->rec_word); w->buf = 0; w->rec_word = 0; }
+    }
     /* keep ascending widx order (reads arrive sorted by start, so new windows normally go last) */
     i = r->n_open++;
     while (i > 0 && r->open[i - 1]->widx > widx) { r->open[i] = r->open[i - 1]; --i; }
@@ -176,6 +187,13 @@ static int window_append(ssn_window *w, const ssn_read *h, const uint8_t *cigar,
 {
     const size_t nc = (size_t)h->n_cigar * 4, ns = ((size_t)h->l_qseq + 1) >> 1, nq = h->l_qseq;
     uint8_t *d;
+    if (w->n_reads == w->cap_reads) {
+        const uint32_t cap = w->cap_reads ? 2 * w->cap_reads : 1024;
+        uint32_t *no = (uint32_t*)realloc(w->rec_word, sizeof(uint32_t) * (size_t)cap);
+        if (!no) return -1;
+        w->rec_word = no; w->cap_reads = cap;
+    }
+    w->rec_word[w->n_reads] = (uint32_t)(w->len >> 2);
     if (w->len + h->bytes > w->cap) {
         size_t cap = w->cap ? w->cap * 2 : ((size_t)1 << 16);
         uint8_t *nb;

@@ -36,6 +36,8 @@ typedef struct ssn_window {
     uint64_t n_bases;          /* sum of max(l_qseq, M-run length): upper bound of the entries the window can produce */
     uint8_t *buf;
     size_t len, cap;
+    uint32_t *rec_word;        /* [n_reads] offset / 4 of every record inside buf (the read batch's index, ready to be rebased) */
+    uint32_t cap_reads;
     struct ssn_window *next;
 } ssn_window;
 

@@ -25,6 +25,7 @@
  * There is no CPU scoring path: without a usable sm_100 device the program fails.
  */
 #include <ctype.h>
+#include <malloc.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -466,6 +467,10 @@ int main(int argc, char *argv[])
     int32_t n_shards_first;
     double t_start = now_s(), t_setup;
 
+    /* window buffers of a megabyte or so are allocated and freed by the dozen per second on many threads: keep them on the
+     * malloc arenas instead of one mmap/munmap system call each (those serialise on the process's address-space lock) */
+    mallopt(M_MMAP_THRESHOLD, 32 << 20);
+    mallopt(M_TRIM_THRESHOLD, 1 << 30);
     memset(&R, 0, sizeof(R));
     memset(&st, 0, sizeof(st));
     ssn_params_default(&R.prm);

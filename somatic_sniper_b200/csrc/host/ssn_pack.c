@@ -534,13 +534,9 @@ static void reads_copy_task(void *arg, int idx)
         }
     } else {
         const ssn_window *w = t->p->w[t->s];
-        size_t o = 0;
-        uint32_t k = 0;
+        uint32_t k;
         memcpy(t->dst, w->buf, w->len);
-        while (o < w->len) {
-            t->off[k++] = t->off_base + (uint32_t)(o >> 2);
-            o += ((const ssn_read*)(w->buf + o))->bytes;
-        }
+        for (k = 0; k < w->n_reads; ++k) t->off[k] = t->off_base + w->rec_word[k];
     }
 }
 

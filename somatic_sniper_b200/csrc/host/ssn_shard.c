@@ -41,6 +41,8 @@ struct ssn_shardset {
     shard *sh;
     int32_t n, next_open, next_claim, n_done;
     int reading, max_reading, max_open;
+    int started;                   /* a caller has asked for a shard: until then only two intervals are read ahead, so that the
+                                    * readers do not crowd out the caller's own set-up (GPU contexts) */
     int long_span, failed;
     pthread_mutex_t mu;
     pthread_cond_t cv;
@@ -60,7 +62,8 @@ static void reader_finished(void *arg)
 /* mu held on entry and exit; opens shards while the read-ahead limits allow */
 static void open_more(ssn_shardset *set)
 {
-    while (set->next_open < set->n && set->reading < set->max_reading && set->next_open - set->n_done < set->max_open) {
+    while (set->next_open < set->n && set->reading < (set->started ? set->max_reading : (set->max_reading < 2 ? set->max_reading : 2)) &&
+           set->next_open - set->n_done < set->max_open) {
         shard *s = &set->sh[set->next_open++];
         ssn_packer *pk;
         char err[256] = "";
@@ -163,7 +166,7 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
             }
             set->max_reading = o.max_reading; set->max_open = o.max_open;
             /* the readers inflate by themselves (one core each); the pool serves the packers' count / fill / copy tasks */
-            set->pool = ssn_pool_create(o.n_threads >= 8 ? o.n_threads / 4 : (o.n_threads >= 2 ? 2 : 0));
+            set->pool = ssn_pool_create(o.n_threads >= 4 ? o.n_threads / 2 : (o.n_threads >= 2 ? 2 : 0));
             set->rc = ssn_refcache_create(fasta, h);
         }
         free(cuts);
@@ -235,6 +238,7 @@ ssn_status ssn_shardset_next(ssn_shardset *set, int32_t *index, ssn_packer **pac
     *index = -1; *packer = 0;
     pthread_mutex_lock(&set->mu);
     if (set->next_claim >= set->n) { pthread_mutex_unlock(&set->mu); return SSN_OK; }
+    set->started = 1;
     s = &set->sh[set->next_claim];
     if (set->serial) { s->pk = set->serial; s->state = SH_OPEN; }
     while (s->state < SH_OPEN && !set->failed) {

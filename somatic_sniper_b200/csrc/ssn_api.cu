@@ -541,7 +541,8 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
          * One slot used back to back: nothing overlaps, so spread 4-column tiles over more SMs (latency). */
         const bool alternating = ctx->last_slot >= 0 && ctx->last_slot != b->index;
         list_width = alternating ? 0u : 4u;
-        const uint32_t cols_per_warp = alternating ? (uint32_t)kListWidth : 4u;
+        uint32_t cols_per_warp = alternating ? (uint32_t)kListWidth : 4u;
+        { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; if (w == 1 || w == 2 || w == 4 || w == 8 || w == 16) cols_per_warp = (uint32_t)w; }
         const uint32_t want = (uint32_t)(est / (cols_per_warp * kWarpsPerCta * tiles_per_warp)) + 1u;
         grid = std::min(grid, std::max(want, 8u));
     }
@@ -565,9 +566,11 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.scratch_words_per_warp = (uint32_t)(((size_t)tile_words + 63) / 64 * 64);
     B.smem_words_per_warp = words;
     B.dev_ncol = b->spec ? b->d_summary : nullptr; B.guard = b->spec ? b->d_summary : nullptr; B.guard_col_words = b->spec_col_words;
+    { static const int nh = getenv("SSN_NO_HIST") != nullptr; B.no_hist = nh ? 1u : 0u; }
     B.collist = listed ? b->d_survivors : nullptr;
     B.list_count = b->d_count + 2;
-    { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 4 || w == 8 || w == 16) ? (uint32_t)w : list_width; }
+    { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 1 || w == 2 || w == 4 || w == 8 || w == 16) ? (uint32_t)w : list_width; }
+    { static const int lg = getenv("SSN_LIST_GENERIC") ? atoi(getenv("SSN_LIST_GENERIC")) : 0; B.list_generic = (uint32_t)lg; }
     KernelTimer &kt = ctx->timers[ctx->timer_next];
     ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
     ssn_status st = timer_collect(ctx, kt);

@@ -118,6 +118,8 @@ struct DevBatch {
     const uint32_t *dev_ncol;
     const uint32_t *guard;          /* pileup summary: [2] error bits, [4] key-store words of the deepest column */
     uint32_t guard_col_words;
+    uint32_t list_generic;          /* 1: gathered tiles take the warp-cooperative sorting path (experiment: short code, one column per warp) */
+    uint32_t no_hist;               /* 1: deep tiles take the sorting path (measurement / cross-check knob SSN_NO_HIST) */
 };
 constexpr uint32_t kGuardStop = 2u | 4u | 16u;   /* pileup::kErrStop */
 
@@ -839,6 +841,107 @@ __device__ __noinline__ void generic_tile(const DevModel &M, const DevBatch &B, 
     chain_flush(ch, slots, lane);
 }
 
+/* -------------------------------------------------------------------------------------------- */
+/* deep columns (panel depths): a histogram instead of a sort              */
+/*
+ * What the sorted order is used for: inside one (sample, base) chain the reference touches the read-bases by falling
+ * q, then valid, then strand (sniper_maqcns.c:157-176), and two read-bases that agree in (q, valid, strand) contribute
+ * the same amount.  With every base quality in [1,63] (checked here; otherwise the tile takes the sorting path) q =
+ * min(baseQ, mapQ) <= 63, every read-base contributes and sub == 1, so a column's keys fall into
+ *     bin = sample<<10 | b4<<8 | q<<2 | valid<<1 | strand            (2048 bins)
+ * and walking the non-empty bins from the top down, each as many times as it holds read-bases, IS the reference's chain.
+ * FRONT, warp per column: the bins are counted in shared memory (over the key store; lanes holding the same bin are
+ * found with MATCH.ANY and their leader adds the group's size, so a bin hit by the whole warp costs one atomic), then
+ * the non-empty bins are compacted, top down, into a run list (bin<<17 | count) in the warp's global scratch.
+ * BACK, lane per column: one flat loop of max(n) steps; a lane fetches its next run when the current one is used up
+ * and otherwise does exactly chain_step's arithmetic.  No key is loaded per step and no sorted run is merged.
+ * Returns false (nothing written that matters) when the tile has to take the sorting path instead.
+ */
+constexpr int kHistBins = 2048;
+
+__device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, const CtaTables &T, uint32_t *slots, uint32_t *hist,
+                                       uint32_t *runs, uint32_t runs_cap, int lane, uint32_t o0, uint32_t nT, uint32_t n, uint32_t ref16,
+                                       uint32_t &my_rms_t, uint32_t &my_rms_n)
+{
+    uint32_t my_start = 0, total = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+    for (int j = 0; j < 32; ++j) {
+        const uint32_t nj = __shfl_sync(kFull, n, j);
+        if (nj == 0) continue;
+        const uint32_t e0 = __shfl_sync(kFull, o0, j), nTj = __shfl_sync(kFull, nT, j), refj = __shfl_sync(kFull, ref16, j);
+        const uint16_t *cls_t = T.cls + (16 + refj) * 32, *cls_n = T.cls + refj * 32;
+        for (int i = lane * 4; i < kHistBins; i += 128) *reinterpret_cast<uint4*>(hist + i) = make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();
+        uint32_t rt = 0, rn = 0, bad = 0;
+        for (uint32_t i0 = 0; i0 < nj; i0 += 32) {
+            const uint32_t i = i0 + (uint32_t)lane;
+            uint32_t bin = 0xffffffffu;
+            if (i < nj) {
+                const uint32_t bs = B.bs[e0 + i], bq = B.bq[e0 + i], mq = B.mq[e0 + i];
+                const bool is_t = i < nTj;
+                const uint32_t cls = is_t ? cls_t[bs & 31u] : cls_n[bs & 31u];      /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
+                bad |= (bq - 1u) > 62u ? 1u : 0u;
+                bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq, mq) & 63u) << 2 | ((cls >> 3) & 3u);
+                const uint32_t m = min(mq & 0x7fu, (uint32_t)M.cap_mapq);           /* sniper_maqcns.c:173-174 */
+                if (is_t) rt += m * m; else rn += m * m;
+            }
+            const uint32_t peers = __match_any_sync(kFull, bin);
+            if (bin != 0xffffffffu && (peers & lt) == 0u) atomicAdd(hist + bin, (uint32_t)__popc(peers));
+        }
+        if (__any_sync(kFull, bad != 0u)) return false;
+        rt = __reduce_add_sync(kFull, rt);
+        rn = __reduce_add_sync(kFull, rn);
+        __syncwarp();
+        uint32_t cnt = 0;
+        for (int it = 0; it < kHistBins / 32; ++it) {
+            const uint32_t bin = (uint32_t)(kHistBins - 1 - (it * 32 + lane));
+            const uint32_t c = hist[bin];
+            const uint32_t mask = __ballot_sync(kFull, c != 0u);
+            if (total + cnt + (uint32_t)__popc(mask) > runs_cap) return false;      /* more runs than the scratch holds */
+            if (c) runs[total + cnt + (uint32_t)__popc(mask & lt)] = bin << 17 | c;  /* c <= 65536 */
+            cnt += (uint32_t)__popc(mask);
+        }
+        if (lane == j) { my_start = total; my_rms_t = rt; my_rms_n = rn; }
+        total += cnt;
+        __syncwarp();
+    }
+    __syncwarp();
+    /* BACK: lane-per-column walk over the runs */
+    Chain ch;
+    chain_init(ch);
+    const uint32_t *mine = runs + my_start;
+    const uint32_t steps = __reduce_max_sync(kFull, n);
+    uint32_t left = 0, k = 0, rev = 0;
+    double qd = 0.0;
+    for (uint32_t it = 0; it < steps; ++it) {
+        if (it < n) {
+            if (left == 0u) {
+                const uint32_t r = mine[k++];
+                const uint32_t bin = r >> 17;
+                left = r & 0x1ffffu;
+                const int sb = (int)(bin >> 8);
+                if (sb != ch.sb) {
+                    chain_flush(ch, slots, lane);
+                    ch.sb = sb; ch.e = 0.0; ch.f = 0.0; ch.c = 0; ch.w0 = 0; ch.w1 = 0;
+                }
+                const uint32_t q = max((bin >> 2) & 63u, 4u);                       /* :165 with baseQ in [1,63] */
+                qd = __hiloint2double(0x43300000, (int)q) - 4503599627370496.0;     /* exact int -> double */
+                rev = bin & 1u;
+            }
+            const uint32_t w = rev ? ch.w1 : ch.w0;
+            const double fkw = T.fk2[w].x;
+            ch.e = round_to_f32(__dadd_rn(ch.e, __dmul_rn(fkw, qd)));               /* esum += fk[w]*q  (:168) */
+            ch.f = round_to_f32(__dadd_rn(ch.f, fkw));                              /* fsum += fk[w]    (:169) */
+            const uint32_t wn = min(w + 1u, 255u);                                  /* :170 */
+            if (rev) ch.w1 = wn; else ch.w0 = wn;
+            ++ch.c;
+            --left;
+        }
+    }
+    chain_flush(ch, slots, lane);
+    return true;
+}
+
 template <int NW>
 __device__ __noinline__ void fast_tile(uint32_t raw_s, uint32_t r0, uint32_t nT, uint32_t n, int C, uint32_t lutK, uint32_t tail_s,
                                        int cap_mapq, uint32_t *keys_s, uint32_t *slots, uint32_t fk2_s, int lane,
@@ -924,7 +1027,8 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
         /* the tile's read-bases are contiguous: [off of its first column, end of its last live column) */
         const uint32_t a0 = __shfl_sync(kFull, o0, 0) & ~15u;
         const uint32_t bytes = (__reduce_max_sync(kFull, o2) - a0 + 15u) & ~15u;
-        const bool fast = need <= 2u * kFastWords && (listed || bytes <= (uint32_t)kRawBytes) && B.smem_words_per_warp >= kFastWords * 32u;
+        const bool fast = need <= 2u * kFastWords && (listed || bytes <= (uint32_t)kRawBytes) && B.smem_words_per_warp >= kFastWords * 32u &&
+                          !(listed && B.list_generic);
 
         uint32_t my_rms_t = 0, my_rms_n = 0;
         bool done = false;
@@ -973,7 +1077,22 @@ ssn_score_kernel(const DevModel M, const DevBatch B)
             for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
             __syncwarp();
             SSN_PL_BAR();
-            if (need != 0u) generic_tile(M, B, T, slots, keys_s, keys_g, lane, o0, nT, n, ref16, my_rms_t, my_rms_n);
+            if (need != 0u) {
+                /* deep tiles count bins instead of sorting, when the launch has a global scratch for the run lists and
+                 * every base quality is in [1,63]; anything else sorts */
+                bool counted = false;
+                if (keys_g && need > 2u * kFastWords && B.smem_words_per_warp >= (uint32_t)kHistBins && !B.no_hist)
+                    counted = hist_tile(M, B, T, slots, keys_s, keys_g, B.scratch_words_per_warp, lane, o0, nT, n, ref16, my_rms_t, my_rms_n);
+                if (!counted) {
+                    if (keys_g && need > 2u * kFastWords) {         /* the attempt may have left partial chains behind */
+                        __syncwarp();
+                        for (int i = 0; i < 24; ++i) slots[i * 32 + lane] = 0;
+                        my_rms_t = 0; my_rms_n = 0;
+                        __syncwarp();
+                    }
+                    generic_tile(M, B, T, slots, keys_s, keys_g, lane, o0, nT, n, ref16, my_rms_t, my_rms_n);
+                }
+            }
             SSN_PL_BAR();
         }
         SSN_PL_BAR();
