@@ -524,7 +524,12 @@ def run_b200(args):
     # ---- panel: BASELINE configs[3] depth (1500x / 1500x), resident, the product path and every-column path ----
     panel = None
     if not args.no_panel:
-        pcols = synth.make_columns(16384, depth_t=1500, depth_n=1500, seed=shard_seed(rank) + 500)
+        # 16384 distinct columns (148 MB), laid out four times over: 65536 columns fill every resident warp of the grid
+        unit = synth.make_columns(16384, depth_t=1500, depth_n=1500, seed=shard_seed(rank) + 500)
+        reps, ue = 4, int(unit["n_entries"])
+        pcols = dict(off=np.concatenate([unit["off"][:-1].astype(np.int64) + r * ue for r in range(reps)] + [np.array([reps * ue], np.int64)]).astype(np.uint32),
+                     bs=np.tile(unit["bs"], reps), bq=np.tile(unit["bq"], reps), mq=np.tile(unit["mq"], reps),
+                     ref_char=np.tile(unit["ref_char"], reps), ncol=reps * unit["ncol"], n_entries=reps * ue)
         p_alg = synth.algorithmic_bytes(pcols)
         sc = api.Scorer(api.default_params(), device=local, n_slots=1, max_columns=pcols["ncol"], max_entries=int(pcols["n_entries"]) + 64)
         pb = sc.acquire()
@@ -550,7 +555,7 @@ def run_b200(args):
         pm = dist_max(dist, res["product"][0])
         ptot = dist_sum(dist, float(pcols["ncol"]))
         panel = {"value": ptot / (pm * 1e-3), "unit": UNIT, "ms_per_step": pm,
-                 "workload": "synthetic targeted panel, 16384 columns at 1500x / 1500x (BASELINE configs[3] depth), %d read-bases, resident" % int(pcols["n_entries"]),
+                 "workload": "synthetic targeted panel, 65536 columns (16384 distinct, four times over) at 1500x / 1500x (BASELINE configs[3] depth), %d read-bases, resident" % int(pcols["n_entries"]),
                  "sites_per_step": int(len(res["product"][3])),
                  "kernels_ms": {"ssn_prefilter_kernel": res["product"][1], "ssn_score_kernel<false>": res["product"][2]},
                  "every_column_ms_per_step": res["every_column"][0],

@@ -2,6 +2,9 @@
 
 #include <pthread.h>
 #include <stdio.h>
+#include <sys/resource.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -269,6 +272,12 @@ static void *reader_main(void *v)
     uint32_t prev_beg = 0;          /* cursor position at the next fetch (0 before the first passing read) */
     const int ranged = r->bf != 0;
     if (ranged) {
+        /* Region shards run more reader threads than there are cores.  They are the bulk of the work but not the critical
+         * path: the one thread per GPU that moves finished windows to the device (and its copy workers) must never wait
+         * for a time slice behind them, so the readers give way (per-thread nice value, Linux). */
+#ifdef SYS_gettid
+        setpriority(PRIO_PROCESS, (id_t)syscall(SYS_gettid), 10);
+#endif
         const int st = range_start(r, &max_tid, &prev_beg);
         if (st < 0) r->failed = 1;
         if (st <= 0) { reader_finish(r); return 0; }

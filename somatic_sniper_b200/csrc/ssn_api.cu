@@ -67,6 +67,8 @@ struct ssn_batch {
     uint32_t *d_dump; size_t d_dump_words;
     uint32_t max_tile_words;
     uint32_t max_col_words;   /* key-store words of the deepest column (list-mode tiles gather arbitrary columns) */
+    bool listed;              /* the last launch ran the pre-filter and scored its survivor list */
+    uint32_t n_deep;          /* columns with more than 255 read-bases in a sample: the pre-filter cannot settle those */
     uint32_t *d_survivors;    /* column indices the pre-filter hands to the full model */
     uint32_t *d_scratch; size_t scratch_words;   /* global key store of this slot's launches (tiles deeper than shared
                                                    * memory); per slot, because slots score concurrently on their own streams */
@@ -447,7 +449,7 @@ static ssn_status scan_offsets(ssn_batch *b)
 {
     const uint32_t *off = b->h_off;
     const uint32_t ncol = b->ncol;
-    b->max_col_words = 0;
+    b->max_col_words = 0; b->n_deep = 0;
     if (ncol == 0) { b->max_tile_words = 0; return SSN_OK; }
     if (off[2 * (size_t)ncol] != b->nent) { ssn_set_error("batch: off[2*ncol]=%u but n_entries=%llu", off[2 * (size_t)ncol], (unsigned long long)b->nent); return SSN_ERR_ARG; }
     uint32_t max_tile = 0;
@@ -458,6 +460,7 @@ static ssn_status scan_offsets(ssn_batch *b)
             const uint32_t a = off[2 * (size_t)c], m = off[2 * (size_t)c + 1], z = off[2 * (size_t)c + 2];
             if (m < a || z < m) { ssn_set_error("batch: offsets of column %u decrease", c); return SSN_ERR_ARG; }
             const uint32_t n = z - a;
+            if (m - a > 255u || z - m > 255u) b->n_deep += 1;
             if (n > (uint32_t)kRunLen * kMaxRuns) { ssn_set_error("batch: column %u holds %u read-bases; this build supports %d", c, n, kRunLen * kMaxRuns); return SSN_ERR_ARG; }
             const uint32_t cw = (n >> 10) * (kRunLen / 2) + (((n & (kRunLen - 1)) + 1) >> 1);
             words += cw;
@@ -500,9 +503,12 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
 {
     const bool dump = (flags & SSN_SUBMIT_COLUMN_DUMP) != 0;
     /* the pre-filter runs unless switched off; with a column dump it only records its decisions (audit) */
-    const bool filter = ctx->pf_on && !(flags & SSN_SUBMIT_NO_PREFILTER);
+    /* a batch of panel depth: the filter would hand (nearly) every column on, and contiguous tiles score faster than
+     * gathered ones */
+    const bool mostly_deep = !b->from_reads && b->ncol && 2ull * b->n_deep > b->ncol;
+    const bool filter = ctx->pf_on && !(flags & SSN_SUBMIT_NO_PREFILTER) && (!mostly_deep || (flags & SSN_SUBMIT_COLUMN_DUMP));
     const bool listed = filter && !dump;
-    b->flags = flags;
+    b->flags = flags; b->listed = listed;
     CU(cudaMemsetAsync(b->d_count, 0, kCountWords * sizeof(uint32_t), b->stream));
     if (b->ncol == 0) return SSN_OK;
     if (dump) {
@@ -638,8 +644,7 @@ static ssn_status collect(ssn_ctx *ctx, ssn_batch *b)
         std::sort(b->h_sites, b->h_sites + n, [](const ssn_site &x, const ssn_site &y) { return x.column < y.column; });
     }
     b->n_sites = n;
-    if ((b->flags & (SSN_SUBMIT_COLUMN_DUMP | SSN_SUBMIT_NO_PREFILTER)) == 0 && ctx->pf_on && b->ncol)
-        ctx->survivor_frac = (double)b->h_count[2] / (double)b->ncol;
+    if (b->listed && b->ncol) ctx->survivor_frac = (double)b->h_count[2] / (double)b->ncol;
     return SSN_OK;
 }
 

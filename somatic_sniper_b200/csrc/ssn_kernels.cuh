@@ -873,20 +873,31 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
         for (int i = lane * 4; i < kHistBins; i += 128) *reinterpret_cast<uint4*>(hist + i) = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
         uint32_t rt = 0, rn = 0, bad = 0;
-        for (uint32_t i0 = 0; i0 < nj; i0 += 32) {
-            const uint32_t i = i0 + (uint32_t)lane;
-            uint32_t bin = 0xffffffffu;
-            if (i < nj) {
-                const uint32_t bs = B.bs[e0 + i], bq = B.bq[e0 + i], mq = B.mq[e0 + i];
-                const bool is_t = i < nTj;
-                const uint32_t cls = is_t ? cls_t[bs & 31u] : cls_n[bs & 31u];      /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
-                bad |= (bq - 1u) > 62u ? 1u : 0u;
-                bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq, mq) & 63u) << 2 | ((cls >> 3) & 3u);
-                const uint32_t m = min(mq & 0x7fu, (uint32_t)M.cap_mapq);           /* sniper_maqcns.c:173-174 */
-                if (is_t) rt += m * m; else rn += m * m;
+        /* four read-bases per lane and iteration (lane l takes i0 + 32 k + l): twelve independent byte loads in flight
+         * before the first MATCH, which is what hides the memory latency at 16 warps per SM */
+        for (uint32_t i0 = 0; i0 < nj; i0 += 128) {
+            uint32_t bs[4], bq[4], mq[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t i = i0 + 32u * (uint32_t)k + (uint32_t)lane;
+                bs[k] = bq[k] = mq[k] = 0u;
+                if (i < nj) { bs[k] = B.bs[e0 + i]; bq[k] = B.bq[e0 + i]; mq[k] = B.mq[e0 + i]; }
             }
-            const uint32_t peers = __match_any_sync(kFull, bin);
-            if (bin != 0xffffffffu && (peers & lt) == 0u) atomicAdd(hist + bin, (uint32_t)__popc(peers));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t i = i0 + 32u * (uint32_t)k + (uint32_t)lane;
+                uint32_t bin = 0xffffffffu;
+                if (i < nj) {
+                    const bool is_t = i < nTj;
+                    const uint32_t cls = is_t ? cls_t[bs[k] & 31u] : cls_n[bs[k] & 31u];  /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
+                    bad |= (bq[k] - 1u) > 62u ? 1u : 0u;
+                    bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq[k], mq[k]) & 63u) << 2 | ((cls >> 3) & 3u);
+                    const uint32_t m = min(mq[k] & 0x7fu, (uint32_t)M.cap_mapq);          /* sniper_maqcns.c:173-174 */
+                    if (is_t) rt += m * m; else rn += m * m;
+                }
+                const uint32_t peers = __match_any_sync(kFull, bin);
+                if (bin != 0xffffffffu && (peers & lt) == 0u) atomicAdd(hist + bin, (uint32_t)__popc(peers));
+            }
         }
         if (__any_sync(kFull, bad != 0u)) return false;
         rt = __reduce_add_sync(kFull, rt);

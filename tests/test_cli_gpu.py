@@ -259,3 +259,26 @@ def test_config4_targeted_panel_depth(ct, tmp_path):
         assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
         assert ct.comparable(mine) == ct.comparable(ref)
     assert r1["stats"]["read_bases"] > 8 * 4000 * 2900
+
+
+def test_region_shards_on_every_physical_gpu(ct, tmp_path):
+    """With more than one GPU in the box: one feeder thread and one scoring context per physical device, shards taken in
+    genome order, output merged in order — byte-identical to the run on one GPU and to the reference binary."""
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("one GPU in this box (the multi-context path runs as SSN_DEVICES=0,0 above)")
+    pair = ct.make_pair_fast(str(tmp_path), [("chr1", 1500000), ("chr2", 700000), ("chr3", 300000)], 60, 30, seed=21)
+    outs = {}
+    for g in sorted({1, 2, n}):
+        o = str(tmp_path / ("out%d" % g))
+        r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], o, ["-F", "vcf"], env={"SSN_GPUS": g, "SSN_SHARD_WINDOWS": 8},
+                       stats=str(tmp_path / "s.json"))
+        assert r["rc"] == 0, r["stderr"]
+        assert r["stats"]["gpus"] == g and r["stats"]["shards"] >= 30
+        outs[g] = ct.comparable(o)
+    assert all(v == outs[1] for v in outs.values())
+    if ct.reference_available():
+        ref = str(tmp_path / "ref")
+        ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, ["-F", "vcf"])
+        assert ct.comparable(ref) == outs[1]

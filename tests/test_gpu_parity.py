@@ -291,7 +291,8 @@ def test_prefilter_audit_and_identical_sites(mods, name, kw):
         if joint == 0:
             want = prefilter_np.decide(cols)
             wanted = (np.diff(cols["off"].astype(np.int64))[0::2] > 0) & (np.diff(cols["off"].astype(np.int64))[1::2] > 0) & (ref16 != 15)
-            assert survivors == int((wanted & ~dropped).sum())
+            # a batch of panel depth skips the filter altogether (it could not settle a column): nothing is "handed on"
+            assert survivors == (0 if name == "deep" else int((wanted & ~dropped).sum()))
             # float rounding (device: fp32 + MUFU.RCP, numpy: fp64) may flip columns that sit exactly on a bound
             # (the kernel's clean-tile check also sees the neighbouring tiles' alignment bytes, so only compare where every
             # base quality is legal)

@@ -26,7 +26,12 @@ def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "wgs"
     knobs = {k: v for k, v in os.environ.items() if k.startswith("SSN_")}
     if mode == "panel":
-        cols = synth.make_columns(int(os.environ.get("KEXP_COLS", 16384)), depth_t=1500, depth_n=1500, seed=1734)
+        import numpy as np
+        unit = synth.make_columns(16384, depth_t=1500, depth_n=1500, seed=1734)
+        reps, ue = int(os.environ.get("KEXP_REPS", 4)), int(unit["n_entries"])
+        cols = dict(off=np.concatenate([unit["off"][:-1].astype(np.int64) + r * ue for r in range(reps)] + [np.array([reps * ue], np.int64)]).astype(np.uint32),
+                    bs=np.tile(unit["bs"], reps), bq=np.tile(unit["bq"], reps), mq=np.tile(unit["mq"], reps),
+                    ref_char=np.tile(unit["ref_char"], reps), ncol=reps * unit["ncol"], n_entries=reps * ue)
     else:
         cols = synth.make_columns(1_000_000, seed=1234)
     sc = api.Scorer(api.default_params(), device=0, n_slots=1, max_columns=cols["ncol"], max_entries=int(cols["n_entries"]) + 64)
