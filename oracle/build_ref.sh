@@ -41,4 +41,19 @@ for f in "$REF"/src/lib/sniper/*.c; do
 done
 gcc -Wall -O3 -DNDEBUG -fPIC -shared $INC "$HERE/ref_harness.c" $SRCS \
     -o "$OUT/libref_harness.so" "$ST/libbam.a" -lm -lz 2>"$OUT/build/ref_harness.log"
+# INTEGRATION.md's binding, compiled: the reference's own main()/walker/formatters with the per-column callback replaced
+# by tools/shim/ssn_shim.c (-> libssn.so).  Needs the built library; skipped (with a note) when it is not there yet.
+ROOT="$(cd "$HERE/.." && pwd)"
+LIBDIR="$ROOT/somatic_sniper_b200/lib"
+if [ -f "$LIBDIR/libssn.so" ]; then
+    OTHERS=""
+    for f in "$REF"/src/lib/sniper/*.c; do OTHERS="$OTHERS $f"; done
+    gcc -Wall -O2 -DNDEBUG $INC -I"$ROOT/include" -I"$REF/src/lib" \
+        -Dglf_somatic=ssn_shim_column -DmakeSoloPrior=ssn_shim_solo_prior -Dsniper_maqcns_destroy=ssn_shim_finish \
+        -c "$REF/src/exe/bam-somaticsniper/main.c" -o "$OUT/build/main_shim.o" 2>"$OUT/build/ref_shim.log"
+    gcc -Wall -O2 -DNDEBUG $INC -I"$ROOT/include" -I"$REF/src/lib" "$OUT/build/main_shim.o" "$ROOT/tools/shim/ssn_shim.c" $OTHERS \
+        -o "$OUT/bam-somaticsniper-shim" "$ST/libbam.a" -L"$LIBDIR" -lssn -Wl,-rpath,"$LIBDIR" -lm -lz 2>>"$OUT/build/ref_shim.log"
+else
+    echo "build_ref: libssn.so not built yet; skipping bam-somaticsniper-shim" >&2
+fi
 echo "build_ref: ok -> $OUT"

@@ -519,6 +519,21 @@ int main(int argc, char *argv[])
             if (R.n_gpus == 0) R.n_gpus = 1;
         }
     }
+    if (!getenv("CUDA_VISIBLE_DEVICES")) {
+        /* the driver initialises every visible GPU at the first CUDA call (about a second each): show it the ones this run
+         * uses and renumber them */
+        char list[16 * MAX_GPUS] = "";
+        int seen[MAX_GPUS], n_seen = 0, k;
+        for (i = 0; i < R.n_gpus; ++i) {
+            for (k = 0; k < n_seen; ++k) if (seen[k] == R.gpus[i].device) break;
+            if (k == n_seen) {
+                seen[n_seen++] = R.gpus[i].device;
+                snprintf(list + strlen(list), sizeof(list) - strlen(list), "%s%d", n_seen > 1 ? "," : "", R.gpus[i].device);
+            }
+            R.gpus[i].device = k;
+        }
+        setenv("CUDA_VISIBLE_DEVICES", list, 1);
+    }
     for (i = 0; i < R.n_gpus; ++i) { R.gpus[i].run = &R; R.gpus[i].index = i; }
     R.n_slots = env_int("SSN_SLOTS", 3, 1, MAX_SLOTS);
     {

@@ -34,17 +34,7 @@ def decide(cols, tables=None, tile_rules=True):
     n1 = cnt(~nonref & rev & live).astype(np.int64)
     q1 = cnt((~nonref & rev & live) * q)
     q0 = cnt((~nonref & ~rev & live) * q)
-    n0 = n - m - n1
-    ok = n_all <= 255
-    nn, mm = np.minimum(n, 255), np.minimum(m, 255)
-    t1 = F[np.minimum(n1, 256)] * q1 / np.maximum(n1 + m, 1) + F[np.minimum(n0, 256)] * q0 / np.maximum(n0 + m, 1)
-    SU = (S + 3 * m) * 1.0001
-    U = np.maximum(SU + ab[nn, mm, 1], 0.0) + 1.1
-    tight = (m >= 1) & (m <= 8) & (SU <= 255.0)
-    vt = t["vt"].astype(np.float64)
-    U = np.where(tight, np.minimum(U, vt[nn, np.clip(m, 1, 8) - 1, np.minimum(np.ceil(SU), 255).astype(np.int64)] + 1.1), U)
-    hs = h[np.minimum(n - m, 255), mm]
-    sample_ok = ok & (t1 > SU) & (t1 + ab[nn, mm, 0] >= U) & (hs + ab[nn, mm, 2] >= U)
+    sample_ok = (n_all <= 255) & (sample_margin(t, n, m, S, n1, q1, q0) >= 0.0)
     nT, nN = n_all[0::2], n_all[1::2]
     wanted = (nT > 0) & (nN > 0) & (ref16 != 15)
     drop = wanted & np.isin(ref16, [1, 2, 4, 8]) & sample_ok[0::2] & sample_ok[1::2]
@@ -59,6 +49,27 @@ def decide(cols, tables=None, tile_rules=True):
         # slack bytes of the neighbouring tiles are scanned too (conservative in the kernel); ignore that here
         drop &= ~tile_bad[tile]
     return drop
+
+
+def sample_margin(t, n, m, S, n1, q1, q0):
+    """How far one sample is from not being settled: min(t1 - SU, t1 + cmin_all - U, h + g2_run - U) with the quantities of
+    ssn_prefilter.cuh's header (fp64 here, fp32 in the kernel); the filter needs t1 > SU and the other two >= 0, so a
+    sample is settled iff the value is >= 0 and t1 > SU (a margin of exactly 0 in the first term does not settle: it is
+    returned as -1e-9).  n: live read-bases (<= 255), m: non-reference ones, S: their base qualities summed, n1 / q1:
+    reference read-bases on the reverse strand and their q summed, q0: the forward strand's q sum."""
+    ab, h, F = t["ab"].astype(np.float64), t["h"].astype(np.float64), t["F"].astype(np.float64)
+    vt = t["vt"].astype(np.float64)
+    n, m, n1 = (np.asarray(x).astype(np.int64) for x in (n, m, n1))
+    n0 = n - m - n1
+    nn, mm = np.minimum(n, 255), np.minimum(m, 255)
+    t1 = F[np.minimum(n1, 256)] * q1 / np.maximum(n1 + m, 1) + F[np.minimum(n0, 256)] * q0 / np.maximum(n0 + m, 1)
+    SU = (S + 3 * m) * 1.0001
+    U = np.maximum(SU + ab[nn, mm, 1], 0.0) + 1.1
+    tight = (m >= 1) & (m <= 8) & (SU <= 255.0)
+    U = np.where(tight, np.minimum(U, vt[nn, np.clip(m, 1, 8) - 1, np.minimum(np.ceil(SU), 255).astype(np.int64)] + 1.1), U)
+    hs = h[np.minimum(n - m, 255), mm]
+    first = np.where(t1 > SU, t1 - SU, -1e-9)
+    return np.minimum(first, np.minimum(t1 + ab[nn, mm, 0] - U, hs + ab[nn, mm, 2] - U))
 
 
 def consensus_genotypes(glf):

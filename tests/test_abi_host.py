@@ -100,3 +100,24 @@ def test_bad_arguments(api):
     bad = api.default_params(n_hap=1)
     t, h = api.Tables(), C.c_void_p()
     assert lib.ssn_host_tables_create(C.byref(bad), C.byref(t), C.byref(h)) == -1
+
+
+def test_shim_binary_links_and_refuses_to_run_without_a_gpu(tmp_path):
+    """tools/shim/ssn_shim.c built against the unmodified reference (oracle/build_ref.sh): the binary exists, resolves
+    libssn.so, and - like everything else here - has no CPU scoring path."""
+    import shutil, subprocess
+    shim = os.path.join(ROOT, "oracle", "_ref", "bam-somaticsniper-shim")
+    if not os.path.exists(shim):
+        pytest.skip("oracle/_ref/bam-somaticsniper-shim is not built (no /root/reference here)")
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present; tests/test_cli_gpu.py runs the shim for real")
+    except ImportError:
+        pass
+    integ = os.path.join(ROOT, "tests", "golden", "integration")
+    fa = str(tmp_path / "small.fa")
+    shutil.copy(os.path.join(integ, "small.fa"), fa)
+    p = subprocess.run([shim, "-f", fa, os.path.join(integ, "t-small.bam"), os.path.join(integ, "n-small.bam"), str(tmp_path / "o")],
+                       stderr=subprocess.PIPE, timeout=120)
+    assert p.returncode == 1 and b"[ssn_shim] ssn_create" in p.stderr

@@ -282,3 +282,39 @@ def test_region_shards_on_every_physical_gpu(ct, tmp_path):
         ref = str(tmp_path / "ref")
         ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, ["-F", "vcf"])
         assert ct.comparable(ref) == outs[1]
+
+
+# ---- INTEGRATION.md's binding, compiled against the unmodified reference (tools/shim/ssn_shim.c) -------------------
+
+SHIM = os.path.join(ROOT, "oracle", "_ref", "bam-somaticsniper-shim")
+
+
+def test_reference_walker_through_the_shim_reproduces_expected_vcf(ct, tmp_path):
+    """Reference main() + reference walker (bam_sspileup_file) -> shim callback -> libssn.so -> reference formatter:
+    the reference's own integration test (integration-test/test_sniper.py:8-19) passes with the GPU behind main.c:146."""
+    if not os.path.exists(SHIM):
+        pytest.skip("oracle/_ref/bam-somaticsniper-shim is not built")
+    fa = str(tmp_path / "small.fa")
+    shutil.copy(os.path.join(INTEG, "small.fa"), fa)
+    out = str(tmp_path / "out.vcf")
+    r = ct.run_cli(SHIM, fa, os.path.join(INTEG, "t-small.bam"), os.path.join(INTEG, "n-small.bam"), out, ["-F", "vcf"])
+    assert r["rc"] == 0, r["stderr"]
+    assert ct.comparable(out) == ct.comparable(os.path.join(INTEG, "expected.vcf"))
+    for run in sorted(RUNS):
+        r = ct.run_cli(SHIM, fa, os.path.join(INTEG, "t-small.bam"), os.path.join(INTEG, "n-small.bam"), out, RUNS[run])
+        assert r["rc"] == 0, r["stderr"]
+        assert ct.comparable(out) == ct.comparable(os.path.join(INTEG, "ref_%s.out" % run)), run
+
+
+@pytest.mark.parametrize("opts", [[], ["-J", "-F", "vcf"], ["-p", "-Q", "0", "-F", "bed"], ["-q", "1", "-Q", "0", "-L", "-G", "-T", "0.7"]],
+                         ids=lambda o: "_".join(o) or "default")
+def test_shim_matches_reference_on_the_synthetic_pair(ct, synthetic_pair, opts, tmp_path):
+    if not os.path.exists(SHIM) or not ct.reference_available():
+        pytest.skip("oracle/_ref is not built")
+    p = synthetic_pair
+    mine, ref = str(tmp_path / "shim"), str(tmp_path / "ref")
+    r1 = ct.run_cli(SHIM, p["fasta"], p["tumor"], p["normal"], mine, opts)
+    r2 = ct.run_cli(ct.REF_CLI, p["fasta"], p["tumor"], p["normal"], ref, opts)
+    assert r1["rc"] == 0 and r2["rc"] == 0, r1["stderr"]
+    assert ct.comparable(mine) == ct.comparable(ref)
+    assert sum(1 for _ in open(ref)) > 20

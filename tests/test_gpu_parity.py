@@ -337,3 +337,31 @@ def test_prefilter_off_when_a_precondition_fails(mods):
     want = Oracle(het_rate=0.4).score_batch(cols["off"], cols["bs"], cols["bq"], cols["mq"], cols["ref_char"])
     assert np.array_equal(sites["column"].astype(np.int64), want["emit_col"].astype(np.int64))
     assert np.array_equal(api.sites_to_records(sites, cols["ref_char"]), want["recs"])
+
+
+@pytest.mark.parametrize("name,kw", [("default", dict()), ("TNr", dict(theta=0.7, n_hap=3, het_rate=0.01)), ("theta95", dict(theta=0.95))])
+def test_prefilter_kernel_on_the_boundary_columns(mods, name, kw):
+    """tests/golden/prefilter_boundary.npz: columns hill-climbed (9 million filter evaluations per parameter set,
+    tests/test_prefilter_fuzz.py) to within a few hundredths of the filter's decision boundary.  The kernel evaluates its
+    bounds in fp32 (MUFU.RCP division, 1e-4 slack): whatever it settles here must be hom-reference in both samples by the
+    full model's own dump, the product path must equal the every-column path, and the oracle must agree."""
+    import prefilter_np
+    api, synth, Oracle = mods
+    z = np.load(os.path.join(GOLD, "prefilter_boundary.npz"))
+    cols = {k: z["%s_%s" % (name, k)] for k in ("off", "bs", "bq", "mq", "ref_char")}
+    cols["ncol"], cols["n_entries"] = len(cols["ref_char"]), len(cols["bs"])
+    prm = api.default_params(min_somatic_qual=0, **kw)
+    sc = api.Scorer(prm, device=0, n_slots=1, max_columns=cols["ncol"], max_entries=cols["n_entries"] + 64)
+    assert sc.prefilter_enabled()
+    _, dump = sc.score(cols, dump=True)
+    full, _ = sc.score(cols, flags=api.SUBMIT_NO_PREFILTER)
+    fast, _ = sc.score(cols)
+    sc.close()
+    dropped = dump[:, 29] == 1
+    tg, ng = prefilter_np.consensus_genotypes(dump)
+    ref16 = api.nt16_lut()[cols["ref_char"]]
+    assert not (dropped & ((tg != ref16) | (ng != ref16))).any()
+    assert fast.tobytes() == full.tobytes()
+    assert dropped.mean() > 0.5, "most boundary columns are still inside for the fp32 evaluation (%.3f)" % dropped.mean()
+    want = Oracle(min_somatic_qual=0, **kw).score_batch(cols["off"], cols["bs"], cols["bq"], cols["mq"], cols["ref_char"], want_glf=True)
+    assert np.array_equal(dump[:, :28], want["glf"])
