@@ -49,7 +49,7 @@ if [ -f "$LIBDIR/libssn.so" ]; then
     OTHERS=""
     for f in "$REF"/src/lib/sniper/*.c; do OTHERS="$OTHERS $f"; done
     gcc -Wall -O2 -DNDEBUG $INC -I"$ROOT/include" -I"$REF/src/lib" \
-        -Dglf_somatic=ssn_shim_column -DmakeSoloPrior=ssn_shim_solo_prior -Dsniper_maqcns_destroy=ssn_shim_finish \
+        -Dglf_somatic=ssn_shim_column -DmakeSoloPrior=ssn_shim_solo_prior -Dbam_header_destroy=ssn_shim_finish \
         -c "$REF/src/exe/bam-somaticsniper/main.c" -o "$OUT/build/main_shim.o" 2>"$OUT/build/ref_shim.log"
     gcc -Wall -O2 -DNDEBUG $INC -I"$ROOT/include" -I"$REF/src/lib" "$OUT/build/main_shim.o" "$ROOT/tools/shim/ssn_shim.c" $OTHERS \
         -o "$OUT/bam-somaticsniper-shim" "$ST/libbam.a" -L"$LIBDIR" -lssn -Wl,-rpath,"$LIBDIR" -lm -lz 2>>"$OUT/build/ref_shim.log"

@@ -865,6 +865,9 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
 {
     uint32_t my_start = 0, total = 0;
     const uint32_t lt = (1u << lane) - 1u;
+    /* the batch descriptor sits in local memory behind the reference: take what the loops need into registers */
+    const uint8_t *__restrict__ g_bs = B.bs, *__restrict__ g_bq = B.bq, *__restrict__ g_mq = B.mq;
+    const uint32_t cap = (uint32_t)M.cap_mapq;
     for (int j = 0; j < 32; ++j) {
         const uint32_t nj = __shfl_sync(kFull, n, j);
         if (nj == 0) continue;
@@ -873,26 +876,29 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
         for (int i = lane * 4; i < kHistBins; i += 128) *reinterpret_cast<uint4*>(hist + i) = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
         uint32_t rt = 0, rn = 0, bad = 0;
-        /* four read-bases per lane and iteration (lane l takes i0 + 32 k + l): twelve independent byte loads in flight
-         * before the first MATCH, which is what hides the memory latency at 16 warps per SM */
-        for (uint32_t i0 = 0; i0 < nj; i0 += 128) {
-            uint32_t bs[4], bq[4], mq[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t i = i0 + 32u * (uint32_t)k + (uint32_t)lane;
-                bs[k] = bq[k] = mq[k] = 0u;
-                if (i < nj) { bs[k] = B.bs[e0 + i]; bq[k] = B.bq[e0 + i]; mq[k] = B.mq[e0 + i]; }
+        /* One aligned 32-bit word of each array per lane and iteration (four read-bases; 128 per warp): three loads in
+         * flight per lane instead of twelve byte loads.  The column starts `lead` bytes into its first word; bytes in
+         * front of it and behind its end are masked (the arrays carry 64 spare bytes behind the batch). */
+        const uint32_t a0 = e0 & ~3u, lead = e0 - a0, span = lead + nj;
+        for (uint32_t w0 = 0; w0 < span; w0 += 128u) {
+            const uint32_t wb = w0 + 4u * (uint32_t)lane;
+            uint32_t ws = 0u, wq = 0u, wm = 0u;
+            if (wb < span) {
+                ws = __ldg(reinterpret_cast<const uint32_t*>(g_bs + a0 + wb));
+                wq = __ldg(reinterpret_cast<const uint32_t*>(g_bq + a0 + wb));
+                wm = __ldg(reinterpret_cast<const uint32_t*>(g_mq + a0 + wb));
             }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint32_t i = i0 + 32u * (uint32_t)k + (uint32_t)lane;
+                const uint32_t idx = wb + (uint32_t)k, i = idx - lead;
+                const uint32_t bs = (ws >> (8 * k)) & 0xffu, bq = (wq >> (8 * k)) & 0xffu, mq = (wm >> (8 * k)) & 0xffu;
                 uint32_t bin = 0xffffffffu;
-                if (i < nj) {
+                if (idx >= lead && idx < span) {
                     const bool is_t = i < nTj;
-                    const uint32_t cls = is_t ? cls_t[bs[k] & 31u] : cls_n[bs[k] & 31u];  /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
-                    bad |= (bq[k] - 1u) > 62u ? 1u : 0u;
-                    bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq[k], mq[k]) & 63u) << 2 | ((cls >> 3) & 3u);
-                    const uint32_t m = min(mq[k] & 0x7fu, (uint32_t)M.cap_mapq);          /* sniper_maqcns.c:173-174 */
+                    const uint32_t cls = is_t ? cls_t[bs & 31u] : cls_n[bs & 31u];        /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
+                    bad |= (bq - 1u) > 62u ? 1u : 0u;
+                    bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq, mq) & 63u) << 2 | ((cls >> 3) & 3u);
+                    const uint32_t m = min(mq & 0x7fu, cap);                            /* sniper_maqcns.c:173-174 */
                     if (is_t) rt += m * m; else rn += m * m;
                 }
                 const uint32_t peers = __match_any_sync(kFull, bin);

@@ -11,7 +11,9 @@
  * oracle/build_ref.sh compiles the reference's main.c with
  *     -Dglf_somatic=ssn_shim_column            the callback installed at main.c:146
  *     -DmakeSoloPrior=ssn_shim_solo_prior      main.c:122-125: only called without -p, which pu_data2_t does not record
- *     -Dsniper_maqcns_destroy=ssn_shim_finish  main.c:154: the first clean-up call behind the walk, before fclose(snp_fh)
+ *     -Dbam_header_destroy=ssn_shim_finish     main.c:151: the first clean-up call behind the walk that can be redirected -
+ *                                              the batches still in flight are drained while the tumor header (target
+ *                                              names) and the output file are still there
  * i.e. the three one-line edits a maintainer would make by hand, and links this file, the other reference sources and
  * -lssn into oracle/_ref/bam-somaticsniper-shim.  Test infrastructure (tests/test_cli_gpu.py::test_reference_walker_
  * through_the_shim); the product's own CLI replaces the walker as well.
@@ -25,7 +27,7 @@
 /* the reference's headers, with the names the build line redirects restored for this file */
 #undef glf_somatic
 #undef makeSoloPrior
-#undef sniper_maqcns_destroy
+#undef bam_header_destroy
 #include "sniper/somatic_sniper.h"
 
 #define SHIM_COLUMNS (1u << 16)
@@ -186,8 +188,8 @@ int ssn_shim_column(uint32_t tid, uint32_t pos, int n1, int n2, const bam_pileup
     return 0;
 }
 
-/* behind the walk, before main() closes the output file (main.c:151-159) */
-void ssn_shim_finish(sniper_maqcns_t *bm)
+/* behind the walk, before main() frees the headers and closes the output file (main.c:149-159) */
+void ssn_shim_finish(bam_header_t *h)
 {
     if (S.ctx) {
         int i;
@@ -198,5 +200,5 @@ void ssn_shim_finish(sniper_maqcns_t *bm)
         S.ctx = 0;
         for (i = 0; i < SHIM_SLOTS; ++i) { free(S.slot[i].tid); free(S.slot[i].pos); free(S.slot[i].rb); }
     }
-    sniper_maqcns_destroy(bm);
+    bam_header_destroy(h);
 }
