@@ -863,7 +863,7 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
                                        uint32_t *runs, uint32_t runs_cap, int lane, uint32_t o0, uint32_t nT, uint32_t n, uint32_t ref16,
                                        uint32_t &my_rms_t, uint32_t &my_rms_n)
 {
-    uint32_t my_start = 0, total = 0;
+    uint32_t my_start = 0, my_count = 0, total = 0;
     const uint32_t lt = (1u << lane) - 1u;
     /* the batch descriptor sits in local memory behind the reference: take what the loops need into registers */
     const uint8_t *__restrict__ g_bs = B.bs, *__restrict__ g_bq = B.bq, *__restrict__ g_mq = B.mq;
@@ -875,50 +875,77 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
         const uint16_t *cls_t = T.cls + (16 + refj) * 32, *cls_n = T.cls + refj * 32;
         for (int i = lane * 4; i < kHistBins; i += 128) *reinterpret_cast<uint4*>(hist + i) = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
-        uint32_t rt = 0, rn = 0, bad = 0;
-        /* One aligned 32-bit word of each array per lane and iteration (four read-bases; 128 per warp): three loads in
-         * flight per lane instead of twelve byte loads.  The column starts `lead` bytes into its first word; bytes in
-         * front of it and behind its end are masked (the arrays carry 64 spare bytes behind the batch). */
+        uint32_t rt = 0, rn = 0, bad = 0, g_lo = 0, g_hi = 0;      /* g_*: groups of 32 bins this lane's atomics touched */
+        /* One aligned 32-bit word of each array per lane and iteration (four read-bases; 128 per warp), the next
+         * iteration's words already in flight while this one's are counted.  The column starts `lead` bytes into its
+         * first word; bytes in front of it and behind its end are masked (the arrays carry 64 spare bytes behind the
+         * batch).  The body is branch-free, so the four MATCH.ANY run converged, back to back. */
         const uint32_t a0 = e0 & ~3u, lead = e0 - a0, span = lead + nj;
-        for (uint32_t w0 = 0; w0 < span; w0 += 128u) {
-            const uint32_t wb = w0 + 4u * (uint32_t)lane;
-            uint32_t ws = 0u, wq = 0u, wm = 0u;
+        uint32_t ws = 0u, wq = 0u, wm = 0u;
+        {
+            const uint32_t wb = 4u * (uint32_t)lane;
             if (wb < span) {
                 ws = __ldg(reinterpret_cast<const uint32_t*>(g_bs + a0 + wb));
                 wq = __ldg(reinterpret_cast<const uint32_t*>(g_bq + a0 + wb));
                 wm = __ldg(reinterpret_cast<const uint32_t*>(g_mq + a0 + wb));
             }
+        }
+        for (uint32_t w0 = 0; w0 < span; w0 += 128u) {
+            const uint32_t wb = w0 + 4u * (uint32_t)lane, nb = wb + 128u;
+            const uint32_t cs = ws, cq = wq, cm = wm;
+            if (nb < span) {
+                ws = __ldg(reinterpret_cast<const uint32_t*>(g_bs + a0 + nb));
+                wq = __ldg(reinterpret_cast<const uint32_t*>(g_bq + a0 + nb));
+                wm = __ldg(reinterpret_cast<const uint32_t*>(g_mq + a0 + nb));
+            }
+            uint32_t bin[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const uint32_t idx = wb + (uint32_t)k, i = idx - lead;
-                const uint32_t bs = (ws >> (8 * k)) & 0xffu, bq = (wq >> (8 * k)) & 0xffu, mq = (wm >> (8 * k)) & 0xffu;
-                uint32_t bin = 0xffffffffu;
-                if (idx >= lead && idx < span) {
-                    const bool is_t = i < nTj;
-                    const uint32_t cls = is_t ? cls_t[bs & 31u] : cls_n[bs & 31u];        /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
-                    bad |= (bq - 1u) > 62u ? 1u : 0u;
-                    bin = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq, mq) & 63u) << 2 | ((cls >> 3) & 3u);
-                    const uint32_t m = min(mq & 0x7fu, cap);                            /* sniper_maqcns.c:173-174 */
-                    if (is_t) rt += m * m; else rn += m * m;
+                const uint32_t bs = (cs >> (8 * k)) & 0xffu, bq = (cq >> (8 * k)) & 0xffu, mq = (cm >> (8 * k)) & 0xffu;
+                const bool valid = idx >= lead && idx < span, is_t = i < nTj;
+                const uint32_t cls = (is_t ? cls_t : cls_n)[bs & 31u];                  /* sample<<15 | b4<<13 | valid<<4 | strand<<3 */
+                bad |= (valid && (bq - 1u) > 62u) ? 1u : 0u;
+                const uint32_t v = (cls >> 15) << 10 | ((cls >> 13) & 3u) << 8 | (min(bq, mq) & 63u) << 2 | ((cls >> 3) & 3u);
+                bin[k] = valid ? v : 0xffffffffu;
+                const uint32_t m = valid ? min(mq & 0x7fu, cap) : 0u;                   /* sniper_maqcns.c:173-174 */
+                rt += is_t ? m * m : 0u;
+                rn += is_t ? 0u : m * m;
+            }
+            uint32_t peers[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) peers[k] = __match_any_sync(kFull, bin[k]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (bin[k] != 0xffffffffu && (peers[k] & lt) == 0u) {
+                    atomicAdd(hist + bin[k], (uint32_t)__popc(peers[k]));
+                    const uint32_t gbit = 1u << ((bin[k] >> 5) & 31u);
+                    if (bin[k] & 1024u) g_hi |= gbit; else g_lo |= gbit;
                 }
-                const uint32_t peers = __match_any_sync(kFull, bin);
-                if (bin != 0xffffffffu && (peers & lt) == 0u) atomicAdd(hist + bin, (uint32_t)__popc(peers));
             }
         }
         if (__any_sync(kFull, bad != 0u)) return false;
         rt = __reduce_add_sync(kFull, rt);
         rn = __reduce_add_sync(kFull, rn);
+        g_lo = __reduce_or_sync(kFull, g_lo);
+        g_hi = __reduce_or_sync(kFull, g_hi);
         __syncwarp();
+        /* compaction, top down, over the groups of 32 bins that hold anything */
         uint32_t cnt = 0;
-        for (int it = 0; it < kHistBins / 32; ++it) {
-            const uint32_t bin = (uint32_t)(kHistBins - 1 - (it * 32 + lane));
-            const uint32_t c = hist[bin];
-            const uint32_t mask = __ballot_sync(kFull, c != 0u);
-            if (total + cnt + (uint32_t)__popc(mask) > runs_cap) return false;      /* more runs than the scratch holds */
-            if (c) runs[total + cnt + (uint32_t)__popc(mask & lt)] = bin << 17 | c;  /* c <= 65536 */
-            cnt += (uint32_t)__popc(mask);
+        for (int half = 1; half >= 0; --half) {
+            uint32_t groups = half ? g_hi : g_lo;
+            while (groups) {
+                const int gidx = 31 - __clz((int)groups);
+                groups &= ~(1u << gidx);
+                const uint32_t bin = (uint32_t)(half * 1024 + gidx * 32 + (31 - lane));
+                const uint32_t c = hist[bin];
+                const uint32_t mask = __ballot_sync(kFull, c != 0u);
+                if (total + cnt + (uint32_t)__popc(mask) > runs_cap) return false;  /* more runs than the scratch holds */
+                if (c) runs[total + cnt + (uint32_t)__popc(mask & lt)] = bin << 17 | c;  /* c <= 65536 */
+                cnt += (uint32_t)__popc(mask);
+            }
         }
-        if (lane == j) { my_start = total; my_rms_t = rt; my_rms_n = rn; }
+        if (lane == j) { my_start = total; my_count = cnt; my_rms_t = rt; my_rms_n = rn; }
         total += cnt;
         __syncwarp();
     }
@@ -928,12 +955,15 @@ __device__ __noinline__ bool hist_tile(const DevModel &M, const DevBatch &B, con
     chain_init(ch);
     const uint32_t *mine = runs + my_start;
     const uint32_t steps = __reduce_max_sync(kFull, n);
-    uint32_t left = 0, k = 0, rev = 0;
+    uint32_t left = 0, k = 1, rev = 0;
+    uint32_t nxt = my_count ? mine[0] : 0u;                 /* the next run is fetched a whole run ahead of its use */
     double qd = 0.0;
     for (uint32_t it = 0; it < steps; ++it) {
         if (it < n) {
             if (left == 0u) {
-                const uint32_t r = mine[k++];
+                const uint32_t r = nxt;
+                nxt = k < my_count ? mine[k] : 0u;
+                ++k;
                 const uint32_t bin = r >> 17;
                 left = r & 0x1ffffu;
                 const int sb = (int)(bin >> 8);
