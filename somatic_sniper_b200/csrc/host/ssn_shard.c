@@ -120,7 +120,8 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
         int32_t t, cap = 16, n = 0;
         ssn_bam_range *cuts;
         if (!o.max_reading) o.max_reading = o.n_threads >= 3 ? (2 * o.n_threads + 2) / 3 : 1;
-        if (!o.max_open) o.max_open = 2 * o.max_reading + 2;
+        if (o.max_reading > 48) o.max_reading = 48;              /* two threads and up to ~75 MB of finished windows each */
+        if (!o.max_open) o.max_open = o.max_reading + (o.max_reading < 8 ? o.max_reading + 2 : 8);
         for (t = 0; t < h->n_targets; ++t) genome += h->target_len[t];
         if (o.stride_windows) stride = (uint64_t)o.stride_windows << SSN_WINDOW_SHIFT;
         else {

@@ -79,7 +79,7 @@ def main():
             e = dict(env)
             e["SSN_GPUS"] = g
             r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine + ".%d" % g, opts, env=e, stats=os.path.join(w, "stats.json"))
-            assert r["rc"] == 0, r["stderr"]
+            assert r["rc"] == 0, "rc=%s\n%s" % (r["rc"], r["stderr"][-2000:])
             runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
         best = min(runs, key=lambda x: x["wall_s"])
         st = best["stats"]
