@@ -32,6 +32,7 @@ struct ssn_bgzf {
      * (region shards: many readers, one core each — the inflated bytes are framed while they are still in the cache) */
     int max_blocks;
     size_t raw_cap;
+    int use_zlib;               /* SSN_ZLIB_INFLATE: every block through zlib (measurement / fall-back knob) */
 };
 
 ssn_bgzf *ssn_bgzf_open(const char *path, ssn_pool *pool) { return ssn_bgzf_open_at(path, pool, 0); }
@@ -53,6 +54,7 @@ ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff)
 #endif
     }
     z->pool = pool;
+    z->use_zlib = getenv("SSN_ZLIB_INFLATE") != 0;
     z->max_blocks = (pool && ssn_pool_threads(pool) > 0) ? MAX_BLOCKS : 16;
     z->raw_cap = (pool && ssn_pool_threads(pool) > 0) ? RAW_CAP : ((size_t)2 << 20);
     z->raw = (uint8_t*)calloc(1, z->raw_cap + SSN_INFLATE_SLACK);
@@ -119,9 +121,7 @@ static void inflate_one(void *arg, int i)
     ssn_bgzf *z = ((inflate_arg*)arg)->z;
     blk *b = &z->blocks[i];
     int st;
-    static int use_zlib = -1;
-    if (use_zlib < 0) use_zlib = getenv("SSN_ZLIB_INFLATE") != 0;          /* measurement / fall-back knob */
-    if (!use_zlib && ssn_inflate_raw(b->cdata, b->clen, z->out + b->uoff, b->ulen) == 0) return;
+    if (!z->use_zlib && ssn_inflate_raw(b->cdata, b->clen, z->out + b->uoff, b->ulen) == 0) return;
     /* zlib reads every stream the reference reads; the fast decoder gave up on this one (or is switched off) */
     if (!t_zs_ready) {
         memset(&t_zs, 0, sizeof(t_zs));

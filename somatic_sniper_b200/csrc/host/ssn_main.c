@@ -25,7 +25,9 @@
  * There is no CPU scoring path: without a usable sm_100 device the program fails.
  */
 #include <ctype.h>
+#include <execinfo.h>
 #include <malloc.h>
+#include <signal.h>
 #include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -131,6 +133,19 @@ struct run {
     pthread_cond_t cv;
     int error, gpus_ready, go;
 };
+
+/* a crash leaves a trace: the faulting address, the call stack (module + offset: addr2line -e <module> <offset>) */
+static void crash_handler(int sig, siginfo_t *si, void *uc)
+{
+    void *frames[48];
+    int n;
+    (void)uc;
+    fprintf(stderr, "[bam-somaticsniper] fatal signal %d at address %p; call stack:\n", sig, si ? si->si_addr : 0);
+    n = backtrace(frames, 48);
+    backtrace_symbols_fd(frames, n, 2);
+    signal(sig, SIG_DFL);
+    raise(sig);
+}
 
 static double now_s(void)
 {
@@ -469,6 +484,12 @@ int main(int argc, char *argv[])
 
     /* window buffers of a megabyte or so are allocated and freed by the dozen per second on many threads: keep them on the
      * malloc arenas instead of one mmap/munmap system call each (those serialise on the process's address-space lock) */
+    {
+        struct sigaction sa;
+        memset(&sa, 0, sizeof(sa));
+        sa.sa_sigaction = crash_handler; sa.sa_flags = SA_SIGINFO;
+        sigaction(SIGSEGV, &sa, 0); sigaction(SIGBUS, &sa, 0); sigaction(SIGABRT, &sa, 0);
+    }
     mallopt(M_MMAP_THRESHOLD, 32 << 20);
     mallopt(M_TRIM_THRESHOLD, 1 << 30);
     memset(&R, 0, sizeof(R));
