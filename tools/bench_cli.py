@@ -78,7 +78,12 @@ def main():
         for i in range(a.repeat):
             e = dict(env)
             e["SSN_GPUS"] = g
-            r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine + ".%d" % g, opts, env=e, stats=os.path.join(w, "stats.json"))
+            for attempt in range(3):
+                r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine + ".%d" % g, opts, env=e, stats=os.path.join(w, "stats.json"))
+                if r["rc"] == 0:
+                    break
+                res.setdefault("failed_runs", []).append(dict(gpus=g, rc=r["rc"], stderr=r["stderr"][-4000:]))
+                print("run failed rc=%s\n%s" % (r["rc"], r["stderr"][-4000:]), file=sys.stderr, flush=True)
             assert r["rc"] == 0, "rc=%s\n%s" % (r["rc"], r["stderr"][-2000:])
             runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
         best = min(runs, key=lambda x: x["wall_s"])
