@@ -240,19 +240,22 @@ ssn_status ssn_shardset_next(ssn_shardset *set, int32_t *index, ssn_packer **pac
     pthread_mutex_lock(&set->mu);
     if (set->next_claim >= set->n) { pthread_mutex_unlock(&set->mu); return SSN_OK; }
     set->started = 1;
-    s = &set->sh[set->next_claim];
+    /* the index is taken before anything can wait: a second caller arriving while this one waits for its shard's readers
+     * must get the NEXT shard, never the same one */
+    const int32_t k = set->next_claim++;
+    s = &set->sh[k];
     if (set->serial) { s->pk = set->serial; s->state = SH_OPEN; }
     while (s->state < SH_OPEN && !set->failed) {
         open_more(set);
         if (s->state < SH_OPEN && !set->failed) pthread_cond_wait(&set->cv, &set->mu);
     }
     if (set->failed || !s->pk) {
-        ssn_host_set_error("region shard %d: %s", (int)set->next_claim, set->err[0] ? set->err : "cannot start its readers");
+        ssn_host_set_error("region shard %d: %s", (int)k, set->err[0] ? set->err : "cannot start its readers");
         pthread_mutex_unlock(&set->mu);
         return SSN_ERR_STATE;
     }
     s->state = SH_CLAIMED;
-    *index = set->next_claim++; *packer = s->pk;
+    *index = k; *packer = s->pk;
     pthread_mutex_unlock(&set->mu);
     return SSN_OK;
 }

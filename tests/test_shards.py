@@ -298,3 +298,40 @@ def test_mixed_routes_windows_too_deep_for_a_read_batch(host, big_pair):
     pk.close()
     assert n_reads_batches >= 2 and n_col_batches >= 10
     assert got == want
+
+
+def test_several_consumers_take_distinct_shards(host, big_pair):
+    """One feeder per GPU takes shards from the same set.  Callers that arrive while an earlier one still waits for its
+    shard's readers must get the next shard, not the same one (a claim race handed one packer to two feeders once: they
+    then freed each other's windows).  Four threads, tiny intervals so that callers outrun the readers; the union of what
+    they pack equals the single consumer's, and every shard is handed out exactly once."""
+    import threading
+    p = big_pair
+    def run(n_consumers):
+        ss = host.ShardSet(p["tumor"], p["normal"], p["fasta"], 0, threads=6, stride_windows=1, lookback_windows=1, max_reading=2, max_open=3)
+        got, seen, lock, errs = {}, [], threading.Lock(), []
+        def work():
+            try:
+                for idx, pk in ss.shards():
+                    cols = 0
+                    sig = 0
+                    for rb in pk.read_batches(max_windows=2):
+                        b = host.pack_read_windows(rb)
+                        cols += b["ncol"]
+                        sig += int(b["bs"].astype(np.int64).sum()) + 3 * int(b["bq"].astype(np.int64).sum())
+                    with lock:
+                        seen.append(idx)
+                        got[idx] = (cols, sig)
+            except Exception as e:          # noqa: BLE001
+                errs.append(e)
+        th = [threading.Thread(target=work) for _ in range(n_consumers)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        n = ss.n_shards()
+        assert not ss.long_span()
+        ss.close()
+        assert not errs, errs
+        assert sorted(seen) == list(range(n))
+        return got
+    one, four = run(1), run(4)
+    assert one == four and sum(c for c, _ in one.values()) > 100000
