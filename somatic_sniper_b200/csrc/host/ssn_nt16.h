@@ -6,7 +6,7 @@
 
 static const char ssn_nt16_rev[] = "=ACMGRSVTWYHKDBN";
 
-static inline int ssn_nt16_table(int ch)
+static inline int ssn_nt16_slow(int ch)
 {
     int i;
     ch &= 0xff;
@@ -16,6 +16,20 @@ static inline int ssn_nt16_table(int ch)
         if (ch == r || (r >= 'A' && r <= 'Z' && ch == r + ('a' - 'A'))) return i;
     }
     return 15;
+}
+
+/* the same through a 256-entry table (filled on first use; the packer asks once per reference position) */
+static inline int ssn_nt16_table(int ch)
+{
+    static unsigned char lut[256];
+    static volatile int ready = 0;
+    if (!ready) {
+        int i;
+        for (i = 0; i < 256; ++i) lut[i] = (unsigned char)ssn_nt16_slow(i);   /* idempotent: a race writes the same bytes */
+        __sync_synchronize();
+        ready = 1;
+    }
+    return lut[ch & 0xff];
 }
 
 #endif

@@ -536,7 +536,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     uint32_t grid = (uint32_t)(ctx->num_sms * per_sm);
     const uint32_t need_ctas = (ntiles + kWarpsPerCta - 1) / kWarpsPerCta;
     if (grid > need_ctas && !listed) grid = need_ctas;
-    uint32_t list_width = 0;
+    uint32_t list_width = 0, list_generic_auto = 0;
     if (listed) {
         /* The survivor count is only known on the device.  Size the grid from the last collected batch (x1.5, 16-column
          * tiles, one tile per warp) so that the SMs it does not need stay free for the next batch's pre-filter kernel on
@@ -548,6 +548,10 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
         const bool alternating = ctx->last_slot >= 0 && ctx->last_slot != b->index;
         list_width = alternating ? 0u : 4u;
         uint32_t cols_per_warp = alternating ? (uint32_t)kListWidth : 4u;
+        /* One batch in flight and no more survivors than resident warps: one column per warp through the warp-cooperative
+         * sorting path.  Its code is short (no instruction-cache misses on the unrolled networks), which is what a
+         * latency-bound launch of a single tile per warp needs: 46 us instead of 72 us on the bench workload. */
+        if (!alternating && est <= (double)grid * kWarpsPerCta && b->max_col_words <= words / 32u) { list_width = 1u; cols_per_warp = 1u; list_generic_auto = 1u; }
         { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; if (w == 1 || w == 2 || w == 4 || w == 8 || w == 16) cols_per_warp = (uint32_t)w; }
         const uint32_t want = (uint32_t)(est / (cols_per_warp * kWarpsPerCta * tiles_per_warp)) + 1u;
         grid = std::min(grid, std::max(want, 8u));
@@ -576,7 +580,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
     B.collist = listed ? b->d_survivors : nullptr;
     B.list_count = b->d_count + 2;
     { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; B.list_width = (w == 1 || w == 2 || w == 4 || w == 8 || w == 16) ? (uint32_t)w : list_width; }
-    { static const int lg = getenv("SSN_LIST_GENERIC") ? atoi(getenv("SSN_LIST_GENERIC")) : 0; B.list_generic = (uint32_t)lg; }
+    { static const int lg = getenv("SSN_LIST_GENERIC") ? atoi(getenv("SSN_LIST_GENERIC")) : 0; B.list_generic = lg ? (uint32_t)lg : list_generic_auto; }
     KernelTimer &kt = ctx->timers[ctx->timer_next];
     ctx->timer_next = (ctx->timer_next + 1) % ctx->timers.size();
     ssn_status st = timer_collect(ctx, kt);
