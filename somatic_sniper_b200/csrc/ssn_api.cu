@@ -551,7 +551,7 @@ static ssn_status launch(ssn_ctx *ctx, ssn_batch *b, uint32_t flags)
         /* One batch in flight and no more survivors than resident warps: one column per warp through the warp-cooperative
          * sorting path.  Its code is short (no instruction-cache misses on the unrolled networks), which is what a
          * latency-bound launch of a single tile per warp needs: 46 us instead of 72 us on the bench workload. */
-        if (!alternating && est <= (double)grid * kWarpsPerCta && b->max_col_words <= words / 32u) { list_width = 1u; cols_per_warp = 1u; list_generic_auto = 1u; }
+        if (!alternating && est <= (double)grid * kWarpsPerCta) { list_width = 1u; cols_per_warp = 1u; list_generic_auto = 1u; }
         { const char *e = getenv("SSN_LIST_W"); const int w = e ? atoi(e) : 0; if (w == 1 || w == 2 || w == 4 || w == 8 || w == 16) cols_per_warp = (uint32_t)w; }
         const uint32_t want = (uint32_t)(est / (cols_per_warp * kWarpsPerCta * tiles_per_warp)) + 1u;
         grid = std::min(grid, std::max(want, 8u));
