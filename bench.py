@@ -567,7 +567,7 @@ def run_b200(args):
                  "roofline": {"bound": "hbm", "achieved": p_alg / (pm * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                               "frac": p_alg / (pm * 1e-3) / 1e9 / peak,
                               "traffic": (int(ncu_traffic("panel_dram_bytes_per_launch") * (p_alg / 295195500.0)) if ncu_traffic("panel_dram_bytes_per_launch") else None),
-                              "traffic_note": "ncu capture of half this batch (32768 columns, 295.2 MB algorithmic, 328.8 MB DRAM), scaled by size",
+                              "traffic_note": "ncu capture of half this batch (32768 columns, 295.2 MB algorithmic, 329.1 MB DRAM), scaled by size",
                               "kernel": "ssn_score_kernel<false> (deep columns)",
                               "algorithmic_bytes_per_launch": p_alg, "ceiling_columns_per_s": peak * 1e9 / (p_alg / pcols["ncol"])},
                  "l2": "inputs (%.0f MB per step) exceed the 126 MB L2; no flush" % (p_alg / 1e6)}
