@@ -241,6 +241,25 @@ ssn_status ssn_batch_download_columns(ssn_ctx *ctx, ssn_batch *b);
 /* Sum of the pileup kernels' durations since the last reset. */
 ssn_status ssn_pileup_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_batches, int reset);
 
+/* ---- BGZF blocks inflated on the device ------------------------------------------------------------------------
+ * Replaces, for the BAM readers, the per-block inflateInit2 / inflate / inflateEnd of samtools-0.1.6 bgzf.c:330-353
+ * (under bgzf_read :489 and bam_read1, bam.c:181-212): one warp per block (csrc/ssn_inflate_dev.cuh).  A reader thread
+ * acquires a LANE (pinned input and output buffers, a stream), lays the deflate payloads of up to max_blocks blocks into
+ * the input buffer back to back, describes them, and calls ssn_inflater_run: synchronous for the caller, no CPU while it
+ * waits; thread-safe, one lane per calling thread at a time.  refused[i] = 1 marks a block the device decoder gave up on
+ * (nothing usable at its out_off): the caller inflates it on the host, so the service never changes what is read. */
+typedef struct { uint32_t in_off, in_len, out_off, out_len; } ssn_inflate_block;
+typedef struct ssn_inflater ssn_inflater;
+ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t in_cap, uint64_t out_cap, uint32_t max_blocks, ssn_inflater **out);
+void ssn_inflater_destroy(ssn_inflater *f);
+ssn_status ssn_inflater_limits(const ssn_inflater *f, uint64_t *in_cap, uint64_t *out_cap, uint32_t *max_blocks);
+/* blocks until a lane is free; *in / *out are its pinned buffers (in_cap / out_cap bytes, valid until the release) */
+ssn_status ssn_inflater_lane_acquire(ssn_inflater *f, int32_t *lane, uint8_t **in, uint8_t **out);
+void ssn_inflater_lane_release(ssn_inflater *f, int32_t lane);
+ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
+                            uint64_t out_bytes, uint8_t *refused);
+ssn_status ssn_inflater_stats(ssn_inflater *f, uint64_t *blocks, uint64_t *refused, uint64_t *runs, uint64_t *in_bytes, uint64_t *out_bytes);
+
 /* Writes a buffer larger than L2 on the ctx's device (cold-cache timing). */
 ssn_status ssn_flush_l2(ssn_ctx *ctx);
 

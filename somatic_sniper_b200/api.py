@@ -105,6 +105,13 @@ SIGNATURES = {
     "ssn_batch_column_positions": (_I, [_VP, C.POINTER(_VP), C.POINTER(_U32), C.POINTER(_U64)]),
     "ssn_batch_download_columns": (_I, [_VP, _VP]),
     "ssn_pileup_time": (_I, [_VP, C.POINTER(C.c_float), C.POINTER(_U64), _I]),
+    "ssn_inflater_create": (_I, [_I, _U32, _U64, _U64, _U32, C.POINTER(_VP)]),
+    "ssn_inflater_destroy": (None, [_VP]),
+    "ssn_inflater_limits": (_I, [_VP, C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U32)]),
+    "ssn_inflater_lane_acquire": (_I, [_VP, C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.POINTER(C.c_uint8))]),
+    "ssn_inflater_lane_release": (None, [_VP, C.c_int32]),
+    "ssn_inflater_run": (_I, [_VP, C.c_int32, _VP, _U32, _U64, _U64, C.POINTER(C.c_uint8)]),
+    "ssn_inflater_stats": (_I, [_VP, C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64)]),
 }
 
 _lib = None
@@ -415,3 +422,59 @@ def sites_to_records(sites, ref_chars):
         rec[:, base + 23] = s["total_depth"]
         rec[:, base + 24] = s["total_mean_mapQ"]
     return rec
+
+
+INFLATE_BLOCK_DTYPE = np.dtype([("in_off", np.uint32), ("in_len", np.uint32), ("out_off", np.uint32), ("out_len", np.uint32)])
+
+
+class Inflater:
+    """ssn_inflater: BGZF blocks inflated on the GPU (csrc/ssn_inflate_api.cu); mirror for tests and tools."""
+
+    def __init__(self, device=0, n_lanes=4, in_cap=8 << 20, out_cap=16 << 20, max_blocks=256):
+        self.lib = load_library()
+        self.h = _VP()
+        _check(self.lib.ssn_inflater_create(device, n_lanes, in_cap, out_cap, max_blocks, C.byref(self.h)))
+        self.in_cap, self.out_cap, self.max_blocks = in_cap, out_cap, max_blocks
+
+    def close(self):
+        if self.h:
+            self.lib.ssn_inflater_destroy(self.h)
+            self.h = _VP()
+
+    def acquire(self):
+        lane, pi, po = C.c_int32(), C.POINTER(C.c_uint8)(), C.POINTER(C.c_uint8)()
+        _check(self.lib.ssn_inflater_lane_acquire(self.h, C.byref(lane), C.byref(pi), C.byref(po)))
+        return lane.value, np.ctypeslib.as_array(pi, shape=(self.in_cap,)), np.ctypeslib.as_array(po, shape=(self.out_cap,))
+
+    def release(self, lane):
+        self.lib.ssn_inflater_lane_release(self.h, lane)
+
+    def run(self, lane, blocks, in_bytes, out_bytes):
+        blocks = np.ascontiguousarray(blocks, INFLATE_BLOCK_DTYPE)
+        refused = np.zeros(len(blocks), np.uint8)
+        _check(self.lib.ssn_inflater_run(self.h, lane, blocks.ctypes.data, len(blocks), in_bytes, out_bytes,
+                                         refused.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return refused
+
+    def inflate_many(self, payloads, sizes):
+        """payloads: list of raw deflate streams, sizes: their inflated sizes -> (list of bytes or None where refused)"""
+        lane, hin, hout = self.acquire()
+        try:
+            out = []
+            i = 0
+            while i < len(payloads):
+                blk, a, b = [], 0, 0
+                j = i
+                while j < len(payloads) and len(blk) < self.max_blocks and a + len(payloads[j]) + 4 <= self.in_cap and b + sizes[j] <= self.out_cap:
+                    hin[a:a + len(payloads[j])] = np.frombuffer(payloads[j], np.uint8)
+                    blk.append((a, len(payloads[j]), b, sizes[j]))
+                    a += len(payloads[j]); b += sizes[j]
+                    j += 1
+                assert j > i, "a block does not fit the lane"
+                refused = self.run(lane, np.array(blk, INFLATE_BLOCK_DTYPE), a, b)
+                for (ao, al, bo, bl), r in zip(blk, refused):
+                    out.append(None if r else hout[bo:bo + bl].tobytes())
+                i = j
+            return out
+        finally:
+            self.release(lane)

@@ -1,0 +1,207 @@
+/*
+ * ssn_inflate_api.cu — BGZF blocks inflated on the GPU: the kernel around ssn_inflate_dev.cuh (one warp per block) and
+ * the thread-safe "lane" service the BAM readers call (include/ssn.h: ssn_inflater_*).
+ *
+ * A lane is what one reader thread owns while it reads: a pinned input buffer it fills with the compressed payloads of
+ * a few dozen blocks, a pinned output buffer it frames records from, their device twins and a stream.  ssn_inflater_run
+ * is synchronous for the caller (copy in, kernel, copy out, wait) and costs it no CPU while it waits; dozens of readers
+ * do that at once, so the device sees dozens of small launches on independent streams that together fill its SMs.
+ * A block the device decoder refuses comes back flagged and the reader inflates it on the host (zlib reads everything
+ * the reference reads), so the service can never change what is read.
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <condition_variable>
+#include <vector>
+
+#include "ssn.h"
+#include "ssn_inflate_dev.cuh"
+
+extern "C" void ssn_set_error(const char *fmt, ...);
+
+#define CUI(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            ssn_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return SSN_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+
+constexpr int kInflWarps = 8;              /* per CTA: 8 x 12.4 KB of tables; two CTAs per SM */
+
+__global__ void __launch_bounds__(kInflWarps * 32)
+ssn_inflate_kernel(const uint8_t *__restrict__ in, const ssn_inflate_block *__restrict__ blk, uint32_t n, uint8_t *out,
+                   uint32_t *status, uint32_t *counter)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    infl::Work &W = reinterpret_cast<infl::Work*>(smem_raw)[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(counter, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= n) break;
+        const ssn_inflate_block b = blk[i];
+        const int rc = infl::inflate_block(W, in + b.in_off, b.in_len, out + b.out_off, b.out_len);
+        if (lane == 0) status[i] = (uint32_t)rc;
+        __syncwarp();
+    }
+}
+
+struct Lane {
+    bool ready = false, busy = false;
+    uint8_t *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    ssn_inflate_block *h_blk = nullptr, *d_blk = nullptr;
+    uint32_t *h_status = nullptr, *d_status = nullptr, *d_counter = nullptr;
+    cudaStream_t stream = nullptr;
+};
+
+struct ssn_inflater {
+    int device, num_sms;
+    uint64_t in_cap, out_cap;
+    uint32_t max_blocks;
+    std::vector<Lane> lanes;
+    std::mutex mu;
+    std::condition_variable cv;
+    uint64_t blocks = 0, refused = 0, runs = 0, in_bytes = 0, out_bytes = 0;
+};
+
+extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t in_cap, uint64_t out_cap, uint32_t max_blocks, ssn_inflater **out)
+{
+    if (!out || !n_lanes || !in_cap || !out_cap || !max_blocks) { ssn_set_error("ssn_inflater_create: bad argument"); return SSN_ERR_ARG; }
+    CUI(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUI(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) { ssn_set_error("ssn_inflater_create: device %d is not sm_100", device); return SSN_ERR_CUDA; }
+    CUI(cudaFuncSetAttribute(ssn_inflate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kInflWarps * sizeof(infl::Work))));
+    ssn_inflater *f = new ssn_inflater();
+    f->device = device; f->num_sms = prop.multiProcessorCount;
+    f->in_cap = (in_cap + 63) & ~63ull; f->out_cap = (out_cap + 63) & ~63ull; f->max_blocks = max_blocks;
+    f->lanes.resize(n_lanes);
+    *out = f;
+    return SSN_OK;
+}
+
+static void lane_free(Lane &L)
+{
+    cudaFreeHost(L.h_in); cudaFreeHost(L.h_out); cudaFreeHost(L.h_blk); cudaFreeHost(L.h_status);
+    cudaFree(L.d_in); cudaFree(L.d_out); cudaFree(L.d_blk); cudaFree(L.d_status); cudaFree(L.d_counter);
+    if (L.stream) cudaStreamDestroy(L.stream);
+    L = Lane();
+}
+
+extern "C" void ssn_inflater_destroy(ssn_inflater *f)
+{
+    if (!f) return;
+    cudaSetDevice(f->device);
+    for (Lane &L : f->lanes) if (L.ready) { cudaStreamSynchronize(L.stream); lane_free(L); }
+    delete f;
+}
+
+/* buffers of a lane on first use (pinned allocations are slow: readers that never come cost nothing) */
+static ssn_status lane_prepare(ssn_inflater *f, Lane &L)
+{
+    if (L.ready) return SSN_OK;
+    CUI(cudaSetDevice(f->device));
+    CUI(cudaMallocHost(&L.h_in, f->in_cap + 64));
+    CUI(cudaMallocHost(&L.h_out, f->out_cap + 64));
+    CUI(cudaMallocHost(&L.h_blk, sizeof(ssn_inflate_block) * f->max_blocks));
+    CUI(cudaMallocHost(&L.h_status, 4 * (size_t)f->max_blocks));
+    CUI(cudaMalloc(&L.d_in, f->in_cap + 64));
+    CUI(cudaMalloc(&L.d_out, f->out_cap + 64));
+    CUI(cudaMalloc(&L.d_blk, sizeof(ssn_inflate_block) * f->max_blocks));
+    CUI(cudaMalloc(&L.d_status, 4 * (size_t)f->max_blocks));
+    CUI(cudaMalloc(&L.d_counter, 4));
+    CUI(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    memset(L.h_in, 0, f->in_cap + 64);
+    L.ready = true;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_inflater_lane_acquire(ssn_inflater *f, int32_t *lane, uint8_t **in, uint8_t **out)
+{
+    if (!f || !lane || !in || !out) { ssn_set_error("ssn_inflater_lane_acquire: null"); return SSN_ERR_ARG; }
+    int pick = -1;
+    {
+        std::unique_lock<std::mutex> lk(f->mu);
+        for (;;) {
+            for (size_t i = 0; i < f->lanes.size(); ++i) if (!f->lanes[i].busy && f->lanes[i].ready) { pick = (int)i; break; }   /* a warm one first */
+            if (pick < 0) for (size_t i = 0; i < f->lanes.size(); ++i) if (!f->lanes[i].busy) { pick = (int)i; break; }
+            if (pick >= 0) break;
+            f->cv.wait(lk);
+        }
+        f->lanes[pick].busy = true;
+    }
+    ssn_status st = lane_prepare(f, f->lanes[pick]);
+    if (st != SSN_OK) {
+        std::lock_guard<std::mutex> lk(f->mu);
+        f->lanes[pick].busy = false;
+        f->cv.notify_one();
+        return st;
+    }
+    *lane = pick; *in = f->lanes[pick].h_in; *out = f->lanes[pick].h_out;
+    return SSN_OK;
+}
+
+extern "C" void ssn_inflater_lane_release(ssn_inflater *f, int32_t lane)
+{
+    if (!f || lane < 0 || (size_t)lane >= f->lanes.size()) return;
+    std::lock_guard<std::mutex> lk(f->mu);
+    f->lanes[lane].busy = false;
+    f->cv.notify_one();
+}
+
+extern "C" ssn_status ssn_inflater_limits(const ssn_inflater *f, uint64_t *in_cap, uint64_t *out_cap, uint32_t *max_blocks)
+{
+    if (!f) { ssn_set_error("ssn_inflater_limits: null"); return SSN_ERR_ARG; }
+    if (in_cap) *in_cap = f->in_cap;
+    if (out_cap) *out_cap = f->out_cap;
+    if (max_blocks) *max_blocks = f->max_blocks;
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
+                                       uint64_t out_bytes, uint8_t *refused)
+{
+    if (!f || lane < 0 || (size_t)lane >= f->lanes.size() || !blk || !refused) { ssn_set_error("ssn_inflater_run: bad argument"); return SSN_ERR_ARG; }
+    Lane &L = f->lanes[lane];
+    if (!L.busy || !L.ready) { ssn_set_error("ssn_inflater_run: lane was not acquired"); return SSN_ERR_STATE; }
+    if (n > f->max_blocks || in_bytes > f->in_cap || out_bytes > f->out_cap) { ssn_set_error("ssn_inflater_run: batch exceeds the lane"); return SSN_ERR_ARG; }
+    if (n == 0) return SSN_OK;
+    for (uint32_t i = 0; i < n; ++i) {
+        if ((uint64_t)blk[i].in_off + blk[i].in_len > in_bytes || (uint64_t)blk[i].out_off + blk[i].out_len > out_bytes) { ssn_set_error("ssn_inflater_run: block %u lies outside the batch", i); return SSN_ERR_ARG; }
+        L.h_blk[i] = blk[i];
+    }
+    CUI(cudaSetDevice(f->device));
+    CUI(cudaMemsetAsync(L.d_counter, 0, 4, L.stream));
+    CUI(cudaMemcpyAsync(L.d_in, L.h_in, ((size_t)in_bytes + 63) & ~(size_t)63, cudaMemcpyHostToDevice, L.stream));
+    CUI(cudaMemcpyAsync(L.d_blk, L.h_blk, sizeof(ssn_inflate_block) * n, cudaMemcpyHostToDevice, L.stream));
+    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)f->num_sms * 2u);
+    ssn_inflate_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), L.stream>>>(L.d_in, L.d_blk, n, L.d_out, L.d_status, L.d_counter);
+    CUI(cudaGetLastError());
+    CUI(cudaMemcpyAsync(L.h_out, L.d_out, (size_t)out_bytes, cudaMemcpyDeviceToHost, L.stream));
+    CUI(cudaMemcpyAsync(L.h_status, L.d_status, 4 * (size_t)n, cudaMemcpyDeviceToHost, L.stream));
+    CUI(cudaStreamSynchronize(L.stream));
+    uint32_t bad = 0;
+    for (uint32_t i = 0; i < n; ++i) { refused[i] = L.h_status[i] != 0; bad += refused[i]; }
+    {
+        std::lock_guard<std::mutex> lk(f->mu);
+        f->blocks += n; f->refused += bad; f->runs += 1; f->in_bytes += in_bytes; f->out_bytes += out_bytes;
+    }
+    return SSN_OK;
+}
+
+extern "C" ssn_status ssn_inflater_stats(ssn_inflater *f, uint64_t *blocks, uint64_t *refused, uint64_t *runs, uint64_t *in_bytes, uint64_t *out_bytes)
+{
+    if (!f) { ssn_set_error("ssn_inflater_stats: null"); return SSN_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(f->mu);
+    if (blocks) *blocks = f->blocks;
+    if (refused) *refused = f->refused;
+    if (runs) *runs = f->runs;
+    if (in_bytes) *in_bytes = f->in_bytes;
+    if (out_bytes) *out_bytes = f->out_bytes;
+    return SSN_OK;
+}

@@ -122,3 +122,120 @@ def test_every_block_of_the_integration_and_simulated_bams(inflate, tmp_path):
             at += bsize
             n += 1
     assert n > 100
+
+
+# ---- the DEVICE decoder's source (csrc/ssn_inflate_dev.cuh), compiled for the host with its lane loops as real loops ----
+
+@pytest.fixture(scope="module")
+def inflate_dev(built):
+    from somatic_sniper_b200 import api
+    lib = api.load_library()
+    lib.ssn_inflate_dev_host_shift.argtypes = [C.c_char_p, C.c_uint32, C.c_char_p, C.c_uint32, C.c_uint32]
+    lib.ssn_inflate_dev_host_shift.restype = C.c_int
+
+    def run(comp, ulen, shift=0):
+        dst = C.create_string_buffer(ulen + 16)
+        dst.raw = b"\x5a" * (ulen + 16)
+        rc = lib.ssn_inflate_dev_host_shift(comp, len(comp), dst, ulen, shift)
+        assert dst.raw[ulen:] == b"\x5a" * 16, "wrote past the end of the output"
+        return rc, dst.raw[:ulen]
+    return run
+
+
+@pytest.mark.parametrize("name", sorted(SAMPLES))
+def test_device_decoder_source_matches_zlib(inflate_dev, name):
+    data = SAMPLES[name]
+    k = 0
+    for level in (0, 1, 6, 9):
+        for strategy in (zlib.Z_DEFAULT_STRATEGY, zlib.Z_FIXED, zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE):
+            comp = _deflate(data, level, strategy, 8 if k % 2 else 1)
+            rc, got = inflate_dev(comp, len(data), shift=k % 4)
+            k += 1
+            assert rc == 0 and got == data, (name, level, strategy, rc)
+
+
+def test_device_decoder_source_on_bam_blocks_and_damage(inflate_dev, tmp_path):
+    from somatic_sniper_b200 import cli_tools
+    fast = cli_tools.make_pair_fast(str(tmp_path / "fast"), [("chr1", 150000)], 30, 15, seed=4, level=6)
+    raw = open(fast["tumor"], "rb").read()
+    at, n, first = 0, 0, None
+    while at < len(raw):
+        xlen = struct.unpack_from("<H", raw, at + 10)[0]
+        bsize = struct.unpack_from("<H", raw, at + 16)[0] + 1
+        comp = raw[at + 12 + xlen:at + bsize - 8]
+        crc, isize = struct.unpack_from("<II", raw, at + bsize - 8)
+        rc, got = inflate_dev(comp, isize, shift=n % 4)
+        assert rc == 0 and zlib.crc32(got) & 0xffffffff == crc
+        if first is None and isize > 30000:
+            first = (comp, isize, got)
+        at += bsize
+        n += 1
+    assert n > 20
+    comp, isize, data = first
+    assert inflate_dev(comp, isize - 1)[0] != 0 and inflate_dev(comp, isize + 1)[0] != 0
+    for cut in (1, 2, 7, len(comp) // 2, len(comp) - 1):
+        assert inflate_dev(comp[:cut], isize)[0] != 0
+    rng = np.random.default_rng(8)
+    for _ in range(200):
+        b = bytearray(comp)
+        for j in rng.integers(0, len(b), int(rng.integers(1, 4))):
+            b[j] ^= 1 << int(rng.integers(0, 8))
+        rc, got = inflate_dev(bytes(b), isize)
+        if rc == 0:
+            assert zlib.decompress(bytes(b), -15) == got
+
+
+# ---- the kernel itself ------------------------------------------------------------------------------------------------
+
+@pytest.mark.gpu
+def test_gpu_inflater_matches_zlib(built, tmp_path):
+    """ssn_inflate_kernel through the lane service: every sample x level x strategy in one batch, whole BAM files block
+    by block, damaged streams refused (flagged for the host) without disturbing their neighbours."""
+    from somatic_sniper_b200 import api, cli_tools
+    inf = api.Inflater(n_lanes=2, in_cap=8 << 20, out_cap=24 << 20, max_blocks=512)
+    try:
+        payloads, want = [], []
+        for name in sorted(SAMPLES):
+            for level in (0, 1, 6, 9):
+                for strategy in (zlib.Z_DEFAULT_STRATEGY, zlib.Z_FIXED, zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE):
+                    payloads.append(_deflate(SAMPLES[name], level, strategy))
+                    want.append(SAMPLES[name])
+        got = inf.inflate_many(payloads, [len(w) for w in want])
+        assert all(g == w for g, w in zip(got, want)), [i for i, (g, w) in enumerate(zip(got, want)) if g != w][:5]
+        fast = cli_tools.make_pair_fast(str(tmp_path), [("chr1", 1500000)], 60, 30, seed=4, level=6)
+        for path in (fast["tumor"], fast["normal"]):
+            raw = open(path, "rb").read()
+            at, pl, sz, crc = 0, [], [], []
+            while at < len(raw):
+                xlen = struct.unpack_from("<H", raw, at + 10)[0]
+                bsize = struct.unpack_from("<H", raw, at + 16)[0] + 1
+                c, n = struct.unpack_from("<II", raw, at + bsize - 8)
+                if n:
+                    pl.append(raw[at + 12 + xlen:at + bsize - 8]); sz.append(n); crc.append(c)
+                at += bsize
+            got = inf.inflate_many(pl, sz)
+            assert len(got) > 500 and all(g is not None and zlib.crc32(g) & 0xffffffff == c for g, c in zip(got, crc))
+        # damage: flipped bits, truncation, wrong sizes -- refused or (rarely) still a valid stream; neighbours untouched
+        rng = np.random.default_rng(3)
+        good = _deflate(SAMPLES["mixed"], 6)
+        batch, sizes, kind = [], [], []
+        for k in range(120):
+            b = bytearray(good)
+            if k % 3 == 0:
+                for j in rng.integers(0, len(b), 2):
+                    b[j] ^= 1 << int(rng.integers(0, 8))
+                batch.append(bytes(b)); sizes.append(len(SAMPLES["mixed"])); kind.append("flip")
+            elif k % 3 == 1:
+                batch.append(bytes(b[:int(rng.integers(1, len(b) - 1))])); sizes.append(len(SAMPLES["mixed"])); kind.append("cut")
+            else:
+                batch.append(good); sizes.append(len(SAMPLES["mixed"])); kind.append("good")
+        got = inf.inflate_many(batch, sizes)
+        for g, c, k in zip(got, batch, kind):
+            if k == "good":
+                assert g == SAMPLES["mixed"]
+            elif k == "cut":
+                assert g is None
+            elif g is not None:
+                assert zlib.decompress(c, -15) == g
+    finally:
+        inf.close()
