@@ -71,6 +71,18 @@ const char *ssn_host_last_error(void);
 void ssn_packer_one_window(ssn_packer *p, int on);
 int ssn_packer_partial(const ssn_packer *p);
 
+/* ---- inflate service -----------------------------------------------------------------------------------------------
+ * libssn_host.so has no CUDA dependency; a caller that owns GPUs hands the readers an inflate service (the CLI wraps
+ * ssn_inflater_* of include/ssn.h).  A reader takes a lane when it starts, lays the deflate payloads of up to max_blocks
+ * BGZF blocks into the lane's input buffer, calls run (blocking; refused[i] != 0: inflate block i on the host) and
+ * frames records straight from the lane's output buffer.  Without a service the readers inflate on the host. */
+typedef struct {
+    void *ctx;
+    int32_t (*lane_acquire)(void *ctx, uint8_t **in, uint64_t *in_cap, uint8_t **out, uint64_t *out_cap, uint32_t *max_blocks);  /* < 0: none */
+    void (*lane_release)(void *ctx, int32_t lane);
+    int (*run)(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes, uint64_t out_bytes, uint8_t *refused);  /* 0 ok */
+} ssn_inflate_service;
+
 /* ---- region shards: the genome cut into contiguous intervals, one packer each ---------------------
  * Replaces the single front-to-back walk of bam_sspileup_file (src/lib/sniper/sniper_pileup.c:226-266) by many walks
  * over disjoint intervals whose union yields exactly the columns of the one walk: interval edges are multiples of the
@@ -103,6 +115,8 @@ ssn_status ssn_shardset_done(ssn_shardset *s, int32_t index);
 /* 1: a read longer than the look-back crossed an interval edge, so a later interval missed it: the results are
  * incomplete and the caller must run the pair again with opts.serial = 1 (checked after the last ssn_shardset_done) */
 int ssn_shardset_long_span(const ssn_shardset *s);
+/* readers of intervals opened from now on inflate through the service (NULL: on the host); *svc must outlive the set */
+void ssn_shardset_set_inflate_service(ssn_shardset *s, const ssn_inflate_service *svc);
 void ssn_shardset_get_stats(const ssn_shardset *s, ssn_packer_stats *out);
 
 /* ---- writers: one passing site -> one line, byte-identical to the reference ---------------------------

@@ -261,6 +261,7 @@ static int range_start(ssn_bamreader *r, int32_t *max_tid, uint32_t *prev_beg)
     }
     r->z = ssn_bgzf_open_at(ssn_bamfile_path(r->bf), r->pool, pt.voff >> 16);
     if (!r->z) return -1;
+    if (g->inflate_service) ssn_bgzf_use_service(r->z, g->inflate_service);   /* no lane to be had: stays on the host */
     if ((pt.voff & 0xffff) && !stream_take(r, (size_t)(pt.voff & 0xffff))) return 0;
     return 1;
 }

@@ -68,6 +68,7 @@ typedef struct {
     int32_t hi_tid; uint32_t hi_pos;
     uint32_t lookback;
     size_t queue_max_bytes;        /* 0: default back-pressure limit */
+    const void *inflate_service;   /* ssn_inflate_service* (include/ssn_host.h) or NULL: inflate on the host */
 } ssn_bam_range;
 ssn_bamreader *ssn_bamreader_open_range(const struct ssn_bamfile *bf, const ssn_bam_range *range, int flag_mask, int mapq_thresh,
                                         ssn_pool *pool, void (*on_finish)(void*), void *on_finish_arg, char *err, size_t errlen);

@@ -1,4 +1,5 @@
 #include "ssn_bgzf.h"
+#include "ssn_host.h"
 #include "ssn_inflate.h"
 
 #include <errno.h>
@@ -14,7 +15,7 @@
 
 typedef struct {
     const uint8_t *cdata;
-    uint32_t clen, ulen;
+    uint32_t clen, ulen, total;
     size_t uoff;
     int bad;
 } blk;
@@ -32,6 +33,14 @@ struct ssn_bgzf {
      * (region shards: many readers, one core each — the inflated bytes are framed while they are still in the cache) */
     int max_blocks;
     size_t raw_cap;
+    /* inflate service (GPU): the lane's pinned buffers replace `out` */
+    const ssn_inflate_service *svc;
+    int32_t lane;
+    uint8_t *lane_in, *lane_out;
+    uint64_t lane_in_cap, lane_out_cap;
+    uint32_t lane_max_blocks;
+    ssn_inflate_block *lane_blk;
+    uint8_t *lane_refused;
     int use_zlib;               /* SSN_ZLIB_INFLATE: every block through zlib (measurement / fall-back knob) */
 };
 
@@ -64,9 +73,40 @@ ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff)
     return z;
 }
 
+int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
+{
+    const ssn_inflate_service *svc = (const ssn_inflate_service*)svc_;
+    uint8_t *raw;
+    if (!z || !svc || z->svc) return 0;
+    z->lane = svc->lane_acquire(svc->ctx, &z->lane_in, &z->lane_in_cap, &z->lane_out, &z->lane_out_cap, &z->lane_max_blocks);
+    if (z->lane < 0) return 0;
+    if (z->lane_max_blocks > MAX_BLOCKS) z->lane_max_blocks = MAX_BLOCKS;
+    if (z->lane_max_blocks > z->lane_in_cap / 65600u) z->lane_max_blocks = (uint32_t)(z->lane_in_cap / 65600u);      /* a block is at most 64 KiB either way */
+    if (z->lane_max_blocks > z->lane_out_cap / 65536u) z->lane_max_blocks = (uint32_t)(z->lane_out_cap / 65536u);
+    if (z->lane_max_blocks == 0) { svc->lane_release(svc->ctx, z->lane); return 0; }
+    z->lane_blk = (ssn_inflate_block*)malloc(sizeof(ssn_inflate_block) * z->lane_max_blocks);
+    z->lane_refused = (uint8_t*)malloc(z->lane_max_blocks);
+    /* the compressed side of a whole batch has to be resident: grow the read buffer (what is buffered so far moves along) */
+    raw = (uint8_t*)calloc(1, RAW_CAP + SSN_INFLATE_SLACK);
+    if (!z->lane_blk || !z->lane_refused || !raw) {
+        free(z->lane_blk); free(z->lane_refused); free(raw); z->lane_blk = 0; z->lane_refused = 0;
+        svc->lane_release(svc->ctx, z->lane);
+        return 0;
+    }
+    memcpy(raw, z->raw + z->raw_pos, z->raw_len - z->raw_pos);
+    z->raw_len -= z->raw_pos; z->raw_pos = 0;
+    free(z->raw);
+    z->raw = raw; z->raw_cap = RAW_CAP;
+    z->max_blocks = (int)z->lane_max_blocks;
+    z->svc = svc;
+    return 1;
+}
+
 void ssn_bgzf_close(ssn_bgzf *z)
 {
     if (!z) return;
+    if (z->svc) z->svc->lane_release(z->svc->ctx, z->lane);
+    free(z->lane_blk); free(z->lane_refused);
     if (z->own_fd && z->fd >= 0) close(z->fd);
     free(z->raw); free(z->out); free(z);
 }
@@ -108,6 +148,7 @@ static int parse_block(const uint8_t *p, size_t avail, blk *b)
     b->clen = total - 12 - xlen - 8;
     b->ulen = p[total - 4] | (uint32_t)p[total - 3] << 8 | (uint32_t)p[total - 2] << 16 | (uint32_t)p[total - 1] << 24;
     b->bad = 0;
+    b->total = total;
     return (int)total;
 }
 
@@ -166,6 +207,42 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
     if (stop) z->done = 1;
     if (n == 0) return 0;
     a.z = z;
+    if (z->svc) {
+        /* payloads back to back into the lane's input buffer (max_blocks was chosen so that any batch fits) */
+        uint64_t in_bytes = 0;
+        int k;
+        for (k = 0; k < n; ++k) {
+            memcpy(z->lane_in + in_bytes, z->blocks[k].cdata, z->blocks[k].clen);
+            z->lane_blk[k].in_off = (uint32_t)in_bytes; z->lane_blk[k].in_len = z->blocks[k].clen;
+            z->lane_blk[k].out_off = (uint32_t)z->blocks[k].uoff; z->lane_blk[k].out_len = z->blocks[k].ulen;
+            in_bytes += z->blocks[k].clen;
+        }
+        if (z->svc->run(z->svc->ctx, z->lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused) != 0) memset(z->lane_refused, 1, (size_t)(unsigned)n);
+        for (k = 0; k < n; ++k) {
+            if (z->lane_refused[k]) {                            /* on the host, the way the reference reads it */
+                blk *b = &z->blocks[k];
+                int st;
+                if (ssn_inflate_raw(b->cdata, b->clen, z->lane_out + b->uoff, b->ulen) == 0) continue;
+                if (!t_zs_ready) { memset(&t_zs, 0, sizeof(t_zs)); if (inflateInit2(&t_zs, -15) != Z_OK) { b->bad = 1; continue; } t_zs_ready = 1; }
+                else inflateReset(&t_zs);
+                t_zs.next_in = (Bytef*)b->cdata; t_zs.avail_in = b->clen;
+                t_zs.next_out = z->lane_out + b->uoff; t_zs.avail_out = b->ulen;
+                st = inflate(&t_zs, Z_FINISH);
+                if (st != Z_STREAM_END || t_zs.avail_out != 0) b->bad = 1;
+            }
+        }
+        for (i = 0; i < n; ++i) {
+            if (z->blocks[i].bad) {
+                fprintf(stderr, "[ssn_bgzf] inflate failed\n");
+                z->done = 1;
+                uoff = z->blocks[i].uoff;
+                break;
+            }
+        }
+        if (uoff == 0) return 0;
+        *data = z->lane_out; *len = uoff;
+        return 1;
+    }
     ssn_pool_for(z->pool, n, inflate_one, &a);
     for (i = 0; i < n; ++i) {
         if (z->blocks[i].bad) {

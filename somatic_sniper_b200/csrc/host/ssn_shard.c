@@ -40,7 +40,8 @@ struct ssn_shardset {
     int min_mapq;
     shard *sh;
     int32_t n, next_open, next_claim, n_done;
-    int reading, max_reading, max_open;
+    int reading, max_reading, max_open, max_reading_user;
+    const ssn_inflate_service *svc;   /* readers of intervals opened from now on inflate through it */
     int started;                   /* a caller has asked for a shard: until then only two intervals are read ahead, so that the
                                     * readers do not crowd out the caller's own set-up (GPU contexts) */
     int long_span, failed;
@@ -68,6 +69,7 @@ static void open_more(ssn_shardset *set)
         ssn_packer *pk;
         char err[256] = "";
         s->state = SH_OPENING; s->readers_left = 2; set->reading += 1;
+        s->rg.inflate_service = set->svc;
         pthread_mutex_unlock(&set->mu);
         pk = ssn_packer_create_shard(set->pool, 0, set->rc, set->bf[0], set->bf[1], &s->rg, set->min_mapq, reader_finished, s, err, sizeof(err));
         pthread_mutex_lock(&set->mu);
@@ -119,6 +121,7 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
         uint64_t genome = 0, stride, next_cut, g = 0;
         int32_t t, cap = 16, n = 0;
         ssn_bam_range *cuts;
+        set->max_reading_user = o.max_reading;
         if (!o.max_reading) o.max_reading = o.n_threads >= 3 ? (2 * o.n_threads + 2) / 3 : 1;
         if (o.max_reading > 48) o.max_reading = 48;              /* two threads and up to ~75 MB of finished windows each */
         if (!o.max_open) o.max_open = o.max_reading + (o.max_reading < 8 ? o.max_reading + 2 : 8);
@@ -288,6 +291,19 @@ ssn_status ssn_shardset_done(ssn_shardset *set, int32_t index)
 }
 
 int ssn_shardset_long_span(const ssn_shardset *set) { return set ? set->long_span : 0; }
+
+void ssn_shardset_set_inflate_service(ssn_shardset *set, const ssn_inflate_service *svc)
+{
+    if (!set) return;
+    pthread_mutex_lock(&set->mu);
+    set->svc = svc;
+    /* with the inflating off the cores a reader mostly waits: more of them may run at once */
+    if (svc && !set->serial && set->max_reading_user == 0) {
+        set->max_reading = set->max_reading * 2 > 48 ? 48 : set->max_reading * 2;
+        if (set->max_open < set->max_reading + 8) set->max_open = set->max_reading + 8;
+    }
+    pthread_mutex_unlock(&set->mu);
+}
 
 void ssn_shardset_get_stats(const ssn_shardset *set, ssn_packer_stats *out)
 {

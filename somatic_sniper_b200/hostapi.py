@@ -27,7 +27,7 @@ class ShardOpts(C.Structure):
 
 
 HOST_SYMBOLS = ["ssn_shardset_open", "ssn_shardset_close", "ssn_shardset_n_shards", "ssn_shardset_n_targets", "ssn_shardset_target_name",
-                "ssn_shardset_range", "ssn_shardset_next", "ssn_shardset_done", "ssn_shardset_long_span", "ssn_shardset_get_stats",
+                "ssn_shardset_range", "ssn_shardset_next", "ssn_shardset_done", "ssn_shardset_long_span", "ssn_shardset_get_stats", "ssn_shardset_set_inflate_service",
                 "ssn_packer_one_window", "ssn_packer_partial", "ssn_packer_open", "ssn_packer_close", "ssn_packer_n_targets", "ssn_packer_target_name", "ssn_packer_next",
                 "ssn_packer_get_stats", "ssn_pack_read_windows", "ssn_packer_next_reads", "ssn_host_last_error", "ssn_writer_create", "ssn_writer_header", "ssn_writer_site",
                 "ssn_writer_destroy", "ssn_writer_n_formats", "ssn_writer_format_name"]

@@ -335,3 +335,79 @@ def test_several_consumers_take_distinct_shards(host, big_pair):
         return got
     one, four = run(1), run(4)
     assert one == four and sum(c for c, _ in one.values()) > 100000
+
+
+def test_readers_through_an_inflate_service(host, big_pair):
+    """The readers' GPU-inflate plumbing without a GPU: a service whose `run` decodes every block with the DEVICE decoder's
+    source compiled for the host (ssn_inflate_dev_host) and refuses every seventh block (the reader must then inflate that
+    one itself).  Lanes are handed out and given back; the columns equal the host-inflate run's."""
+    import threading
+    from somatic_sniper_b200 import api
+    p = big_pair
+    dev = api.load_library()
+    dev.ssn_inflate_dev_host_shift.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32]
+    dev.ssn_inflate_dev_host_shift.restype = C.c_int
+    lib = host.load_library()
+
+    class Block(C.Structure):
+        _fields_ = [("in_off", C.c_uint32), ("in_len", C.c_uint32), ("out_off", C.c_uint32), ("out_len", C.c_uint32)]
+
+    ACQ = C.CFUNCTYPE(C.c_int32, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32))
+    REL = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
+    RUN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(Block), C.c_uint32, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint8))
+
+    class Service(C.Structure):
+        _fields_ = [("ctx", C.c_void_p), ("lane_acquire", ACQ), ("lane_release", REL), ("run", RUN)]
+
+    MAXB, lock = 24, threading.Lock()
+    lanes = [dict(busy=False, i=np.zeros(MAXB * 65600 + 64, np.uint8), o=np.zeros(MAXB * 65536 + 64, np.uint8)) for _ in range(8)]
+    stats = dict(acquired=0, released=0, blocks=0, refused=0, none_free=0)
+
+    def acquire(ctx, pin, pin_cap, pout, pout_cap, pmax):
+        with lock:
+            for k, L in enumerate(lanes):
+                if not L["busy"]:
+                    L["busy"] = True
+                    stats["acquired"] += 1
+                    pin[0] = L["i"].ctypes.data; pin_cap[0] = MAXB * 65600
+                    pout[0] = L["o"].ctypes.data; pout_cap[0] = MAXB * 65536
+                    pmax[0] = MAXB
+                    return k
+            stats["none_free"] += 1
+            return -1
+
+    def release(ctx, k):
+        with lock:
+            lanes[k]["busy"] = False
+            stats["released"] += 1
+
+    def run(ctx, k, blk, n, in_bytes, out_bytes, refused):
+        L = lanes[k]
+        for j in range(n):
+            b = blk[j]
+            with lock:
+                stats["blocks"] += 1
+                nth = stats["blocks"]
+            if nth % 7 == 0:
+                refused[j] = 1
+                with lock:
+                    stats["refused"] += 1
+                continue
+            rc = dev.ssn_inflate_dev_host_shift(L["i"].ctypes.data + b.in_off, b.in_len, L["o"].ctypes.data + b.out_off, b.out_len, 0)
+            refused[j] = 1 if rc else 0
+        return 0
+
+    svc = Service(None, ACQ(acquire), REL(release), RUN(run))
+    lib.ssn_shardset_set_inflate_service.argtypes = [C.c_void_p, C.POINTER(Service)]
+    lib.ssn_shardset_set_inflate_service.restype = None
+    ss = host.ShardSet(p["tumor"], p["normal"], p["fasta"], 0, threads=4, stride_windows=2, lookback_windows=1, max_reading=3, max_open=4,
+                       max_columns=5000, max_entries=300000)
+    lib.ssn_shardset_set_inflate_service(ss.h, C.byref(svc))
+    got = _packed_columns(list(ss))
+    assert not ss.long_span()
+    ss.close()
+    pk = host.Packer(p["tumor"], p["normal"], p["fasta"], 0, threads=2)
+    want = _packed_columns(list(pk))
+    pk.close()
+    assert got == want
+    assert stats["blocks"] > 200 and stats["refused"] > 20 and stats["acquired"] == stats["released"] > 10
