@@ -18,6 +18,8 @@
  *   SSN_THREADS  host threads to plan for: readers, inflate, packing (default: online cores - 2, at least 1)
  *   SSN_SLOTS    batches in flight per GPU (default 3)
  *   SSN_DEVICE_PILEUP  1 (default): ship the filtered reads, build the columns on the GPU; 0: pack columns on the host
+ *   SSN_GPU_INFLATE  1 (default): the readers hand BGZF blocks to the GPU(s) to inflate (ssn_inflater_*, one warp per
+ *                block) and only frame the records; 0: inflate on the host cores
  *   SSN_SERIAL   1: one interval, front to back (what a pair that cannot be cut gets anyway)
  *   SSN_SHARD_WINDOWS / SSN_SHARD_LOOKBACK / SSN_SHARD_READERS  interval length and look-back in windows of 8192
  *                positions, intervals read at once (ssn_host.h)
@@ -384,6 +386,34 @@ static void *gpu_main(void *arg)
     return 0;
 }
 
+/* ---- the readers' inflate service: lanes of one ssn_inflater per GPU, handed out round robin ---------------------- */
+#define INFL_BLOCKS 96u
+typedef struct {
+    ssn_inflater *inf[MAX_GPUS];
+    int n;
+    unsigned next;
+} infl_ctx;
+
+static int32_t svc_acquire(void *ctx, uint8_t **in, uint64_t *in_cap, uint8_t **out, uint64_t *out_cap, uint32_t *max_blocks)
+{
+    infl_ctx *c = (infl_ctx*)ctx;
+    const int g = (int)(__atomic_fetch_add(&c->next, 1u, __ATOMIC_RELAXED) % (unsigned)c->n);
+    int32_t lane = -1;
+    if (ssn_inflater_lane_acquire(c->inf[g], &lane, in, out) != SSN_OK) return -1;
+    ssn_inflater_limits(c->inf[g], in_cap, out_cap, max_blocks);
+    return g * 4096 + lane;
+}
+static void svc_release(void *ctx, int32_t lane)
+{
+    infl_ctx *c = (infl_ctx*)ctx;
+    ssn_inflater_lane_release(c->inf[lane / 4096], lane % 4096);
+}
+static int svc_run(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes, uint64_t out_bytes, uint8_t *refused)
+{
+    infl_ctx *c = (infl_ctx*)ctx;
+    return ssn_inflater_run(c->inf[lane / 4096], lane % 4096, blk, n, in_bytes, out_bytes, refused) == SSN_OK ? 0 : -1;
+}
+
 static int start_feeders(run_t *R)
 {
     int i;
@@ -476,6 +506,10 @@ int main(int argc, char *argv[])
     int c, use_priors = 1, mapq = 0, i, rc = 0, passes = 1;
     const char *normal_id = default_normal_id, *tumor_id = default_tumor_id, *fn_fa = 0, *format = default_format;
     static run_t R;
+    static infl_ctx infl;
+    static ssn_inflate_service svc;
+    int gpu_inflate = 0;
+    uint64_t infl_blocks = 0, infl_refused = 0;
     ssn_writer *wr;
     FILE *out;
     ssn_packer_stats st;
@@ -593,6 +627,19 @@ int main(int argc, char *argv[])
         exit(1);
     }
     ssn_writer_header(wr, fn_fa, normal_id, tumor_id);
+    if (env_int("SSN_GPU_INFLATE", 1, 0, 1) && ssn_shardset_n_shards(R.set) > 1) {
+        /* lanes are cheap until used (their pinned buffers are allocated by the reader that first takes them) */
+        const uint32_t lanes = (uint32_t)(2 * 48 + 16) / (uint32_t)R.n_gpus + 4u;
+        int ok = 1;
+        for (i = 0; i < R.n_gpus && ok; ++i)
+            ok = ssn_inflater_create(R.gpus[i].device, lanes, (uint64_t)INFL_BLOCKS * 65600u, (uint64_t)INFL_BLOCKS * 65536u, INFL_BLOCKS, &infl.inf[i]) == SSN_OK;
+        if (ok) {
+            infl.n = R.n_gpus;
+            svc.ctx = &infl; svc.lane_acquire = svc_acquire; svc.lane_release = svc_release; svc.run = svc_run;
+            ssn_shardset_set_inflate_service(R.set, &svc);
+            gpu_inflate = 1;
+        } else fprintf(stderr, "[bam-somaticsniper] no GPU inflate (%s); the readers inflate on the host\n", ssn_last_error());
+    }
     t_setup = now_s() - t_start;
 
     rc = stream_pass(&R, out);
@@ -614,6 +661,10 @@ int main(int argc, char *argv[])
         if (rc == 2) rc = 1;
     }
     fflush(out);
+    for (i = 0; i < infl.n; ++i) {
+        uint64_t b = 0, r = 0;
+        if (ssn_inflater_stats(infl.inf[i], &b, &r, 0, 0, 0) == SSN_OK) { infl_blocks += b; infl_refused += r; }
+    }
     {
         const char *sp = getenv("SSN_STATS");
         if (sp && *sp) {
@@ -635,18 +686,19 @@ int main(int argc, char *argv[])
                         "\"records_normal\": %llu, \"wall_s\": %.6f, \"setup_s\": %.6f, \"gpu_setup_s\": %.6f, \"pack_wait_s\": %.6f, \"pack_count_s\": %.6f, "
                         "\"pack_fill_s\": %.6f, \"gpu_wait_s\": %.6f, \"gpus\": %d, \"threads\": %d, \"slots\": %d, \"kernel_launches\": %llu, "
                         "\"prefilter\": %d, \"prefilter_survivors\": %llu, \"device_pileup\": %d, \"column_route_batches\": %llu, \"shards\": %d, "
-                        "\"passes\": %d, \"columns_per_s\": %.1f}\n",
+                        "\"passes\": %d, \"gpu_inflate\": %d, \"gpu_inflate_blocks\": %llu, \"gpu_inflate_refused\": %llu, \"columns_per_s\": %.1f}\n",
                         (unsigned long long)st.columns, (unsigned long long)st.entries, (unsigned long long)n_batches,
                         (unsigned long long)n_sites, (unsigned long long)st.records[0], (unsigned long long)st.records[1], wall, t_setup, t_ctx,
                         st.t_wait, st.t_count, st.t_fill, t_gpu_wait, R.n_gpus, R.n_threads, R.n_slots, (unsigned long long)launches,
                         R.gpus[0].ctx ? ssn_prefilter_enabled(R.gpus[0].ctx) : 0, (unsigned long long)survivors, R.device_pileup,
-                        (unsigned long long)colb, (int)n_shards_first, passes, wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
+                        (unsigned long long)colb, (int)n_shards_first, passes, gpu_inflate, (unsigned long long)infl_blocks, (unsigned long long)infl_refused, wall > t_setup ? (double)st.columns / (wall - t_setup) : 0.0);
                 fclose(sf);
             }
         }
     }
     free_outs(&R);
-    ssn_shardset_close(R.set);
+    ssn_shardset_close(R.set);                      /* joins the readers: their lanes are back */
+    for (i = 0; i < infl.n; ++i) ssn_inflater_destroy(infl.inf[i]);
     for (i = 0; i < R.n_gpus; ++i) {
         int k;
         gpu_t *g = &R.gpus[i];

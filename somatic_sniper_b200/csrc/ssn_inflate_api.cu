@@ -57,6 +57,7 @@ struct Lane {
     ssn_inflate_block *h_blk = nullptr, *d_blk = nullptr;
     uint32_t *h_status = nullptr, *d_status = nullptr, *d_counter = nullptr;
     cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;          /* blocking-sync: a waiting reader sleeps, its core goes to another reader */
 };
 
 struct ssn_inflater {
@@ -89,6 +90,7 @@ static void lane_free(Lane &L)
 {
     cudaFreeHost(L.h_in); cudaFreeHost(L.h_out); cudaFreeHost(L.h_blk); cudaFreeHost(L.h_status);
     cudaFree(L.d_in); cudaFree(L.d_out); cudaFree(L.d_blk); cudaFree(L.d_status); cudaFree(L.d_counter);
+    if (L.done) cudaEventDestroy(L.done);
     if (L.stream) cudaStreamDestroy(L.stream);
     L = Lane();
 }
@@ -116,6 +118,7 @@ static ssn_status lane_prepare(ssn_inflater *f, Lane &L)
     CUI(cudaMalloc(&L.d_status, 4 * (size_t)f->max_blocks));
     CUI(cudaMalloc(&L.d_counter, 4));
     CUI(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    CUI(cudaEventCreateWithFlags(&L.done, cudaEventBlockingSync | cudaEventDisableTiming));
     memset(L.h_in, 0, f->in_cap + 64);
     L.ready = true;
     return SSN_OK;
@@ -184,7 +187,8 @@ extern "C" ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_
     CUI(cudaGetLastError());
     CUI(cudaMemcpyAsync(L.h_out, L.d_out, (size_t)out_bytes, cudaMemcpyDeviceToHost, L.stream));
     CUI(cudaMemcpyAsync(L.h_status, L.d_status, 4 * (size_t)n, cudaMemcpyDeviceToHost, L.stream));
-    CUI(cudaStreamSynchronize(L.stream));
+    CUI(cudaEventRecord(L.done, L.stream));
+    CUI(cudaEventSynchronize(L.done));
     uint32_t bad = 0;
     for (uint32_t i = 0; i < n; ++i) { refused[i] = L.h_status[i] != 0; bad += refused[i]; }
     {

@@ -13,7 +13,8 @@
  * instruction, matches are copied 32 bytes per step, code tables are filled 32 entries per step.
  *
  * The same source compiles for the host (SSN_INFL_HOST: the lane loops become real loops), which is how the CPU tests
- * check the decoder against zlib without a GPU (tests/test_inflate.py through ssn_inflate_dev_host in libssn_host.so).
+ * check the decoder against zlib without a GPU (tests/test_inflate.py through ssn_inflate_dev_host, ssn_inflate_emul.cpp,
+ * in libssn.so; no compute path of the product calls it).
  *
  * Contract: in[] readable up to in_len + 16 bytes; nothing is written outside out[0, out_len).  Returns 0 when the stream
  * decodes to exactly out_len bytes, non-zero otherwise — the caller then inflates that block on the host (zlib reads

@@ -45,6 +45,8 @@ def main():
     ap.add_argument("--reference", choices=["none", "single", "split"], default="single")
     ap.add_argument("--threads", default=None)
     ap.add_argument("--env", default="", help="extra environment for this repo's CLI, e.g. 'SSN_DEVICE_PILEUP=0 SSN_SLOTS=4'")
+    ap.add_argument("--variants", default="", help="';'-separated environments run one after the other on the same pair, "
+                    "e.g. 'SSN_GPU_INFLATE=0;SSN_GPU_INFLATE=1'; every output is compared with the first")
     ap.add_argument("--workdir", default=None)
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
@@ -73,28 +75,37 @@ def main():
                reads=[pair["reads_tumor"], pair["reads_normal"]], bam_bytes=[os.path.getsize(pair["tumor"]), os.path.getsize(pair["normal"])],
                simulate_s=t_sim, host_cores=os.cpu_count(), runs={})
     mine = os.path.join(w, "mine.out")
-    for g in [int(x) for x in a.gpus.split(",")]:
-        runs = []
-        for i in range(a.repeat):
-            e = dict(env)
-            e["SSN_GPUS"] = g
-            for attempt in range(3):
-                r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], mine + ".%d" % g, opts, env=e, stats=os.path.join(w, "stats.json"))
-                if r["rc"] == 0:
-                    break
-                res.setdefault("failed_runs", []).append(dict(gpus=g, rc=r["rc"], stderr=r["stderr"][-4000:]))
-                print("run failed rc=%s\n%s" % (r["rc"], r["stderr"][-4000:]), file=sys.stderr, flush=True)
-            assert r["rc"] == 0, "rc=%s\n%s" % (r["rc"], r["stderr"][-2000:])
-            runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
-        best = min(runs, key=lambda x: x["wall_s"])
-        st = best["stats"]
-        res["runs"]["gpus_%d" % g] = dict(wall_s=best["wall_s"], setup_s=st["setup_s"], stream_s=st["wall_s"] - st["setup_s"], columns=st["columns"],
-                                          columns_per_s_stream=st["columns_per_s"], columns_per_s_wall=st["columns"] / best["wall_s"],
-                                          all_walls=[x["wall_s"] for x in runs], stats=st)
-        if g != int(a.gpus.split(",")[0]):
-            res["runs"]["gpus_%d" % g]["identical_to_first_gpu_count"] = ct.comparable(mine + ".%d" % g) == ct.comparable(mine + ".%s" % a.gpus.split(",")[0])
-    first = mine + ".%s" % a.gpus.split(",")[0]
-    ncols = res["runs"]["gpus_%s" % a.gpus.split(",")[0]]["columns"]
+    first = first_key = None
+    for variant in a.variants.split(";") if a.variants else [""]:
+        venv = dict(env)
+        for kv in variant.split():
+            k, v = kv.split("=", 1)
+            venv[k] = v
+        for g in [int(x) for x in a.gpus.split(",")]:
+            key = "gpus_%d" % g + ("|" + variant if variant else "")
+            o = mine + ".%d" % len(res["runs"])
+            runs = []
+            for i in range(a.repeat):
+                e = dict(venv)
+                e["SSN_GPUS"] = g
+                for attempt in range(3):
+                    r = ct.run_cli(ct.CLI, pair["fasta"], pair["tumor"], pair["normal"], o, opts, env=e, stats=os.path.join(w, "stats.json"))
+                    if r["rc"] == 0:
+                        break
+                    res.setdefault("failed_runs", []).append(dict(run=key, rc=r["rc"], stderr=r["stderr"][-4000:]))
+                    print("run failed rc=%s\n%s" % (r["rc"], r["stderr"][-4000:]), file=sys.stderr, flush=True)
+                assert r["rc"] == 0, "rc=%s\n%s" % (r["rc"], r["stderr"][-2000:])
+                runs.append(dict(wall_s=r["wall_s"], stats=r["stats"]))
+            best = min(runs, key=lambda x: x["wall_s"])
+            st = best["stats"]
+            res["runs"][key] = dict(wall_s=best["wall_s"], setup_s=st["setup_s"], stream_s=st["wall_s"] - st["setup_s"], columns=st["columns"],
+                                    columns_per_s_stream=st["columns_per_s"], columns_per_s_wall=st["columns"] / best["wall_s"],
+                                    all_walls=[x["wall_s"] for x in runs], all_stream_columns_per_s=[x["stats"]["columns_per_s"] for x in runs], stats=st)
+            if first is None:
+                first, first_key = o, key
+            else:
+                res["runs"][key]["identical_to_first_run"] = ct.comparable(o) == ct.comparable(first)
+    ncols = res["runs"][first_key]["columns"]
     if a.reference == "single" and ct.reference_available():
         ref = os.path.join(w, "ref.out")
         r = ct.run_cli(ct.REF_CLI, pair["fasta"], pair["tumor"], pair["normal"], ref, opts)
@@ -129,7 +140,7 @@ def main():
         res["output_lines"] = len(a_)
         res["lines_in_b1_zones"] = [sum(1 for _ in open(ref, "rb")) - len(a_), sum(1 for _ in open(first, "rb")) - len(b_)]
     if "reference" in res:
-        g0 = res["runs"]["gpus_%s" % a.gpus.split(",")[0]]
+        g0 = res["runs"][first_key]
         res["speedup_wall"] = res["reference"]["wall_s"] / g0["wall_s"]
     print(json.dumps(res), flush=True)
     if a.out:
