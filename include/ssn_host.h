@@ -73,9 +73,11 @@ int ssn_packer_partial(const ssn_packer *p);
 
 /* ---- inflate service -----------------------------------------------------------------------------------------------
  * libssn_host.so has no CUDA dependency; a caller that owns GPUs hands the readers an inflate service (the CLI wraps
- * ssn_inflater_* of include/ssn.h).  A reader takes a lane when it starts, lays the deflate payloads of up to max_blocks
- * BGZF blocks into the lane's input buffer, calls run (blocking; refused[i] != 0: inflate block i on the host) and
- * frames records straight from the lane's output buffer.  Without a service the readers inflate on the host. */
+ * ssn_inflater_* of include/ssn.h).  Per batch of BGZF blocks a reader takes a lane (lane_acquire may block until one is
+ * free: the number of lanes is the number of batches in flight), lays the deflate payloads of up to max_blocks blocks /
+ * in_cap bytes into the lane's input buffer, calls run (blocking; refused[i] != 0: inflate block i on the host), copies
+ * the inflated bytes out of the lane's output buffer and gives the lane back — a reader held up by its queue holds no
+ * lane.  All lanes of a service have the same capacities.  Without a service the readers inflate on the host. */
 typedef struct {
     void *ctx;
     int32_t (*lane_acquire)(void *ctx, uint8_t **in, uint64_t *in_cap, uint8_t **out, uint64_t *out_cap, uint32_t *max_blocks);  /* < 0: none */

@@ -33,12 +33,9 @@ struct ssn_bgzf {
      * (region shards: many readers, one core each — the inflated bytes are framed while they are still in the cache) */
     int max_blocks;
     size_t raw_cap;
-    /* inflate service (GPU): the lane's pinned buffers replace `out` */
+    /* inflate service (GPU): a lane (pinned in / out) is taken per batch; the inflated bytes are copied into `out` */
     const ssn_inflate_service *svc;
-    int32_t lane;
-    uint8_t *lane_in, *lane_out;
-    uint64_t lane_in_cap, lane_out_cap;
-    uint32_t lane_max_blocks;
+    uint64_t lane_in_cap;
     ssn_inflate_block *lane_blk;
     uint8_t *lane_refused;
     int use_zlib;               /* SSN_ZLIB_INFLATE: every block through zlib (measurement / fall-back knob) */
@@ -76,28 +73,35 @@ ssn_bgzf *ssn_bgzf_open_at(const char *path, ssn_pool *pool, uint64_t coff)
 int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
 {
     const ssn_inflate_service *svc = (const ssn_inflate_service*)svc_;
-    uint8_t *raw;
+    uint8_t *raw, *out, *li, *lo;
+    uint64_t in_cap = 0, out_cap = 0;
+    uint32_t mb = 0;
+    int32_t lane;
     if (!z || !svc || z->svc) return 0;
-    z->lane = svc->lane_acquire(svc->ctx, &z->lane_in, &z->lane_in_cap, &z->lane_out, &z->lane_out_cap, &z->lane_max_blocks);
-    if (z->lane < 0) return 0;
-    if (z->lane_max_blocks > MAX_BLOCKS) z->lane_max_blocks = MAX_BLOCKS;
-    if (z->lane_max_blocks > z->lane_in_cap / 65600u) z->lane_max_blocks = (uint32_t)(z->lane_in_cap / 65600u);      /* a block is at most 64 KiB either way */
-    if (z->lane_max_blocks > z->lane_out_cap / 65536u) z->lane_max_blocks = (uint32_t)(z->lane_out_cap / 65536u);
-    if (z->lane_max_blocks == 0) { svc->lane_release(svc->ctx, z->lane); return 0; }
-    z->lane_blk = (ssn_inflate_block*)malloc(sizeof(ssn_inflate_block) * z->lane_max_blocks);
-    z->lane_refused = (uint8_t*)malloc(z->lane_max_blocks);
+    /* a lane is held only while a batch is on its way (ssn_bgzf_next); all lanes have the same size: ask once */
+    lane = svc->lane_acquire(svc->ctx, &li, &in_cap, &lo, &out_cap, &mb);
+    if (lane < 0) return 0;
+    svc->lane_release(svc->ctx, lane);
+    if (mb > MAX_BLOCKS) mb = MAX_BLOCKS;
+    if (mb > out_cap / 65536u) mb = (uint32_t)(out_cap / 65536u);                  /* a block inflates to at most 64 KiB */
+    if (in_cap > RAW_CAP) in_cap = RAW_CAP;
+    if (mb == 0 || in_cap < 65600u) return 0;
+    z->lane_blk = (ssn_inflate_block*)malloc(sizeof(ssn_inflate_block) * mb);
+    z->lane_refused = (uint8_t*)malloc(mb);
     /* the compressed side of a whole batch has to be resident: grow the read buffer (what is buffered so far moves along) */
     raw = (uint8_t*)calloc(1, RAW_CAP + SSN_INFLATE_SLACK);
-    if (!z->lane_blk || !z->lane_refused || !raw) {
-        free(z->lane_blk); free(z->lane_refused); free(raw); z->lane_blk = 0; z->lane_refused = 0;
-        svc->lane_release(svc->ctx, z->lane);
+    out = (uint8_t*)malloc((size_t)mb * 65536);
+    if (!z->lane_blk || !z->lane_refused || !raw || !out) {
+        free(z->lane_blk); free(z->lane_refused); free(raw); free(out); z->lane_blk = 0; z->lane_refused = 0;
         return 0;
     }
     memcpy(raw, z->raw + z->raw_pos, z->raw_len - z->raw_pos);
     z->raw_len -= z->raw_pos; z->raw_pos = 0;
-    free(z->raw);
+    free(z->raw); free(z->out);
     z->raw = raw; z->raw_cap = RAW_CAP;
-    z->max_blocks = (int)z->lane_max_blocks;
+    z->out = out; z->out_cap = (size_t)mb * 65536;
+    z->max_blocks = (int)mb;
+    z->lane_in_cap = in_cap;
     z->svc = svc;
     return 1;
 }
@@ -105,7 +109,6 @@ int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
 void ssn_bgzf_close(ssn_bgzf *z)
 {
     if (!z) return;
-    if (z->svc) z->svc->lane_release(z->svc->ctx, z->lane);
     free(z->lane_blk); free(z->lane_refused);
     if (z->own_fd && z->fd >= 0) close(z->fd);
     free(z->raw); free(z->out); free(z);
@@ -179,6 +182,7 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
 {
     int n = 0, i, stop = 0;
     size_t uoff = 0;
+    uint64_t csum = 0;
     inflate_arg a;
     *data = 0; *len = 0;
     if (z->done) return 0;
@@ -197,6 +201,8 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
             continue;
         }
         if (r < 0) { fprintf(stderr, "[ssn_bgzf] invalid block header\n"); stop = 1; break; }
+        if (z->svc && n > 0 && csum + b->clen > z->lane_in_cap) break;        /* the lane's input buffer is full: next call */
+        csum += b->clen;
         z->raw_pos += (size_t)r;
         z->consumed += (uint64_t)r;
         if (b->ulen == 0) { stop = 1; break; }          /* empty block: the reference's reader stops here */
@@ -208,41 +214,31 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
     if (n == 0) return 0;
     a.z = z;
     if (z->svc) {
-        /* payloads back to back into the lane's input buffer (max_blocks was chosen so that any batch fits) */
-        uint64_t in_bytes = 0;
+        /* A lane for this batch only (so a reader held up by its queue keeps none): payloads back to back into the lane's
+         * pinned input, one run, the inflated bytes into this reader's own buffer, lane back.  What the service refused
+         * is inflated here, the way the reference reads it. */
+        const ssn_inflate_service *svc = z->svc;
+        uint8_t *li = 0, *lo = 0;
+        uint64_t ic = 0, oc = 0, in_bytes = 0;
+        uint32_t mb = 0;
         int k;
-        for (k = 0; k < n; ++k) {
-            memcpy(z->lane_in + in_bytes, z->blocks[k].cdata, z->blocks[k].clen);
-            z->lane_blk[k].in_off = (uint32_t)in_bytes; z->lane_blk[k].in_len = z->blocks[k].clen;
-            z->lane_blk[k].out_off = (uint32_t)z->blocks[k].uoff; z->lane_blk[k].out_len = z->blocks[k].ulen;
-            in_bytes += z->blocks[k].clen;
-        }
-        if (z->svc->run(z->svc->ctx, z->lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused) != 0) memset(z->lane_refused, 1, (size_t)(unsigned)n);
-        for (k = 0; k < n; ++k) {
-            if (z->lane_refused[k]) {                            /* on the host, the way the reference reads it */
-                blk *b = &z->blocks[k];
-                int st;
-                if (ssn_inflate_raw(b->cdata, b->clen, z->lane_out + b->uoff, b->ulen) == 0) continue;
-                if (!t_zs_ready) { memset(&t_zs, 0, sizeof(t_zs)); if (inflateInit2(&t_zs, -15) != Z_OK) { b->bad = 1; continue; } t_zs_ready = 1; }
-                else inflateReset(&t_zs);
-                t_zs.next_in = (Bytef*)b->cdata; t_zs.avail_in = b->clen;
-                t_zs.next_out = z->lane_out + b->uoff; t_zs.avail_out = b->ulen;
-                st = inflate(&t_zs, Z_FINISH);
-                if (st != Z_STREAM_END || t_zs.avail_out != 0) b->bad = 1;
+        const int32_t lane = svc->lane_acquire(svc->ctx, &li, &ic, &lo, &oc, &mb);
+        memset(z->lane_refused, 1, (size_t)(unsigned)n);
+        if (lane >= 0) {
+            if (csum <= ic && uoff <= oc && (uint32_t)n <= mb) {
+                for (k = 0; k < n; ++k) {
+                    memcpy(li + in_bytes, z->blocks[k].cdata, z->blocks[k].clen);
+                    z->lane_blk[k].in_off = (uint32_t)in_bytes; z->lane_blk[k].in_len = z->blocks[k].clen;
+                    z->lane_blk[k].out_off = (uint32_t)z->blocks[k].uoff; z->lane_blk[k].out_len = z->blocks[k].ulen;
+                    in_bytes += z->blocks[k].clen;
+                }
+                if (svc->run(svc->ctx, lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused) == 0) memcpy(z->out, lo, uoff);
+                else memset(z->lane_refused, 1, (size_t)(unsigned)n);
             }
+            svc->lane_release(svc->ctx, lane);
         }
-        for (i = 0; i < n; ++i) {
-            if (z->blocks[i].bad) {
-                fprintf(stderr, "[ssn_bgzf] inflate failed\n");
-                z->done = 1;
-                uoff = z->blocks[i].uoff;
-                break;
-            }
-        }
-        if (uoff == 0) return 0;
-        *data = z->lane_out; *len = uoff;
-        return 1;
-    }
+        for (k = 0; k < n; ++k) if (z->lane_refused[k]) inflate_one(&a, k);
+    } else
     ssn_pool_for(z->pool, n, inflate_one, &a);
     for (i = 0; i < n; ++i) {
         if (z->blocks[i].bad) {

@@ -170,7 +170,12 @@ ssn_status ssn_shardset_open(const char *tumor_bam, const char *normal_bam, cons
             }
             set->max_reading = o.max_reading; set->max_open = o.max_open;
             /* the readers inflate by themselves (one core each); the pool serves the packers' count / fill / copy tasks */
-            set->pool = ssn_pool_create(o.n_threads >= 4 ? o.n_threads / 2 : (o.n_threads >= 2 ? 2 : 0));
+            {
+                const char *pe = getenv("SSN_POOL_THREADS");                  /* copy workers of the packers (measurement knob) */
+                int np = o.n_threads >= 4 ? o.n_threads / 2 : (o.n_threads >= 2 ? 2 : 0);
+                if (pe && *pe && atoi(pe) >= 0 && atoi(pe) <= 256) np = atoi(pe);
+                set->pool = ssn_pool_create(np);
+            }
             set->rc = ssn_refcache_create(fasta, h);
         }
         free(cuts);

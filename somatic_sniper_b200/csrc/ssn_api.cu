@@ -175,7 +175,13 @@ static ssn_status slot_alloc(ssn_ctx *ctx, ssn_batch *b, uint32_t max_columns, u
     CU(cudaMalloc(&b->d_sites, sizeof(ssn_site) * (size_t)b->site_cap));
     b->h_sites_cap = 4096;
     CU(cudaMallocHost(&b->h_sites, sizeof(ssn_site) * (size_t)b->h_sites_cap));
-    CU(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    {
+        /* highest priority: scoring launches go in front of whatever else shares the device (the readers' inflate lanes) */
+        int lo = 0, hi = 0;
+        static const int flat = getenv("SSN_FLAT_PRIORITY") ? atoi(getenv("SSN_FLAT_PRIORITY")) : 0;      /* measurement knob */
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&b->stream, cudaStreamNonBlocking, flat ? lo : hi));
+    }
     CU(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
     return SSN_OK;
 }

@@ -53,6 +53,7 @@ ssn_inflate_kernel(const uint8_t *__restrict__ in, const ssn_inflate_block *__re
 
 struct Lane {
     bool ready = false, busy = false;
+    uint8_t *h_slab = nullptr, *d_slab = nullptr;                 /* one pinned and one device allocation per lane */
     uint8_t *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
     ssn_inflate_block *h_blk = nullptr, *d_blk = nullptr;
     uint32_t *h_status = nullptr, *d_status = nullptr, *d_counter = nullptr;
@@ -88,8 +89,7 @@ extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t
 
 static void lane_free(Lane &L)
 {
-    cudaFreeHost(L.h_in); cudaFreeHost(L.h_out); cudaFreeHost(L.h_blk); cudaFreeHost(L.h_status);
-    cudaFree(L.d_in); cudaFree(L.d_out); cudaFree(L.d_blk); cudaFree(L.d_status); cudaFree(L.d_counter);
+    cudaFreeHost(L.h_slab); cudaFree(L.d_slab);
     if (L.done) cudaEventDestroy(L.done);
     if (L.stream) cudaStreamDestroy(L.stream);
     L = Lane();
@@ -103,23 +103,24 @@ extern "C" void ssn_inflater_destroy(ssn_inflater *f)
     delete f;
 }
 
-/* buffers of a lane on first use (pinned allocations are slow: readers that never come cost nothing) */
+/* buffers of a lane on first use (pinned allocations are slow: lanes nobody needs cost nothing) */
 static ssn_status lane_prepare(ssn_inflater *f, Lane &L)
 {
     if (L.ready) return SSN_OK;
     CUI(cudaSetDevice(f->device));
-    CUI(cudaMallocHost(&L.h_in, f->in_cap + 64));
-    CUI(cudaMallocHost(&L.h_out, f->out_cap + 64));
-    CUI(cudaMallocHost(&L.h_blk, sizeof(ssn_inflate_block) * f->max_blocks));
-    CUI(cudaMallocHost(&L.h_status, 4 * (size_t)f->max_blocks));
-    CUI(cudaMalloc(&L.d_in, f->in_cap + 64));
-    CUI(cudaMalloc(&L.d_out, f->out_cap + 64));
-    CUI(cudaMalloc(&L.d_blk, sizeof(ssn_inflate_block) * f->max_blocks));
-    CUI(cudaMalloc(&L.d_status, 4 * (size_t)f->max_blocks));
-    CUI(cudaMalloc(&L.d_counter, 4));
-    CUI(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+    const size_t n_in = f->in_cap + 64, n_out = f->out_cap + 64;
+    const size_t n_blk = (sizeof(ssn_inflate_block) * f->max_blocks + 63) & ~(size_t)63, n_st = (4 * (size_t)f->max_blocks + 63) & ~(size_t)63;
+    CUI(cudaMallocHost(&L.h_slab, n_in + n_out + n_blk + n_st));
+    CUI(cudaMalloc(&L.d_slab, n_in + n_out + n_blk + n_st + 64));
+    L.h_in = L.h_slab; L.h_out = L.h_in + n_in; L.h_blk = (ssn_inflate_block*)(L.h_out + n_out); L.h_status = (uint32_t*)(L.h_out + n_out + n_blk);
+    L.d_in = L.d_slab; L.d_out = L.d_in + n_in; L.d_blk = (ssn_inflate_block*)(L.d_out + n_out); L.d_status = (uint32_t*)(L.d_out + n_out + n_blk);
+    L.d_counter = (uint32_t*)(L.d_out + n_out + n_blk + n_st);
+    /* numerically lowest = highest priority is for the scoring streams; these take what is left */
+    int lo = 0, hi = 0;
+    CUI(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CUI(cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, lo));
     CUI(cudaEventCreateWithFlags(&L.done, cudaEventBlockingSync | cudaEventDisableTiming));
-    memset(L.h_in, 0, f->in_cap + 64);
+    memset(L.h_in, 0, n_in);
     L.ready = true;
     return SSN_OK;
 }

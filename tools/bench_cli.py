@@ -46,7 +46,7 @@ def main():
     ap.add_argument("--threads", default=None)
     ap.add_argument("--env", default="", help="extra environment for this repo's CLI, e.g. 'SSN_DEVICE_PILEUP=0 SSN_SLOTS=4'")
     ap.add_argument("--variants", default="", help="';'-separated environments run one after the other on the same pair, "
-                    "e.g. 'SSN_GPU_INFLATE=0;SSN_GPU_INFLATE=1'; every output is compared with the first")
+                    "e.g. 'SSN_GPU_INFLATE=0;SSN_GPU_INFLATE=1' ('ENV=1 @1,2': on these GPU counts only); every output is compared with the first")
     ap.add_argument("--workdir", default=None)
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
@@ -77,11 +77,14 @@ def main():
     mine = os.path.join(w, "mine.out")
     first = first_key = None
     for variant in a.variants.split(";") if a.variants else [""]:
+        gpu_list = a.gpus
+        if "@" in variant:                                  # 'ENV=... @1,2,4': this variant on these GPU counts only
+            variant, gpu_list = [x.strip() for x in variant.split("@", 1)]
         venv = dict(env)
         for kv in variant.split():
             k, v = kv.split("=", 1)
             venv[k] = v
-        for g in [int(x) for x in a.gpus.split(",")]:
+        for g in [int(x) for x in gpu_list.split(",")]:
             key = "gpus_%d" % g + ("|" + variant if variant else "")
             o = mine + ".%d" % len(res["runs"])
             runs = []
