@@ -260,6 +260,20 @@ ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_blo
                             uint64_t out_bytes, uint8_t *refused);
 ssn_status ssn_inflater_stats(ssn_inflater *f, uint64_t *blocks, uint64_t *refused, uint64_t *runs, uint64_t *in_bytes, uint64_t *out_bytes);
 
+/* The same decoder for callers that cannot allocate (no counterpart in the reference; added:
+ * code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The call allocates
+ * NOTHING, on the host or on the device: the block table and the warps' work counter go into a file-scope __device__
+ * array of the library (64.25 KB per GPU that loads it, held until exit), which limits one call to
+ * SSN_INFLATE_STATIC_MAX_BLOCKS blocks — more is refused with SSN_ERR_ARG and a message naming the limit.
+ * d_in (in_bytes of payloads, readable 64 bytes further), d_out (out_bytes) and d_status (n words; 0 = block inflated,
+ * else refused: nothing usable at its out_off) are DEVICE memory of `device` owned by the caller; blk[0, n) is host memory and
+ * may be reused when the call returns.  The work is queued on `stream` (a cudaStream_t, NULL = the default stream) and the
+ * call does not wait for it.  Every call shares the one array: two calls whose work may overlap on the GPU (different
+ * streams, different threads) race — order them on one stream or with events. */
+#define SSN_INFLATE_STATIC_MAX_BLOCKS 4096u
+ssn_status ssn_inflate_static(int device, const uint8_t *d_in, uint64_t in_bytes, const ssn_inflate_block *blk, uint32_t n,
+                              uint8_t *d_out, uint64_t out_bytes, uint32_t *d_status, void *stream);
+
 /* Writes a buffer larger than L2 on the ctx's device (cold-cache timing). */
 ssn_status ssn_flush_l2(ssn_ctx *ctx);
 

@@ -112,6 +112,7 @@ SIGNATURES = {
     "ssn_inflater_lane_release": (None, [_VP, C.c_int32]),
     "ssn_inflater_run": (_I, [_VP, C.c_int32, _VP, _U32, _U64, _U64, C.POINTER(C.c_uint8)]),
     "ssn_inflater_stats": (_I, [_VP, C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64)]),
+    "ssn_inflate_static": (_I, [C.c_int, _VP, _U64, _VP, _U32, _VP, _U64, _VP, _VP]),
 }
 
 _lib = None
@@ -425,6 +426,16 @@ def sites_to_records(sites, ref_chars):
 
 
 INFLATE_BLOCK_DTYPE = np.dtype([("in_off", np.uint32), ("in_len", np.uint32), ("out_off", np.uint32), ("out_len", np.uint32)])
+
+
+INFLATE_STATIC_MAX_BLOCKS = 4096          # include/ssn.h: SSN_INFLATE_STATIC_MAX_BLOCKS
+
+
+def inflate_static(device, d_in, in_bytes, blocks, d_out, out_bytes, d_status, stream=0):
+    """ssn_inflate_static: d_in / d_out / d_status are device addresses (ints) the caller owns; nothing is allocated."""
+    lib = load_library()
+    blocks = np.ascontiguousarray(blocks, INFLATE_BLOCK_DTYPE)
+    _check(lib.ssn_inflate_static(device, d_in, in_bytes, blocks.ctypes.data, len(blocks), d_out, out_bytes, d_status, stream))
 
 
 class Inflater:

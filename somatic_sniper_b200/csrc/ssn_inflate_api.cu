@@ -210,3 +210,83 @@ extern "C" ssn_status ssn_inflater_stats(ssn_inflater *f, uint64_t *blocks, uint
     if (out_bytes) *out_bytes = f->out_bytes;
     return SSN_OK;
 }
+
+/* ---- ssn_inflate_static: the same decoder with no allocation anywhere ----------------------------------------------------
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  The caller owns the input, output and status
+ * buffers on the device; what ssn_inflater_run keeps per lane in cudaMalloc'ed memory — the block table and the work
+ * counter the warps pull from — lives in a file-scope __device__ array of fixed size instead (every GPU that loads the
+ * library holds its 64.25 KB until exit).  All calls share that array: calls that overlap on the GPU race. */
+constexpr uint32_t kStaticHeadWords = 64;                              /* word 0: work counter; the table starts 256 B in */
+static __device__ __align__(256) uint32_t g_infl_static[kStaticHeadWords + 4u * SSN_INFLATE_STATIC_MAX_BLOCKS];
+
+__global__ void __launch_bounds__(kInflWarps * 32)
+ssn_inflate_static_kernel(const uint8_t *__restrict__ in, uint32_t n, uint8_t *out, uint32_t *status, uint32_t *scratch)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    infl::Work &W = reinterpret_cast<infl::Work*>(smem_raw)[threadIdx.x >> 5];
+    const ssn_inflate_block *blk = reinterpret_cast<const ssn_inflate_block*>(scratch + kStaticHeadWords);
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(scratch, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= n) break;
+        const ssn_inflate_block b = blk[i];
+        const int rc = infl::inflate_block(W, in + b.in_off, b.in_len, out + b.out_off, b.out_len);
+        if (lane == 0) status[i] = (uint32_t)rc;
+        __syncwarp();
+    }
+}
+
+/* per device, set up once with that device current: the array's DEVICE address (its name is only a host-side stand-in
+ * here) and the kernel's shared-memory opt-in */
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static uint32_t *g_static_ptr[kStaticMaxDevices];
+static int g_static_sms[kStaticMaxDevices];
+
+extern "C" ssn_status ssn_inflate_static(int device, const uint8_t *d_in, uint64_t in_bytes, const ssn_inflate_block *blk, uint32_t n,
+                                         uint8_t *d_out, uint64_t out_bytes, uint32_t *d_status, void *stream)
+{
+    if (device < 0 || device >= kStaticMaxDevices) { ssn_set_error("ssn_inflate_static: device %d out of range", device); return SSN_ERR_ARG; }
+    if (n > SSN_INFLATE_STATIC_MAX_BLOCKS) {
+        ssn_set_error("ssn_inflate_static: %u blocks in one call, the static scratch holds at most %u (SSN_INFLATE_STATIC_MAX_BLOCKS); split the batch",
+                      n, (unsigned)SSN_INFLATE_STATIC_MAX_BLOCKS);
+        return SSN_ERR_ARG;
+    }
+    if (n == 0) return SSN_OK;
+    if (!d_in || !blk || !d_out || !d_status) { ssn_set_error("ssn_inflate_static: null argument"); return SSN_ERR_ARG; }
+    if (in_bytes > 0xffffffffull || out_bytes > 0xffffffffull) { ssn_set_error("ssn_inflate_static: a batch is addressed with 32-bit offsets"); return SSN_ERR_ARG; }
+    for (uint32_t i = 0; i < n; ++i)
+        if ((uint64_t)blk[i].in_off + blk[i].in_len > in_bytes || (uint64_t)blk[i].out_off + blk[i].out_len > out_bytes) {
+            ssn_set_error("ssn_inflate_static: block %u lies outside the batch", i);
+            return SSN_ERR_ARG;
+        }
+    CUI(cudaSetDevice(device));
+    uint32_t *scratch;
+    int sms;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ptr[device]) {
+            cudaDeviceProp prop;
+            uint32_t *p = nullptr;
+            CUI(cudaGetDeviceProperties(&prop, device));
+            if (prop.major < 10) { ssn_set_error("ssn_inflate_static: device %d is not sm_100", device); return SSN_ERR_CUDA; }
+            CUI(cudaGetSymbolAddress((void**)&p, g_infl_static));
+            CUI(cudaFuncSetAttribute(ssn_inflate_static_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kInflWarps * sizeof(infl::Work))));
+            g_static_sms[device] = prop.multiProcessorCount;
+            g_static_ptr[device] = p;
+        }
+        scratch = g_static_ptr[device];
+        sms = g_static_sms[device];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    /* the array keeps the last call's contents: the counter starts at zero, the table is overwritten for [0, n) */
+    CUI(cudaMemsetAsync(scratch, 0, kStaticHeadWords * 4, st));
+    CUI(cudaMemcpyAsync(scratch + kStaticHeadWords, blk, sizeof(ssn_inflate_block) * (size_t)n, cudaMemcpyHostToDevice, st));
+    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)sms * 2u);
+    ssn_inflate_static_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), st>>>(d_in, n, d_out, d_status, scratch);
+    CUI(cudaGetLastError());
+    return SSN_OK;
+}
