@@ -520,6 +520,31 @@ typedef struct {
     uint8_t *nt16, *chars;
 } reads_task;
 
+/* Copy into a slot's pinned read array: the destination is read next by the GPU's copy engine, never by this host, so the
+ * lines are written with streaming stores (no read-for-ownership, nothing of it kept in the caches the readers work in). */
+#if defined(__x86_64__)
+#include <emmintrin.h>
+static int g_stream_copy = -1;
+static void copy_streaming(uint8_t *dst, const uint8_t *src, size_t n)
+{
+    size_t head;
+    if (g_stream_copy < 0) { const char *e = getenv("SSN_STREAM_COPY"); g_stream_copy = e && *e ? atoi(e) != 0 : 1; }   /* measurement knob */
+    if (!g_stream_copy || n < 4096) { memcpy(dst, src, n); return; }
+    head = (size_t)(-(uintptr_t)dst & 15u);
+    memcpy(dst, src, head); dst += head; src += head; n -= head;
+    for (; n >= 64; n -= 64, dst += 64, src += 64) {
+        const __m128i a = _mm_loadu_si128((const __m128i*)src), b = _mm_loadu_si128((const __m128i*)(src + 16));
+        const __m128i c = _mm_loadu_si128((const __m128i*)(src + 32)), d = _mm_loadu_si128((const __m128i*)(src + 48));
+        _mm_stream_si128((__m128i*)dst, a); _mm_stream_si128((__m128i*)(dst + 16), b);
+        _mm_stream_si128((__m128i*)(dst + 32), c); _mm_stream_si128((__m128i*)(dst + 48), d);
+    }
+    memcpy(dst, src, n);
+    _mm_sfence();
+}
+#else
+static void copy_streaming(uint8_t *dst, const uint8_t *src, size_t n) { memcpy(dst, src, n); }
+#endif
+
 static void reads_copy_task(void *arg, int idx)
 {
     const reads_task *t = &((const reads_task*)arg)[idx];
@@ -535,7 +560,7 @@ static void reads_copy_task(void *arg, int idx)
     } else {
         const ssn_window *w = t->p->w[t->s];
         uint32_t k;
-        memcpy(t->dst, w->buf, w->len);
+        copy_streaming(t->dst, w->buf, w->len);
         for (k = 0; k < w->n_reads; ++k) t->off[k] = t->off_base + w->rec_word[k];
     }
 }

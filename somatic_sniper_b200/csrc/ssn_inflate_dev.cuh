@@ -199,13 +199,23 @@ INFL_FN void pair_literals(uint32_t *tab, uint32_t tb)
 }
 
 /* ---- the bit reader: 32-bit aligned words, the same on every lane ------------------------------------------------ */
+/* The input is staged through registers: lane l keeps word (chunk * 32 + l) of the current 32-word chunk and of the
+ * next one, both fetched with one coalesced 128-byte load.  A refill is then a shuffle (the word's owner broadcasts it),
+ * and the global load of the chunk after next is in flight while two chunks' worth of symbols are decoded: the input
+ * latency, a dependent L2/DRAM round trip every 32 bits before, leaves the decode loop. */
 
 struct Bits {
     const uint32_t *w;         /* aligned word pointer at or below the first input byte */
-    uint32_t widx;             /* next word to load */
+    uint32_t widx;             /* next word to take */
     uint32_t lead;             /* bytes of w[0] that lie in front of the input */
+    uint32_t limit;            /* words of w[] that may be read (the caller's buffer is readable 16 bytes past the input) */
     uint64_t buf;
     uint32_t cnt;
+#ifdef SSN_INFL_HOST
+    uint32_t cur[32], nxt[32];
+#else
+    uint32_t cur, nxt;
+#endif
 };
 
 INFL_FN uint32_t load_word(const uint32_t *p)
@@ -217,18 +227,55 @@ INFL_FN uint32_t load_word(const uint32_t *p)
 #endif
 }
 
-INFL_FN void bits_seek(Bits &b, const uint8_t *in, uint32_t byte_pos)
+/* lane l <- word first + l (0 behind the readable end) */
+#ifdef SSN_INFL_HOST
+INFL_FN void bits_fetch(const Bits &b, uint32_t *dst, uint32_t first)
+{
+    for (uint32_t l = 0; l < 32u; ++l) dst[l] = first + l < b.limit ? load_word(b.w + first + l) : 0u;
+}
+INFL_FN uint32_t bits_word(const Bits &b, uint32_t idx) { return b.cur[idx & 31u]; }
+#else
+INFL_FN void bits_fetch(const Bits &b, uint32_t *dst, uint32_t first)
+{
+    const uint32_t i = first + (threadIdx.x & 31u);
+    *dst = i < b.limit ? load_word(b.w + i) : 0u;
+}
+INFL_FN uint32_t bits_word(const Bits &b, uint32_t idx) { return __shfl_sync(0xffffffffu, b.cur, (int)(idx & 31u)); }
+#endif
+
+/* positions the reader on input byte byte_pos; `remaining` = input bytes from there to the end */
+INFL_FN void bits_seek(Bits &b, const uint8_t *in, uint32_t byte_pos, uint32_t remaining)
 {
     const uintptr_t a = (uintptr_t)(in + byte_pos);
     b.w = (const uint32_t*)(a & ~(uintptr_t)3);
     b.lead = (uint32_t)(a & 3u);
+    b.limit = (b.lead + remaining + 16u) >> 2;
+#ifdef SSN_INFL_HOST
+    bits_fetch(b, b.cur, 0u);
+    bits_fetch(b, b.nxt, 32u);
+#else
+    bits_fetch(b, &b.cur, 0u);
+    bits_fetch(b, &b.nxt, 32u);
+#endif
     b.widx = 1;
-    b.buf = (uint64_t)(load_word(b.w) >> (8u * b.lead));
+    b.buf = (uint64_t)(bits_word(b, 0u) >> (8u * b.lead));
     b.cnt = 32u - 8u * b.lead;
 }
-INFL_FN void bits_refill(Bits &b)          /* afterwards at least 33 bits are buffered */
+INFL_FN void bits_refill(Bits &b)          /* afterwards at least 33 bits are buffered; the same on every lane */
 {
-    if (b.cnt <= 32u) { b.buf |= (uint64_t)load_word(b.w + b.widx) << b.cnt; b.widx += 1; b.cnt += 32u; }
+    if (b.cnt <= 32u) {
+        b.buf |= (uint64_t)bits_word(b, b.widx) << b.cnt;
+        b.widx += 1; b.cnt += 32u;
+        if ((b.widx & 31u) == 0u) {
+#ifdef SSN_INFL_HOST
+            for (int l = 0; l < 32; ++l) b.cur[l] = b.nxt[l];
+            bits_fetch(b, b.nxt, b.widx + 32u);
+#else
+            b.cur = b.nxt;
+            bits_fetch(b, &b.nxt, b.widx + 32u);
+#endif
+        }
+    }
 }
 /* bytes of the input consumed so far, counted from the last seek position (rounded up to whole bytes) */
 INFL_FN uint32_t bits_consumed_bytes(const Bits &b) { return (b.widx * 32u - 8u * b.lead - b.cnt + 7u) >> 3; }
@@ -340,7 +387,7 @@ INFL_FN int inflate_block(Work &W, const uint8_t *in, uint32_t in_len, uint8_t *
 #ifndef SSN_INFL_HOST
     o.mine = 0;
 #endif
-    bits_seek(b, in, 0);
+    bits_seek(b, in, 0, in_len);
     uint32_t seek_base = 0;                 /* input byte the bit reader was last positioned on */
     for (uint32_t guard = 0; guard < 65536u; ++guard) {
         bits_refill(b);
@@ -363,7 +410,7 @@ INFL_FN int inflate_block(Work &W, const uint8_t *in, uint32_t in_len, uint8_t *
             INFL_SYNC();
             o.pos += len; o.win_lo = o.pos & 31u;
             seek_base = at + len;
-            bits_seek(b, in, seek_base);
+            bits_seek(b, in, seek_base, in_len - seek_base);
             if (last) break;
             continue;
         }
