@@ -258,6 +258,14 @@ ssn_status ssn_inflater_lane_acquire(ssn_inflater *f, int32_t *lane, uint8_t **i
 void ssn_inflater_lane_release(ssn_inflater *f, int32_t lane);
 ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
                             uint64_t out_bytes, uint8_t *refused);
+/* The same, the inflated bytes delivered to h_dst instead of the lane's output buffer (NULL: the lane's).  h_dst must be
+ * page-locked memory the device can write: ssn_inflater_host_alloc hands such buffers out (usable with the lanes of any
+ * inflater of the process; given back with ssn_inflater_host_free, they are kept for the next caller and released with
+ * the inflater).  A reader that owns its output buffer this way saves one copy of everything it reads. */
+ssn_status ssn_inflater_run_to(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
+                               uint64_t out_bytes, uint8_t *refused, uint8_t *h_dst);
+ssn_status ssn_inflater_host_alloc(ssn_inflater *f, uint64_t bytes, void **out);
+void ssn_inflater_host_free(ssn_inflater *f, void *p);
 ssn_status ssn_inflater_stats(ssn_inflater *f, uint64_t *blocks, uint64_t *refused, uint64_t *runs, uint64_t *in_bytes, uint64_t *out_bytes);
 
 /* The same decoder for callers that cannot allocate (no counterpart in the reference; added

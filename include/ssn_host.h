@@ -83,6 +83,12 @@ typedef struct {
     int32_t (*lane_acquire)(void *ctx, uint8_t **in, uint64_t *in_cap, uint8_t **out, uint64_t *out_cap, uint32_t *max_blocks);  /* < 0: none */
     void (*lane_release)(void *ctx, int32_t lane);
     int (*run)(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes, uint64_t out_bytes, uint8_t *refused);  /* 0 ok */
+    /* optional, all three or none (NULL): memory the service can deliver into directly.  A reader then owns its output
+     * buffer (host_alloc, for its lifetime) and run_to writes the inflated bytes there, which saves it the copy out of
+     * the lane's buffer. */
+    void *(*host_alloc)(void *ctx, uint64_t bytes);
+    void (*host_free)(void *ctx, void *p);
+    int (*run_to)(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes, uint64_t out_bytes, uint8_t *refused, uint8_t *dst);
 } ssn_inflate_service;
 
 /* ---- region shards: the genome cut into contiguous intervals, one packer each ---------------------

@@ -112,6 +112,9 @@ SIGNATURES = {
     "ssn_inflater_lane_release": (None, [_VP, C.c_int32]),
     "ssn_inflater_run": (_I, [_VP, C.c_int32, _VP, _U32, _U64, _U64, C.POINTER(C.c_uint8)]),
     "ssn_inflater_stats": (_I, [_VP, C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64), C.POINTER(_U64)]),
+    "ssn_inflater_run_to": (_I, [_VP, C.c_int32, _VP, _U32, _U64, _U64, C.POINTER(C.c_uint8), _VP]),
+    "ssn_inflater_host_alloc": (_I, [_VP, _U64, C.POINTER(_VP)]),
+    "ssn_inflater_host_free": (None, [_VP, _VP]),
     "ssn_inflate_static": (_I, [C.c_int, _VP, _U64, _VP, _U32, _VP, _U64, _VP, _VP]),
 }
 

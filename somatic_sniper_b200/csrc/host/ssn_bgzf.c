@@ -36,6 +36,7 @@ struct ssn_bgzf {
     /* inflate service (GPU): a lane (pinned in / out) is taken per batch; the inflated bytes are copied into `out` */
     const ssn_inflate_service *svc;
     uint64_t lane_in_cap;
+    int out_direct;             /* `out` came from the service (host_alloc): run_to delivers into it */
     ssn_inflate_block *lane_blk;
     uint8_t *lane_refused;
     int use_zlib;               /* SSN_ZLIB_INFLATE: every block through zlib (measurement / fall-back knob) */
@@ -77,6 +78,7 @@ int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
     uint64_t in_cap = 0, out_cap = 0;
     uint32_t mb = 0;
     int32_t lane;
+    int direct = 0;
     if (!z || !svc || z->svc) return 0;
     /* a lane is held only while a batch is on its way (ssn_bgzf_next); all lanes have the same size: ask once */
     lane = svc->lane_acquire(svc->ctx, &li, &in_cap, &lo, &out_cap, &mb);
@@ -90,9 +92,11 @@ int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
     z->lane_refused = (uint8_t*)malloc(mb);
     /* the compressed side of a whole batch has to be resident: grow the read buffer (what is buffered so far moves along) */
     raw = (uint8_t*)calloc(1, RAW_CAP + SSN_INFLATE_SLACK);
-    out = (uint8_t*)malloc((size_t)mb * 65536);
+    if (svc->host_alloc && svc->host_free && svc->run_to) { out = (uint8_t*)svc->host_alloc(svc->ctx, (uint64_t)mb * 65536); direct = out != 0; }
+    if (!direct) out = (uint8_t*)malloc((size_t)mb * 65536);
     if (!z->lane_blk || !z->lane_refused || !raw || !out) {
-        free(z->lane_blk); free(z->lane_refused); free(raw); free(out); z->lane_blk = 0; z->lane_refused = 0;
+        free(z->lane_blk); free(z->lane_refused); free(raw); z->lane_blk = 0; z->lane_refused = 0;
+        if (direct) svc->host_free(svc->ctx, out); else free(out);
         return 0;
     }
     memcpy(raw, z->raw + z->raw_pos, z->raw_len - z->raw_pos);
@@ -102,6 +106,7 @@ int ssn_bgzf_use_service(ssn_bgzf *z, const void *svc_)
     z->out = out; z->out_cap = (size_t)mb * 65536;
     z->max_blocks = (int)mb;
     z->lane_in_cap = in_cap;
+    z->out_direct = direct;
     z->svc = svc;
     return 1;
 }
@@ -111,7 +116,8 @@ void ssn_bgzf_close(ssn_bgzf *z)
     if (!z) return;
     free(z->lane_blk); free(z->lane_refused);
     if (z->own_fd && z->fd >= 0) close(z->fd);
-    free(z->raw); free(z->out); free(z);
+    if (z->out_direct) z->svc->host_free(z->svc->ctx, z->out); else free(z->out);
+    free(z->raw); free(z);
 }
 
 uint64_t ssn_bgzf_compressed_bytes(const ssn_bgzf *z) { return z->consumed; }
@@ -232,8 +238,10 @@ int ssn_bgzf_next(ssn_bgzf *z, const uint8_t **data, size_t *len)
                     z->lane_blk[k].out_off = (uint32_t)z->blocks[k].uoff; z->lane_blk[k].out_len = z->blocks[k].ulen;
                     in_bytes += z->blocks[k].clen;
                 }
-                if (svc->run(svc->ctx, lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused) == 0) memcpy(z->out, lo, uoff);
-                else memset(z->lane_refused, 1, (size_t)(unsigned)n);
+                int ok;
+                if (z->out_direct) ok = svc->run_to(svc->ctx, lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused, z->out) == 0;
+                else if ((ok = svc->run(svc->ctx, lane, z->lane_blk, (uint32_t)n, in_bytes, uoff, z->lane_refused) == 0)) memcpy(z->out, lo, uoff);
+                if (!ok) memset(z->lane_refused, 1, (size_t)(unsigned)n);
             }
             svc->lane_release(svc->ctx, lane);
         }

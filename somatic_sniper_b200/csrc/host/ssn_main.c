@@ -415,6 +415,19 @@ static int svc_run(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32
     return ssn_inflater_run(c->inf[lane / 4096], lane % 4096, blk, n, in_bytes, out_bytes, refused) == SSN_OK ? 0 : -1;
 }
 
+static int svc_run_to(void *ctx, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes, uint64_t out_bytes, uint8_t *refused, uint8_t *dst)
+{
+    infl_ctx *c = (infl_ctx*)ctx;
+    return ssn_inflater_run_to(c->inf[lane / 4096], lane % 4096, blk, n, in_bytes, out_bytes, refused, dst) == SSN_OK ? 0 : -1;
+}
+/* the readers' own output buffers: page-locked, from the first inflater's pool (portable: any GPU's lane writes into them) */
+static void *svc_host_alloc(void *ctx, uint64_t bytes)
+{
+    void *p = 0;
+    return ssn_inflater_host_alloc(((infl_ctx*)ctx)->inf[0], bytes, &p) == SSN_OK ? p : 0;
+}
+static void svc_host_free(void *ctx, void *p) { ssn_inflater_host_free(((infl_ctx*)ctx)->inf[0], p); }
+
 static int start_feeders(run_t *R)
 {
     int i;
@@ -642,6 +655,7 @@ int main(int argc, char *argv[])
         if (ok) {
             infl.n = R.n_gpus;
             svc.ctx = &infl; svc.lane_acquire = svc_acquire; svc.lane_release = svc_release; svc.run = svc_run;
+            if (env_int("SSN_INFLATE_DIRECT", 1, 0, 1)) { svc.host_alloc = svc_host_alloc; svc.host_free = svc_host_free; svc.run_to = svc_run_to; }
             ssn_shardset_set_inflate_service(R.set, &svc);
             gpu_inflate = 1;
         } else fprintf(stderr, "[bam-somaticsniper] no GPU inflate (%s); the readers inflate on the host\n", ssn_last_error());

@@ -30,7 +30,8 @@ extern "C" void ssn_set_error(const char *fmt, ...);
         }                                                                                          \
     } while (0)
 
-constexpr int kInflWarps = 8;              /* per CTA: 8 x 12.4 KB of tables; two CTAs per SM */
+constexpr int kInflWarps = 8;              /* per CTA: 8 x 9.3 KB of tables; three CTAs per SM */
+constexpr uint32_t kInflCtasPerSm = 3;
 
 __global__ void __launch_bounds__(kInflWarps * 32)
 ssn_inflate_kernel(const uint8_t *__restrict__ in, const ssn_inflate_block *__restrict__ blk, uint32_t n, uint8_t *out,
@@ -69,6 +70,10 @@ struct ssn_inflater {
     std::mutex mu;
     std::condition_variable cv;
     uint64_t blocks = 0, refused = 0, runs = 0, in_bytes = 0, out_bytes = 0;
+    /* page-locked buffers handed to callers (ssn_inflater_host_alloc); given back ones are kept for the next caller and
+     * freed with the inflater: cudaFreeHost waits for the whole device, which a running stream cannot afford */
+    struct HostBuf { void *p; uint64_t bytes; bool busy; };
+    std::vector<HostBuf> host_bufs;
 };
 
 extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t in_cap, uint64_t out_cap, uint32_t max_blocks, ssn_inflater **out)
@@ -100,6 +105,7 @@ extern "C" void ssn_inflater_destroy(ssn_inflater *f)
     if (!f) return;
     cudaSetDevice(f->device);
     for (Lane &L : f->lanes) if (L.ready) { cudaStreamSynchronize(L.stream); lane_free(L); }
+    for (auto &h : f->host_bufs) cudaFreeHost(h.p);
     delete f;
 }
 
@@ -167,8 +173,37 @@ extern "C" ssn_status ssn_inflater_limits(const ssn_inflater *f, uint64_t *in_ca
     return SSN_OK;
 }
 
+extern "C" ssn_status ssn_inflater_host_alloc(ssn_inflater *f, uint64_t bytes, void **out)
+{
+    if (!f || !out || !bytes) { ssn_set_error("ssn_inflater_host_alloc: bad argument"); return SSN_ERR_ARG; }
+    {
+        std::lock_guard<std::mutex> lk(f->mu);
+        for (auto &h : f->host_bufs) if (!h.busy && h.bytes >= bytes && h.bytes <= 2 * bytes) { h.busy = true; *out = h.p; return SSN_OK; }
+    }
+    void *p = nullptr;
+    CUI(cudaSetDevice(f->device));
+    CUI(cudaHostAlloc(&p, bytes, cudaHostAllocPortable));           /* any GPU's lane may write into it */
+    std::lock_guard<std::mutex> lk(f->mu);
+    f->host_bufs.push_back({p, bytes, true});
+    *out = p;
+    return SSN_OK;
+}
+
+extern "C" void ssn_inflater_host_free(ssn_inflater *f, void *p)
+{
+    if (!f || !p) return;
+    std::lock_guard<std::mutex> lk(f->mu);
+    for (auto &h : f->host_bufs) if (h.p == p) { h.busy = false; return; }
+}
+
 extern "C" ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
                                        uint64_t out_bytes, uint8_t *refused)
+{
+    return ssn_inflater_run_to(f, lane, blk, n, in_bytes, out_bytes, refused, nullptr);
+}
+
+extern "C" ssn_status ssn_inflater_run_to(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
+                                          uint64_t out_bytes, uint8_t *refused, uint8_t *h_dst)
 {
     if (!f || lane < 0 || (size_t)lane >= f->lanes.size() || !blk || !refused) { ssn_set_error("ssn_inflater_run: bad argument"); return SSN_ERR_ARG; }
     Lane &L = f->lanes[lane];
@@ -183,10 +218,10 @@ extern "C" ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_
     CUI(cudaMemsetAsync(L.d_counter, 0, 4, L.stream));
     CUI(cudaMemcpyAsync(L.d_in, L.h_in, ((size_t)in_bytes + 63) & ~(size_t)63, cudaMemcpyHostToDevice, L.stream));
     CUI(cudaMemcpyAsync(L.d_blk, L.h_blk, sizeof(ssn_inflate_block) * n, cudaMemcpyHostToDevice, L.stream));
-    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)f->num_sms * 2u);
+    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)f->num_sms * kInflCtasPerSm);
     ssn_inflate_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), L.stream>>>(L.d_in, L.d_blk, n, L.d_out, L.d_status, L.d_counter);
     CUI(cudaGetLastError());
-    CUI(cudaMemcpyAsync(L.h_out, L.d_out, (size_t)out_bytes, cudaMemcpyDeviceToHost, L.stream));
+    CUI(cudaMemcpyAsync(h_dst ? h_dst : L.h_out, L.d_out, (size_t)out_bytes, cudaMemcpyDeviceToHost, L.stream));
     CUI(cudaMemcpyAsync(L.h_status, L.d_status, 4 * (size_t)n, cudaMemcpyDeviceToHost, L.stream));
     CUI(cudaEventRecord(L.done, L.stream));
     CUI(cudaEventSynchronize(L.done));
@@ -285,7 +320,7 @@ extern "C" ssn_status ssn_inflate_static(int device, const uint8_t *d_in, uint64
     /* the array keeps the last call's contents: the counter starts at zero, the table is overwritten for [0, n) */
     CUI(cudaMemsetAsync(scratch, 0, kStaticHeadWords * 4, st));
     CUI(cudaMemcpyAsync(scratch + kStaticHeadWords, blk, sizeof(ssn_inflate_block) * (size_t)n, cudaMemcpyHostToDevice, st));
-    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)sms * 2u);
+    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)sms * kInflCtasPerSm);
     ssn_inflate_static_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), st>>>(d_in, n, d_out, d_status, scratch);
     CUI(cudaGetLastError());
     return SSN_OK;

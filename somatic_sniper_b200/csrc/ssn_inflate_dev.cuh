@@ -36,7 +36,7 @@
 namespace infl {
 
 constexpr int kLLBits = 10, kDBits = 8;
-constexpr int kLLSub = 1024, kDSub = 512;              /* second-level entries a block may need at most (else: refused) */
+constexpr int kLLSub = 512, kDSub = 512;               /* second-level entries a block may need at most (else: refused) */
 constexpr int kLLSize = (1 << kLLBits) + kLLSub, kDSize = (1 << kDBits) + kDSub;
 
 /* entry: bits 0-3 code bits to consume, 4-7 extra bits (pointer: width of its second-level index), 8-10 kind,
@@ -58,8 +58,7 @@ struct Work {
     uint32_t ll[kLLSize];
     uint32_t d[kDSize];
     uint8_t lens[320];
-    uint8_t sub_bits[1 << kLLBits];
-};
+};                                          /* 9536 B: 8 warps per CTA, three CTAs per SM */
 
 INFL_FN uint32_t len_base(uint32_t s)      /* s = symbol - 257 */
 {
@@ -97,7 +96,8 @@ INFL_FN uint32_t bitrev(uint32_t code, uint32_t len)
 /* Canonical code -> two-level table.  The counting and the code assignment are the same on every lane; the table
  * entries are written 32 at a time.  Returns non-zero for an over-subscribed code or one whose second-level tables do not
  * fit.  Incomplete codes are accepted (unused entries are K_BAD and fail only if they are hit). */
-INFL_FN int build(Work &W, uint32_t *tab, uint32_t sub_cap, const uint8_t *lens, uint32_t nsym, uint32_t tb, bool is_dist)
+/* sub_bits: 1 << tb bytes of scratch (widths of the second-level tables) that are free while this table is built */
+INFL_FN int build(uint8_t *sub_bits, uint32_t *tab, uint32_t sub_cap, const uint8_t *lens, uint32_t nsym, uint32_t tb, bool is_dist)
 {
     const uint32_t main_size = 1u << tb;
     uint32_t cnt[16];
@@ -113,7 +113,7 @@ INFL_FN int build(Work &W, uint32_t *tab, uint32_t sub_cap, const uint8_t *lens,
     nx[0] = 0;
     for (int l = 1; l < 16; ++l) { code = (code + cnt[l - 1]) << 1; nx[l] = code; if ((uint32_t)l > tb && cnt[l]) long_codes = true; }
     INFL_SYNC();
-    { INFL_LANES(lane) { for (uint32_t i = (uint32_t)lane; i < main_size; i += 32u) { tab[i] = entry(0, K_BAD, 0, 1); W.sub_bits[i] = 0; } } }
+    { INFL_LANES(lane) { for (uint32_t i = (uint32_t)lane; i < main_size; i += 32u) { tab[i] = entry(0, K_BAD, 0, 1); sub_bits[i] = 0; } } }
     INFL_SYNC();
     uint32_t nfree = main_size;
     if (long_codes) {
@@ -124,15 +124,15 @@ INFL_FN int build(Work &W, uint32_t *tab, uint32_t sub_cap, const uint8_t *lens,
             const uint32_t l = lens[i];
             if (l > tb) {
                 const uint32_t prefix = bitrev(n2[l]++, l) & (main_size - 1u);
-                if (W.sub_bits[prefix] < l - tb) {
+                if (sub_bits[prefix] < l - tb) {
                     INFL_SYNC();
-                    { INFL_LANES(lane) { if (lane == 0) W.sub_bits[prefix] = (uint8_t)(l - tb); } }
+                    { INFL_LANES(lane) { if (lane == 0) sub_bits[prefix] = (uint8_t)(l - tb); } }
                     INFL_SYNC();
                 }
             } else if (l) n2[l]++;
         }
         for (uint32_t i = 0; i < main_size; ++i) {
-            const uint32_t sb = W.sub_bits[i];
+            const uint32_t sb = sub_bits[i];
             if (sb) {
                 if (nfree - main_size + (1u << sb) > sub_cap) return 2;
                 INFL_SYNC();
@@ -348,7 +348,10 @@ INFL_FN uint32_t load_out(const uint8_t *p)
 #ifdef SSN_INFL_HOST
     return *p;
 #else
-    return __ldcg(p);          /* L2: what the other lanes of the warp stored before the last __syncwarp */
+    /* An ordinary load: the bytes were stored by lanes of this warp before the last __syncwarp, which orders them for
+     * every lane taking part, and one SM has one L1 - so the copy may hit L1 instead of paying an L2 round trip per
+     * match (a quarter of all stall samples with ld.cg, profiles/r02/inflate_ncu.md). */
+    return *p;
 #endif
 }
 
@@ -419,7 +422,7 @@ INFL_FN int inflate_block(Work &W, const uint8_t *in, uint32_t in_len, uint8_t *
             INFL_SYNC();
             { INFL_LANES(lane) { for (uint32_t i = (uint32_t)lane; i < 320u; i += 32u) W.lens[i] = i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : i < 288u ? 8 : 5; } }
             INFL_SYNC();
-            if (build(W, W.ll, kLLSub, W.lens, 288, kLLBits, false) || build(W, W.d, kDSub, W.lens + 288, 32, kDBits, true)) return 13;
+            if (build((uint8_t*)W.d, W.ll, kLLSub, W.lens, 288, kLLBits, false) || build(W.lens, W.d, kDSub, W.lens + 288, 32, kDBits, true)) return 13;
             pair_literals(W.ll, kLLBits);
         } else {
             const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
@@ -438,7 +441,7 @@ INFL_FN int inflate_block(Work &W, const uint8_t *in, uint32_t in_len, uint8_t *
                 { INFL_LANES(lane) { if (lane == 0) W.lens[288 + order[i]] = (uint8_t)v; } }
             }
             INFL_SYNC();
-            if (build(W, W.d, 0, W.lens + 288, 19, 7, false)) return 15;
+            if (build(W.lens, W.d, 0, W.lens + 288, 19, 7, false)) return 15;
             { INFL_LANES(lane) { if (lane < 19) W.lens[288 + lane] = 0; } }
             INFL_SYNC();
             const uint32_t n = hlit + hdist;
@@ -471,13 +474,15 @@ INFL_FN int inflate_block(Work &W, const uint8_t *in, uint32_t in_len, uint8_t *
                 i += rep;
             }
             if (W.lens[256] == 0) return 21;
-            if (build(W, W.ll, kLLSub, W.lens, 288, kLLBits, false) || build(W, W.d, kDSub, W.lens + 288, 32, kDBits, true)) return 22;
+            if (build((uint8_t*)W.d, W.ll, kLLSub, W.lens, 288, kLLBits, false) || build(W.lens, W.d, kDSub, W.lens + 288, 32, kDBits, true)) return 22;
             pair_literals(W.ll, kLLBits);
         }
         /* the symbols of the block */
         for (;;) {
+            /* no input bound check per symbol: behind the input the reader yields zero words (bits_fetch), every turn of
+             * this loop either ends it or produces output, and the output is bounded - a stream that runs off its end is
+             * caught by the output checks or by the consumed-bytes check behind the loop */
             bits_refill(b);
-            if (seek_base + bits_consumed_bytes(b) > in_len) return 30;
             uint32_t e = ll[BITS_PEEK(b, kLLBits)];
             if (E_KIND(e) == K_SUB) { BITS_TAKE(b, kLLBits); e = ll[E_VAL(e) + BITS_PEEK(b, E_EXTRA(e))]; }
             if (E_ISLIT(e)) {

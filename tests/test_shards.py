@@ -337,10 +337,12 @@ def test_several_consumers_take_distinct_shards(host, big_pair):
     assert one == four and sum(c for c, _ in one.values()) > 100000
 
 
-def test_readers_through_an_inflate_service(host, big_pair):
+@pytest.mark.parametrize("direct", [0, 1])
+def test_readers_through_an_inflate_service(host, big_pair, direct):
     """The readers' GPU-inflate plumbing without a GPU: a service whose `run` decodes every block with the DEVICE decoder's
     source compiled for the host (ssn_inflate_dev_host) and refuses every seventh block (the reader must then inflate that
-    one itself).  Lanes are handed out and given back; the columns equal the host-inflate run's."""
+    one itself).  Lanes are handed out and given back; the columns equal the host-inflate run's.  direct = 1: the service
+    also offers host_alloc / host_free / run_to, so the readers own their output buffers and the service writes there."""
     import threading
     from somatic_sniper_b200 import api
     p = big_pair
@@ -356,8 +358,13 @@ def test_readers_through_an_inflate_service(host, big_pair):
     REL = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
     RUN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(Block), C.c_uint32, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint8))
 
+    ALLOC = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_uint64)
+    FREE = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p)
+    RUNTO = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(Block), C.c_uint32, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint8), C.c_void_p)
+
     class Service(C.Structure):
-        _fields_ = [("ctx", C.c_void_p), ("lane_acquire", ACQ), ("lane_release", REL), ("run", RUN)]
+        _fields_ = [("ctx", C.c_void_p), ("lane_acquire", ACQ), ("lane_release", REL), ("run", RUN),
+                    ("host_alloc", ALLOC), ("host_free", FREE), ("run_to", RUNTO)]
 
     MAXB, lock = 24, threading.Lock()
     lanes = [dict(busy=False, i=np.zeros(MAXB * 65600 + 64, np.uint8), o=np.zeros(MAXB * 65536 + 64, np.uint8)) for _ in range(8)]
@@ -381,8 +388,26 @@ def test_readers_through_an_inflate_service(host, big_pair):
             lanes[k]["busy"] = False
             stats["released"] += 1
 
-    def run(ctx, k, blk, n, in_bytes, out_bytes, refused):
+    owned = {}
+
+    def host_alloc(ctx, nbytes):
+        a = np.zeros(nbytes + 64, np.uint8)
+        with lock:
+            owned[a.ctypes.data] = a
+            stats["allocs"] = stats.get("allocs", 0) + 1
+        return a.ctypes.data
+
+    def host_free(ctx, ptr):
+        with lock:
+            del owned[ptr]
+
+    def run(ctx, k, blk, n, in_bytes, out_bytes, refused, dst=None):
         L = lanes[k]
+        out_base = dst if dst else L["o"].ctypes.data
+        if dst:
+            assert dst in owned
+            with lock:
+                stats["direct_runs"] = stats.get("direct_runs", 0) + 1
         for j in range(n):
             b = blk[j]
             with lock:
@@ -393,11 +418,14 @@ def test_readers_through_an_inflate_service(host, big_pair):
                 with lock:
                     stats["refused"] += 1
                 continue
-            rc = dev.ssn_inflate_dev_host_shift(L["i"].ctypes.data + b.in_off, b.in_len, L["o"].ctypes.data + b.out_off, b.out_len, 0)
+            rc = dev.ssn_inflate_dev_host_shift(L["i"].ctypes.data + b.in_off, b.in_len, out_base + b.out_off, b.out_len, 0)
             refused[j] = 1 if rc else 0
         return 0
 
-    svc = Service(None, ACQ(acquire), REL(release), RUN(run))
+    if direct:
+        svc = Service(None, ACQ(acquire), REL(release), RUN(run), ALLOC(host_alloc), FREE(host_free), RUNTO(run))
+    else:
+        svc = Service(None, ACQ(acquire), REL(release), RUN(run), ALLOC(), FREE(), RUNTO())
     lib.ssn_shardset_set_inflate_service.argtypes = [C.c_void_p, C.POINTER(Service)]
     lib.ssn_shardset_set_inflate_service.restype = None
     ss = host.ShardSet(p["tumor"], p["normal"], p["fasta"], 0, threads=4, stride_windows=2, lookback_windows=1, max_reading=3, max_open=4,
@@ -411,3 +439,5 @@ def test_readers_through_an_inflate_service(host, big_pair):
     pk.close()
     assert got == want
     assert stats["blocks"] > 200 and stats["refused"] > 20 and stats["acquired"] == stats["released"] > 10
+    if direct:
+        assert stats["allocs"] >= 2 and stats["direct_runs"] > 10 and not owned      # every buffer came back
