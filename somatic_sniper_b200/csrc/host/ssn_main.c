@@ -20,7 +20,7 @@
  *   SSN_DEVICE_PILEUP  1 (default): ship the filtered reads, build the columns on the GPU; 0: pack columns on the host
  *   SSN_GPU_INFLATE  1 (default): the readers hand BGZF blocks to the GPU(s) to inflate (ssn_inflater_*, one warp per
  *                block) and only frame the records; 0: inflate on the host cores.  SSN_INFLATE_LANES batches in flight
- *                per GPU (16), SSN_INFLATE_BLOCKS blocks per batch (96)
+ *                per GPU (24), SSN_INFLATE_BLOCKS blocks per batch (96)
  *   SSN_SERIAL   1: one interval, front to back (what a pair that cannot be cut gets anyway)
  *   SSN_SHARD_WINDOWS / SSN_SHARD_LOOKBACK / SSN_SHARD_READERS  interval length and look-back in windows of 8192
  *                positions, intervals read at once (ssn_host.h)
@@ -603,10 +603,6 @@ int main(int argc, char *argv[])
         }
         setenv("CUDA_VISIBLE_DEVICES", list, 1);
     }
-    /* The inflate lanes add a stream per batch in flight.  With the driver's default of 8 hardware queues the scoring streams
-     * share queues with them, and every scoring launch waits behind an inflate kernel it does not depend on (measured on
-     * B200: 2.6 ms per scoring batch, the stream a third slower than with host inflate).  One queue per stream ends that. */
-    if (env_int("SSN_GPU_INFLATE", 1, 0, 1)) setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     for (i = 0; i < R.n_gpus; ++i) { R.gpus[i].run = &R; R.gpus[i].index = i; }
     R.n_slots = env_int("SSN_SLOTS", 3, 1, MAX_SLOTS);
     {
@@ -647,7 +643,7 @@ int main(int argc, char *argv[])
     ssn_writer_header(wr, fn_fa, normal_id, tumor_id);
     if (env_int("SSN_GPU_INFLATE", 1, 0, 1) && ssn_shardset_n_shards(R.set) > 1) {
         /* lanes = inflate batches in flight per GPU; a lane's buffers are allocated when it is first taken */
-        const uint32_t lanes = (uint32_t)env_int("SSN_INFLATE_LANES", 16, 1, 256);
+        const uint32_t lanes = (uint32_t)env_int("SSN_INFLATE_LANES", 24, 1, 256);
         const uint32_t nblk = (uint32_t)env_int("SSN_INFLATE_BLOCKS", (int)INFL_BLOCKS, 4, 512);
         int ok = 1;
         for (i = 0; i < R.n_gpus && ok; ++i)

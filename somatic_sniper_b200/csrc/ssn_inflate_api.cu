@@ -2,17 +2,20 @@
  * ssn_inflate_api.cu — BGZF blocks inflated on the GPU: the kernel around ssn_inflate_dev.cuh (one warp per block) and
  * the thread-safe "lane" service the BAM readers call (include/ssn.h: ssn_inflater_*).
  *
- * A lane is what one reader thread owns while it reads: a pinned input buffer it fills with the compressed payloads of
- * a few dozen blocks, a pinned output buffer it frames records from, their device twins and a stream.  ssn_inflater_run
- * is synchronous for the caller (copy in, kernel, copy out, wait) and costs it no CPU while it waits; dozens of readers
- * do that at once, so the device sees dozens of small launches on independent streams that together fill its SMs.
+ * A lane is what a reader thread holds for one batch: a pinned input buffer it fills with the compressed payloads of
+ * a few dozen blocks and a pinned output buffer it takes the inflated bytes from.  ssn_inflater_run is synchronous for the
+ * caller and costs it no CPU while it waits.  Behind it one worker thread per inflater gathers the requests of all the
+ * readers waiting at that moment into a WAVE — one launch over all their blocks, their copies in front and behind it — on
+ * one of three streams; the stream's completion callback wakes the callers.
  * A block the device decoder refuses comes back flagged and the reader inflates it on the host (zlib reads everything
  * the reference reads), so the service can never change what is read.
  */
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <mutex>
+#include <thread>
 #include <condition_variable>
 #include <vector>
 
@@ -52,33 +55,82 @@ ssn_inflate_kernel(const uint8_t *__restrict__ in, const ssn_inflate_block *__re
     }
 }
 
+/* A lane is a reader's view: a pinned input buffer to fill, a pinned output buffer to read, and one request at a time.
+ * Its device twin is a slice of the inflater's arenas, so that one kernel launch can serve the requests of many lanes:
+ * block offsets are relative to the arena. */
 struct Lane {
     bool ready = false, busy = false;
-    uint8_t *h_slab = nullptr, *d_slab = nullptr;                 /* one pinned and one device allocation per lane */
-    uint8_t *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    uint8_t *h_slab = nullptr, *h_in = nullptr, *h_out = nullptr;
+    /* the request in flight (owner: the calling thread until it is queued, the worker / completion until done) */
+    std::vector<ssn_inflate_block> blk;
+    uint32_t n = 0;
+    uint64_t in_bytes = 0, out_bytes = 0;
+    uint8_t *refused = nullptr, *h_dst = nullptr;
+    bool done = false;
+    int error = 0;
+};
+
+struct ssn_inflater;
+
+/* A wave is one launch: the requests that were waiting when the worker came round, up to wave_blocks blocks.  Three
+ * waves on three streams keep copies in, kernel and copies out of successive waves overlapped — and three streams, not one
+ * per lane, is what keeps the inflate work off the hardware queues the scoring streams use (with the driver's default of
+ * eight queues, a stream per lane made every scoring launch wait behind an inflate kernel it did not depend on). */
+struct Wave {
+    ssn_inflater *f = nullptr;
+    bool busy = false;
+    cudaStream_t stream = nullptr;
     ssn_inflate_block *h_blk = nullptr, *d_blk = nullptr;
     uint32_t *h_status = nullptr, *d_status = nullptr, *d_counter = nullptr;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;          /* blocking-sync: a waiting reader sleeps, its core goes to another reader */
+    std::vector<int> lanes;                 /* lanes served, in table order */
+    uint32_t n = 0;
 };
+
+constexpr int kWaves = 3;
 
 struct ssn_inflater {
     int device, num_sms;
-    uint64_t in_cap, out_cap;
-    uint32_t max_blocks;
+    uint64_t in_cap, out_cap, in_stride, out_stride;
+    uint32_t max_blocks, wave_blocks;
     std::vector<Lane> lanes;
+    uint8_t *d_in = nullptr, *d_out = nullptr;           /* arenas: lane i owns [i * stride, (i + 1) * stride) */
+    Wave waves[kWaves];
+    std::vector<int> pending;               /* lanes with a request, oldest first */
+    std::thread worker;
+    bool stop = false, worker_failed = false;
     std::mutex mu;
-    std::condition_variable cv;
-    uint64_t blocks = 0, refused = 0, runs = 0, in_bytes = 0, out_bytes = 0;
+    std::condition_variable cv_lane, cv_work, cv_done;
+    uint64_t blocks = 0, refused = 0, runs = 0, in_bytes = 0, out_bytes = 0, launches = 0;
     /* page-locked buffers handed to callers (ssn_inflater_host_alloc); given back ones are kept for the next caller and
      * freed with the inflater: cudaFreeHost waits for the whole device, which a running stream cannot afford */
     struct HostBuf { void *p; uint64_t bytes; bool busy; };
     std::vector<HostBuf> host_bufs;
 };
 
+static void inflater_worker(ssn_inflater *f);
+
+static void inflater_release(ssn_inflater *f)
+{
+    for (Lane &L : f->lanes) if (L.h_slab) cudaFreeHost(L.h_slab);
+    for (Wave &w : f->waves) {
+        if (w.stream) cudaStreamDestroy(w.stream);
+        cudaFreeHost(w.h_blk); cudaFreeHost(w.h_status);
+        cudaFree(w.d_blk); cudaFree(w.d_status); cudaFree(w.d_counter);
+    }
+    cudaFree(f->d_in); cudaFree(f->d_out);
+    for (auto &h : f->host_bufs) cudaFreeHost(h.p);
+    delete f;
+}
+
 extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t in_cap, uint64_t out_cap, uint32_t max_blocks, ssn_inflater **out)
 {
     if (!out || !n_lanes || !in_cap || !out_cap || !max_blocks) { ssn_set_error("ssn_inflater_create: bad argument"); return SSN_ERR_ARG; }
+    const uint64_t in_stride = ((in_cap + 63) & ~63ull) + 64, out_stride = ((out_cap + 63) & ~63ull) + 64;
+    if (in_stride * n_lanes > 0xffffffffull || out_stride * n_lanes > 0xffffffffull) {
+        ssn_set_error("ssn_inflater_create: %u lanes of %llu + %llu bytes exceed the 4 GiB a launch addresses", n_lanes,
+                      (unsigned long long)in_cap, (unsigned long long)out_cap);
+        return SSN_ERR_ARG;
+    }
     CUI(cudaSetDevice(device));
     cudaDeviceProp prop;
     CUI(cudaGetDeviceProperties(&prop, device));
@@ -87,46 +139,52 @@ extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t
     ssn_inflater *f = new ssn_inflater();
     f->device = device; f->num_sms = prop.multiProcessorCount;
     f->in_cap = (in_cap + 63) & ~63ull; f->out_cap = (out_cap + 63) & ~63ull; f->max_blocks = max_blocks;
+    f->in_stride = in_stride; f->out_stride = out_stride;
+    f->wave_blocks = std::max<uint32_t>(max_blocks, 8192u);
     f->lanes.resize(n_lanes);
+#define CUF(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ssn_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); inflater_release(f); return SSN_ERR_CUDA; } } while (0)
+    CUF(cudaMalloc(&f->d_in, in_stride * n_lanes));
+    CUF(cudaMalloc(&f->d_out, out_stride * n_lanes));
+    int lo = 0, hi = 0;
+    CUF(cudaDeviceGetStreamPriorityRange(&lo, &hi));    /* numerically lowest = highest priority is for the scoring streams */
+    for (Wave &w : f->waves) {
+        w.f = f;
+        CUF(cudaStreamCreateWithPriority(&w.stream, cudaStreamNonBlocking, lo));
+        CUF(cudaMallocHost(&w.h_blk, sizeof(ssn_inflate_block) * f->wave_blocks));
+        CUF(cudaMallocHost(&w.h_status, 4 * (size_t)f->wave_blocks));
+        CUF(cudaMalloc(&w.d_blk, sizeof(ssn_inflate_block) * f->wave_blocks));
+        CUF(cudaMalloc(&w.d_status, 4 * (size_t)f->wave_blocks));
+        CUF(cudaMalloc(&w.d_counter, 256));
+    }
+#undef CUF
+    f->worker = std::thread(inflater_worker, f);
     *out = f;
     return SSN_OK;
-}
-
-static void lane_free(Lane &L)
-{
-    cudaFreeHost(L.h_slab); cudaFree(L.d_slab);
-    if (L.done) cudaEventDestroy(L.done);
-    if (L.stream) cudaStreamDestroy(L.stream);
-    L = Lane();
 }
 
 extern "C" void ssn_inflater_destroy(ssn_inflater *f)
 {
     if (!f) return;
+    {
+        std::unique_lock<std::mutex> lk(f->mu);
+        f->stop = true;
+        f->cv_work.notify_all();
+    }
+    if (f->worker.joinable()) f->worker.join();
     cudaSetDevice(f->device);
-    for (Lane &L : f->lanes) if (L.ready) { cudaStreamSynchronize(L.stream); lane_free(L); }
-    for (auto &h : f->host_bufs) cudaFreeHost(h.p);
-    delete f;
+    for (Wave &w : f->waves) if (w.stream) cudaStreamSynchronize(w.stream);
+    inflater_release(f);
 }
 
-/* buffers of a lane on first use (pinned allocations are slow: lanes nobody needs cost nothing) */
+/* pinned buffers of a lane on first use (pinned allocations are slow: lanes nobody needs cost nothing) */
 static ssn_status lane_prepare(ssn_inflater *f, Lane &L)
 {
     if (L.ready) return SSN_OK;
     CUI(cudaSetDevice(f->device));
-    const size_t n_in = f->in_cap + 64, n_out = f->out_cap + 64;
-    const size_t n_blk = (sizeof(ssn_inflate_block) * f->max_blocks + 63) & ~(size_t)63, n_st = (4 * (size_t)f->max_blocks + 63) & ~(size_t)63;
-    CUI(cudaMallocHost(&L.h_slab, n_in + n_out + n_blk + n_st));
-    CUI(cudaMalloc(&L.d_slab, n_in + n_out + n_blk + n_st + 64));
-    L.h_in = L.h_slab; L.h_out = L.h_in + n_in; L.h_blk = (ssn_inflate_block*)(L.h_out + n_out); L.h_status = (uint32_t*)(L.h_out + n_out + n_blk);
-    L.d_in = L.d_slab; L.d_out = L.d_in + n_in; L.d_blk = (ssn_inflate_block*)(L.d_out + n_out); L.d_status = (uint32_t*)(L.d_out + n_out + n_blk);
-    L.d_counter = (uint32_t*)(L.d_out + n_out + n_blk + n_st);
-    /* numerically lowest = highest priority is for the scoring streams; these take what is left */
-    int lo = 0, hi = 0;
-    CUI(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    CUI(cudaStreamCreateWithPriority(&L.stream, cudaStreamNonBlocking, lo));
-    CUI(cudaEventCreateWithFlags(&L.done, cudaEventBlockingSync | cudaEventDisableTiming));
-    memset(L.h_in, 0, n_in);
+    CUI(cudaMallocHost(&L.h_slab, f->in_stride + f->out_stride));
+    L.h_in = L.h_slab; L.h_out = L.h_slab + f->in_stride;
+    memset(L.h_in, 0, f->in_stride);
+    L.blk.resize(f->max_blocks);
     L.ready = true;
     return SSN_OK;
 }
@@ -141,7 +199,7 @@ extern "C" ssn_status ssn_inflater_lane_acquire(ssn_inflater *f, int32_t *lane, 
             for (size_t i = 0; i < f->lanes.size(); ++i) if (!f->lanes[i].busy && f->lanes[i].ready) { pick = (int)i; break; }   /* a warm one first */
             if (pick < 0) for (size_t i = 0; i < f->lanes.size(); ++i) if (!f->lanes[i].busy) { pick = (int)i; break; }
             if (pick >= 0) break;
-            f->cv.wait(lk);
+            f->cv_lane.wait(lk);
         }
         f->lanes[pick].busy = true;
     }
@@ -149,7 +207,7 @@ extern "C" ssn_status ssn_inflater_lane_acquire(ssn_inflater *f, int32_t *lane, 
     if (st != SSN_OK) {
         std::lock_guard<std::mutex> lk(f->mu);
         f->lanes[pick].busy = false;
-        f->cv.notify_one();
+        f->cv_lane.notify_one();
         return st;
     }
     *lane = pick; *in = f->lanes[pick].h_in; *out = f->lanes[pick].h_out;
@@ -161,7 +219,7 @@ extern "C" void ssn_inflater_lane_release(ssn_inflater *f, int32_t lane)
     if (!f || lane < 0 || (size_t)lane >= f->lanes.size()) return;
     std::lock_guard<std::mutex> lk(f->mu);
     f->lanes[lane].busy = false;
-    f->cv.notify_one();
+    f->cv_lane.notify_one();
 }
 
 extern "C" ssn_status ssn_inflater_limits(const ssn_inflater *f, uint64_t *in_cap, uint64_t *out_cap, uint32_t *max_blocks)
@@ -196,6 +254,98 @@ extern "C" void ssn_inflater_host_free(ssn_inflater *f, void *p)
     for (auto &h : f->host_bufs) if (h.p == p) { h.busy = false; return; }
 }
 
+/* stream callback (a driver thread; no CUDA calls here): the wave's copies back have landed */
+static void CUDART_CB wave_done(void *arg)
+{
+    Wave *w = (Wave*)arg;
+    ssn_inflater *f = w->f;
+    std::lock_guard<std::mutex> lk(f->mu);
+    uint32_t at = 0;
+    for (int li : w->lanes) {
+        Lane &L = f->lanes[li];
+        uint32_t bad = 0;
+        for (uint32_t i = 0; i < L.n; ++i) { L.refused[i] = w->h_status[at + i] != 0; bad += L.refused[i]; }
+        at += L.n;
+        f->blocks += L.n; f->refused += bad; f->runs += 1; f->in_bytes += L.in_bytes; f->out_bytes += L.out_bytes;
+        L.done = true;
+    }
+    f->launches += 1;
+    w->lanes.clear();
+    w->busy = false;
+    f->cv_done.notify_all();
+    f->cv_work.notify_all();
+}
+
+static cudaError_t wave_issue(ssn_inflater *f, Wave *w)
+{
+#define CUW(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return e_; } while (0)
+    cudaStream_t st = w->stream;
+    uint32_t at = 0;
+    for (int li : w->lanes) {
+        Lane &L = f->lanes[li];
+        const uint32_t base_in = (uint32_t)(f->in_stride * (uint64_t)li), base_out = (uint32_t)(f->out_stride * (uint64_t)li);
+        for (uint32_t i = 0; i < L.n; ++i) {
+            const ssn_inflate_block b = L.blk[i];
+            w->h_blk[at + i] = ssn_inflate_block{b.in_off + base_in, b.in_len, b.out_off + base_out, b.out_len};
+        }
+        CUW(cudaMemcpyAsync(f->d_in + base_in, L.h_in, ((size_t)L.in_bytes + 63) & ~(size_t)63, cudaMemcpyHostToDevice, st));
+        at += L.n;
+    }
+    CUW(cudaMemsetAsync(w->d_counter, 0, 4, st));
+    CUW(cudaMemcpyAsync(w->d_blk, w->h_blk, sizeof(ssn_inflate_block) * at, cudaMemcpyHostToDevice, st));
+    const uint32_t grid = std::min<uint32_t>((at + kInflWarps - 1) / kInflWarps, (uint32_t)f->num_sms * kInflCtasPerSm);
+    ssn_inflate_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), st>>>(f->d_in, w->d_blk, at, f->d_out, w->d_status, w->d_counter);
+    CUW(cudaGetLastError());
+    for (int li : w->lanes) {
+        Lane &L = f->lanes[li];
+        CUW(cudaMemcpyAsync(L.h_dst ? L.h_dst : L.h_out, f->d_out + f->out_stride * (uint64_t)li, (size_t)L.out_bytes, cudaMemcpyDeviceToHost, st));
+    }
+    CUW(cudaMemcpyAsync(w->h_status, w->d_status, 4 * (size_t)at, cudaMemcpyDeviceToHost, st));
+    CUW(cudaLaunchHostFunc(st, wave_done, w));
+#undef CUW
+    return cudaSuccess;
+}
+
+/* one thread per inflater: gathers the waiting requests into a wave and queues it; completion is the stream's callback */
+static void inflater_worker(ssn_inflater *f)
+{
+    cudaSetDevice(f->device);
+    int turn = 0;
+    for (;;) {
+        Wave *w = nullptr;
+        {
+            std::unique_lock<std::mutex> lk(f->mu);
+            for (;;) {
+                if (f->stop) return;
+                if (!f->pending.empty()) {
+                    for (int k = 0; k < kWaves && !w; ++k) { Wave &c = f->waves[(turn + k) % kWaves]; if (!c.busy) { w = &c; turn = (turn + k + 1) % kWaves; } }
+                    if (w) break;
+                }
+                f->cv_work.wait(lk);
+            }
+            uint32_t nb = 0;
+            size_t k = 0;
+            while (k < f->pending.size() && nb + f->lanes[f->pending[k]].n <= f->wave_blocks) { nb += f->lanes[f->pending[k]].n; ++k; }
+            w->lanes.assign(f->pending.begin(), f->pending.begin() + (long)k);
+            f->pending.erase(f->pending.begin(), f->pending.begin() + (long)k);
+            w->n = nb;
+            w->busy = true;
+        }
+        const cudaError_t e = wave_issue(f, w);
+        if (e != cudaSuccess) {
+            /* what was queued on the stream before the failure is waited for, then the wave's callers are told */
+            cudaStreamSynchronize(w->stream);
+            std::lock_guard<std::mutex> lk(f->mu);
+            if (w->busy) {                                   /* the callback did not run */
+                for (int li : w->lanes) { f->lanes[li].error = (int)e; f->lanes[li].done = true; }
+                w->lanes.clear();
+                w->busy = false;
+                f->cv_done.notify_all();
+            }
+        }
+    }
+}
+
 extern "C" ssn_status ssn_inflater_run(ssn_inflater *f, int32_t lane, const ssn_inflate_block *blk, uint32_t n, uint64_t in_bytes,
                                        uint64_t out_bytes, uint8_t *refused)
 {
@@ -212,25 +362,18 @@ extern "C" ssn_status ssn_inflater_run_to(ssn_inflater *f, int32_t lane, const s
     if (n == 0) return SSN_OK;
     for (uint32_t i = 0; i < n; ++i) {
         if ((uint64_t)blk[i].in_off + blk[i].in_len > in_bytes || (uint64_t)blk[i].out_off + blk[i].out_len > out_bytes) { ssn_set_error("ssn_inflater_run: block %u lies outside the batch", i); return SSN_ERR_ARG; }
-        L.h_blk[i] = blk[i];
+        L.blk[i] = blk[i];
     }
-    CUI(cudaSetDevice(f->device));
-    CUI(cudaMemsetAsync(L.d_counter, 0, 4, L.stream));
-    CUI(cudaMemcpyAsync(L.d_in, L.h_in, ((size_t)in_bytes + 63) & ~(size_t)63, cudaMemcpyHostToDevice, L.stream));
-    CUI(cudaMemcpyAsync(L.d_blk, L.h_blk, sizeof(ssn_inflate_block) * n, cudaMemcpyHostToDevice, L.stream));
-    const uint32_t grid = std::min<uint32_t>((n + kInflWarps - 1) / kInflWarps, (uint32_t)f->num_sms * kInflCtasPerSm);
-    ssn_inflate_kernel<<<grid, kInflWarps * 32, kInflWarps * sizeof(infl::Work), L.stream>>>(L.d_in, L.d_blk, n, L.d_out, L.d_status, L.d_counter);
-    CUI(cudaGetLastError());
-    CUI(cudaMemcpyAsync(h_dst ? h_dst : L.h_out, L.d_out, (size_t)out_bytes, cudaMemcpyDeviceToHost, L.stream));
-    CUI(cudaMemcpyAsync(L.h_status, L.d_status, 4 * (size_t)n, cudaMemcpyDeviceToHost, L.stream));
-    CUI(cudaEventRecord(L.done, L.stream));
-    CUI(cudaEventSynchronize(L.done));
-    uint32_t bad = 0;
-    for (uint32_t i = 0; i < n; ++i) { refused[i] = L.h_status[i] != 0; bad += refused[i]; }
+    L.n = n; L.in_bytes = in_bytes; L.out_bytes = out_bytes; L.refused = refused; L.h_dst = h_dst; L.error = 0;
     {
-        std::lock_guard<std::mutex> lk(f->mu);
-        f->blocks += n; f->refused += bad; f->runs += 1; f->in_bytes += in_bytes; f->out_bytes += out_bytes;
+        /* the caller sleeps until its wave has landed: its core goes to another reader */
+        std::unique_lock<std::mutex> lk(f->mu);
+        L.done = false;
+        f->pending.push_back(lane);
+        f->cv_work.notify_all();
+        f->cv_done.wait(lk, [&] { return L.done; });
     }
+    if (L.error) { ssn_set_error("ssn_inflater_run: %s", cudaGetErrorString((cudaError_t)L.error)); return SSN_ERR_CUDA; }
     return SSN_OK;
 }
 
