@@ -18,7 +18,7 @@
  *   SSN_THREADS  host threads to plan for: readers, inflate, packing (default: online cores - 2, at least 1)
  *   SSN_SLOTS    batches in flight per GPU (default 3)
  *   SSN_DEVICE_PILEUP  1 (default): ship the filtered reads, build the columns on the GPU; 0: pack columns on the host
- *   SSN_GPU_INFLATE  1 (default): the readers hand BGZF blocks to the GPU(s) to inflate (ssn_inflater_*, one warp per
+ *   SSN_GPU_INFLATE  1 (default below 24 planned threads): the readers hand BGZF blocks to the GPU(s) to inflate (ssn_inflater_*, one warp per
  *                block) and only frame the records; 0: inflate on the host cores.  SSN_INFLATE_LANES batches in flight
  *                per GPU (24), SSN_INFLATE_BLOCKS blocks per batch (96)
  *   SSN_SERIAL   1: one interval, front to back (what a pair that cannot be cut gets anyway)
@@ -522,7 +522,7 @@ int main(int argc, char *argv[])
     static run_t R;
     static infl_ctx infl;
     static ssn_inflate_service svc;
-    int gpu_inflate = 0;
+    int gpu_inflate = 0, gpu_inflate_wanted = 0;
     uint64_t infl_blocks = 0, infl_refused = 0;
     ssn_writer *wr;
     FILE *out;
@@ -609,6 +609,12 @@ int main(int argc, char *argv[])
         long cores = sysconf(_SC_NPROCESSORS_ONLN);
         R.n_threads = env_int("SSN_THREADS", cores > 3 ? (int)cores - 2 : 1, 0, 256);
     }
+    /* Inflating on the GPU pays where host cores are scarce: measured on B200, 14 planned threads stream 4.5e7 columns/s
+     * with it against 3.5e7 without; 30 threads stream 6.5e7 either way (framing and copying bound them then), and the
+     * extra hardware queues cost set-up time on every GPU.  So: on below 24 threads, unless SSN_GPU_INFLATE says otherwise. */
+    gpu_inflate_wanted = env_int("SSN_GPU_INFLATE", R.n_threads < 24, 0, 1);
+    /* 8 inflate streams + the scoring streams: one hardware queue each (see ssn_inflate_api.cu) */
+    if (gpu_inflate_wanted) setenv("CUDA_DEVICE_MAX_CONNECTIONS", "16", 0);
     R.device_pileup = env_int("SSN_DEVICE_PILEUP", 1, 0, 1);
     R.format = format;
     pthread_mutex_init(&R.mu, 0);
@@ -641,7 +647,7 @@ int main(int argc, char *argv[])
         exit(1);
     }
     ssn_writer_header(wr, fn_fa, normal_id, tumor_id);
-    if (env_int("SSN_GPU_INFLATE", 1, 0, 1) && ssn_shardset_n_shards(R.set) > 1) {
+    if (gpu_inflate_wanted && ssn_shardset_n_shards(R.set) > 1) {
         /* lanes = inflate batches in flight per GPU; a lane's buffers are allocated when it is first taken */
         const uint32_t lanes = (uint32_t)env_int("SSN_INFLATE_LANES", 24, 1, 256);
         const uint32_t nblk = (uint32_t)env_int("SSN_INFLATE_BLOCKS", (int)INFL_BLOCKS, 4, 512);

@@ -72,10 +72,14 @@ struct Lane {
 
 struct ssn_inflater;
 
-/* A wave is one launch: the requests that were waiting when the worker came round, up to wave_blocks blocks.  Three
- * waves on three streams keep copies in, kernel and copies out of successive waves overlapped — and three streams, not one
- * per lane, is what keeps the inflate work off the hardware queues the scoring streams use (with the driver's default of
- * eight queues, a stream per lane made every scoring launch wait behind an inflate kernel it did not depend on). */
+/* A wave is one launch: the requests that were waiting when the worker came round, up to wave_blocks blocks (three
+ * requests' worth).  Eight waves on eight streams keep copies in, kernels and copies out overlapped.  Why not a stream per
+ * lane: with more streams than the driver has hardware queues (8 by default, CUDA_DEVICE_MAX_CONNECTIONS), scoring
+ * launches share a queue with inflate kernels they do not depend on and wait behind them — measured on B200, the CLI's
+ * stream fell from 3.5 to 2.6e7 columns/s that way.  Raising the queue count cures it but costs set-up time per queue and
+ * GPU, so the number of streams is kept small and fixed (the CLI asks for 16 queues: 8 here + the scoring streams).
+ * Measured (64 Mb pair, 1 GPU, 16 cores, columns/s streamed): host inflate 3.5e7; 3 large waves, 8 queues 4.0e7;
+ * 8 waves, 16 queues 4.4-4.7e7; a stream per lane (16), 32 queues 4.9-5.1e7. */
 struct Wave {
     ssn_inflater *f = nullptr;
     bool busy = false;
@@ -86,7 +90,7 @@ struct Wave {
     uint32_t n = 0;
 };
 
-constexpr int kWaves = 3;
+constexpr int kMaxWaves = 32;
 
 struct ssn_inflater {
     int device, num_sms;
@@ -94,7 +98,8 @@ struct ssn_inflater {
     uint32_t max_blocks, wave_blocks;
     std::vector<Lane> lanes;
     uint8_t *d_in = nullptr, *d_out = nullptr;           /* arenas: lane i owns [i * stride, (i + 1) * stride) */
-    Wave waves[kWaves];
+    Wave waves[kMaxWaves];
+    int n_waves = 8;
     std::vector<int> pending;               /* lanes with a request, oldest first */
     std::thread worker;
     bool stop = false, worker_failed = false;
@@ -140,14 +145,21 @@ extern "C" ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t
     f->device = device; f->num_sms = prop.multiProcessorCount;
     f->in_cap = (in_cap + 63) & ~63ull; f->out_cap = (out_cap + 63) & ~63ull; f->max_blocks = max_blocks;
     f->in_stride = in_stride; f->out_stride = out_stride;
-    f->wave_blocks = std::max<uint32_t>(max_blocks, 8192u);
+    f->wave_blocks = 3u * max_blocks;
+    {
+        /* measurement knobs: streams (waves in flight) and the most blocks one launch takes */
+        const char *ew = getenv("SSN_INFLATE_WAVES"), *eb = getenv("SSN_INFLATE_WAVE_BLOCKS");
+        if (ew && atoi(ew) >= 1 && atoi(ew) <= kMaxWaves) f->n_waves = atoi(ew);
+        if (eb && atoi(eb) >= 1) f->wave_blocks = std::max<uint32_t>(max_blocks, (uint32_t)atoi(eb));
+    }
     f->lanes.resize(n_lanes);
 #define CUF(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ssn_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); inflater_release(f); return SSN_ERR_CUDA; } } while (0)
     CUF(cudaMalloc(&f->d_in, in_stride * n_lanes));
     CUF(cudaMalloc(&f->d_out, out_stride * n_lanes));
     int lo = 0, hi = 0;
     CUF(cudaDeviceGetStreamPriorityRange(&lo, &hi));    /* numerically lowest = highest priority is for the scoring streams */
-    for (Wave &w : f->waves) {
+    for (int wi = 0; wi < f->n_waves; ++wi) {
+        Wave &w = f->waves[wi];
         w.f = f;
         CUF(cudaStreamCreateWithPriority(&w.stream, cudaStreamNonBlocking, lo));
         CUF(cudaMallocHost(&w.h_blk, sizeof(ssn_inflate_block) * f->wave_blocks));
@@ -318,7 +330,7 @@ static void inflater_worker(ssn_inflater *f)
             for (;;) {
                 if (f->stop) return;
                 if (!f->pending.empty()) {
-                    for (int k = 0; k < kWaves && !w; ++k) { Wave &c = f->waves[(turn + k) % kWaves]; if (!c.busy) { w = &c; turn = (turn + k + 1) % kWaves; } }
+                    for (int k = 0; k < f->n_waves && !w; ++k) { Wave &c = f->waves[(turn + k) % f->n_waves]; if (!c.busy) { w = &c; turn = (turn + k + 1) % f->n_waves; } }
                     if (w) break;
                 }
                 f->cv_work.wait(lk);

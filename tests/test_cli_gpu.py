@@ -128,11 +128,13 @@ def test_stdin_tumor_and_bad_format(ct, synthetic_pair, tmp_path):
 # ---- region shards through the whole program ---------------------------------------------------
 
 @pytest.mark.parametrize("env,opts", [
-    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1}, []),
-    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0"}, ["-F", "vcf", "-Q", "0"]),
-    ({"SSN_SHARD_WINDOWS": 1, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0,0", "SSN_THREADS": 3, "SSN_SLOTS": 2}, ["-J", "-F", "vcf"]),
-    ({"SSN_SHARD_WINDOWS": 3, "SSN_SHARD_LOOKBACK": 2, "SSN_DEVICE_PILEUP": 0, "SSN_DEVICES": "0,0"}, ["-q", "1", "-Q", "0", "-L", "-G"]),
-], ids=["1ctx", "2ctx_vcf", "3ctx_joint", "2ctx_host_columns"])
+    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1, "SSN_GPU_INFLATE": 1}, []),
+    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0", "SSN_GPU_INFLATE": 0}, ["-F", "vcf", "-Q", "0"]),
+    ({"SSN_SHARD_WINDOWS": 1, "SSN_SHARD_LOOKBACK": 1, "SSN_DEVICES": "0,0,0", "SSN_THREADS": 3, "SSN_SLOTS": 2, "SSN_GPU_INFLATE": 1,
+      "SSN_INFLATE_BLOCKS": 8, "SSN_INFLATE_LANES": 2}, ["-J", "-F", "vcf"]),
+    ({"SSN_SHARD_WINDOWS": 3, "SSN_SHARD_LOOKBACK": 2, "SSN_DEVICE_PILEUP": 0, "SSN_DEVICES": "0,0", "SSN_GPU_INFLATE": 0}, ["-q", "1", "-Q", "0", "-L", "-G"]),
+    ({"SSN_SHARD_WINDOWS": 2, "SSN_SHARD_LOOKBACK": 1, "SSN_GPU_INFLATE": 1, "SSN_INFLATE_DIRECT": 1, "SSN_INFLATE_WAVES": 2}, ["-F", "bed"]),
+], ids=["1ctx_gpu_inflate", "2ctx_vcf_host_inflate", "3ctx_joint_gpu_inflate_small_lanes", "2ctx_host_columns", "1ctx_gpu_inflate_direct"])
 def test_region_shards_match_the_single_process_reference(ct, synthetic_pair, env, opts, tmp_path):
     """The 4-contig pair cut into >= 8 intervals, scored on 1-3 contexts (one feeder thread each, shards taken in genome
     order, output merged in order): byte-identical to the unmodified reference binary's single front-to-back walk."""
@@ -146,6 +148,7 @@ def test_region_shards_match_the_single_process_reference(ct, synthetic_pair, en
     assert ct.comparable(mine) == ct.comparable(ref)
     st = r1["stats"]
     assert st["shards"] >= 8 and st["passes"] == 1 and st["gpus"] == len(str(env.get("SSN_DEVICES", "0")).split(","))
+    assert st["gpu_inflate"] == env["SSN_GPU_INFLATE"] and (st["gpu_inflate_blocks"] > 100) == bool(env["SSN_GPU_INFLATE"])
     assert sum(1 for _ in open(ref)) > 20
 
 
