@@ -308,6 +308,7 @@ def bam_level(args):
             "wall_s": wall, "setup_s": st["setup_s"], "stream_s": st["wall_s"] - st["setup_s"], "columns_per_s_wall": st["columns"] / wall,
             "all_walls_s": [w for w, _ in runs], "bam_bytes": bam_bytes, "shards": st["shards"], "threads": st["threads"],
             "host_cores": os.cpu_count(), "gpus": args.gpus, "pack_wait_s": st["pack_wait_s"], "gpu_wait_s": st["gpu_wait_s"],
+            "gpu_inflate": st.get("gpu_inflate"), "gpu_inflate_blocks": st.get("gpu_inflate_blocks"), "gpu_inflate_refused": st.get("gpu_inflate_refused"),
             "generate_s": t_gen,
             "workload": "%d contigs x %d bp, tumor %gx / normal %gx, 150 bp reads, BGZF level 1 (tools/simbam_fast.c); classic output, "
                         "default options; file cache warm" % (args.bam_contigs, args.bam_len, args.depth_t, args.depth_n)}
