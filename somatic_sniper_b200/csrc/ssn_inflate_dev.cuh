@@ -355,19 +355,49 @@ INFL_FN uint32_t load_out(const uint8_t *p)
 #endif
 }
 
+/* some r with (i * r) >> 20 == i / dist for i, dist <= 258: any r in (2^20 / dist, 2^20 / dist + 2] does, since
+ * i * dist * 2 < 2^20 */
+INFL_FN uint32_t recip20(uint32_t dist)
+{
+#ifdef SSN_INFL_HOST
+    return ((1u << 20) + dist - 1u) / dist;
+#else
+    return (uint32_t)(__frcp_ru((float)dist) * 1048576.0f) + 1u;       /* rounded up, times 2^20 exactly, truncated, + 1 */
+#endif
+}
+
 INFL_FN void out_match(Out &o, uint32_t length, uint32_t dist)    /* caller checked dist <= pos, pos + length <= len */
 {
     out_settle(o);
     uint8_t *dst = o.p + o.pos;
-    if (dist >= length) {
+    if (length <= 32u) {
+        /* Nearly every match of a level-1 BAM (19 turns of the symbol loop in 20 are matches, 8 bytes each on average):
+         * one predicated load and store, no loop. */
+        if (dist >= length) {
+            INFL_LANES(lane) { if ((uint32_t)lane < length) dst[lane] = (uint8_t)load_out(dst + lane - dist); }
+        } else if (dist == 1u) {                                      /* a run of one byte (qualities) */
+            INFL_LANES(lane) { if ((uint32_t)lane < length) dst[lane] = (uint8_t)load_out(dst - 1); }
+        } else {
+            const uint32_t recip = recip20(dist);
+            INFL_LANES(lane) {
+                if ((uint32_t)lane < length) { const uint32_t q = ((uint32_t)lane * recip) >> 20; dst[lane] = (uint8_t)load_out(dst - dist + ((uint32_t)lane - q * dist)); }
+            }
+        }
+    } else if (dist >= length) {
+#ifndef SSN_INFL_HOST
+#pragma unroll 1
+#endif
         for (uint32_t base = 0; base < length; base += 32u) {
             INFL_LANES(lane) { const uint32_t i = base + (uint32_t)lane; if (i < length) dst[i] = (uint8_t)load_out(dst + i - dist); }
         }
     } else {
         /* the copy overlaps itself: byte i repeats byte i mod dist of the `dist` bytes in front of the match, all of
-         * which are in memory already (i <= 257, dist <= 257: i * dist < 2^20, so the reciprocal is exact) */
-        const uint32_t recip = ((1u << 20) + dist - 1u) / dist;
+         * which are in memory already */
+        const uint32_t recip = recip20(dist);
         const uint8_t *src = dst - dist;
+#ifndef SSN_INFL_HOST
+#pragma unroll 1
+#endif
         for (uint32_t base = 0; base < length; base += 32u) {
             INFL_LANES(lane) {
                 const uint32_t i = base + (uint32_t)lane;
