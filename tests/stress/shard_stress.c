@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include "ssn_host.h"
 
 #define BATCH_COLUMNS (16u << 13)
@@ -13,6 +14,8 @@
 static ssn_shardset *set;
 static unsigned long long g_windows, g_reads;
 static pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+
+static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return (double)t.tv_sec + 1e-9 * (double)t.tv_nsec; }
 
 static void *consumer(void *arg)
 {
@@ -59,9 +62,16 @@ int main(int argc, char **argv)
         if (argc > 7) o.stride_windows = (uint32_t)atoi(argv[7]);
         if (ssn_shardset_open(argv[1], argv[2], argv[3], 0, &o, &set) != SSN_OK) { fprintf(stderr, "open: %s\n", ssn_host_last_error()); return 2; }
         g_windows = g_reads = 0;
+        const double t0 = now_s();
         for (i = 0; i < consumers; ++i) pthread_create(&th[i], 0, consumer, 0);
         for (i = 0; i < consumers; ++i) pthread_join(th[i], 0);
-        printf("repeat %d: shards %d windows %llu reads %llu long_span %d\n", r, (int)ssn_shardset_n_shards(set), g_windows, g_reads, ssn_shardset_long_span(set));
+        {
+            const double dt = now_s() - t0;
+            ssn_packer_stats ps;
+            ssn_shardset_get_stats(set, &ps);
+            printf("repeat %d: shards %d windows %llu reads %llu long_span %d  %.3f s, %.3g positions/s (wait %.2f s, fill %.2f s)\n", r,
+                   (int)ssn_shardset_n_shards(set), g_windows, g_reads, ssn_shardset_long_span(set), dt, (double)g_windows * SSN_READ_WINDOW / dt, ps.t_wait, ps.t_fill);
+        }
         if (r == 0) { first_w = g_windows; first_r = g_reads; }
         else if (g_windows != first_w || g_reads != first_r) { fprintf(stderr, "run %d differs from run 0\n", r); return 3; }
         ssn_shardset_close(set);
