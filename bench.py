@@ -161,6 +161,31 @@ def dist_setup(n, backend="nccl"):
     return dist, rank, local
 
 
+def bind_near_gpu(local):
+    """N > 1: keep this rank (and so the first touch of its pinned batches) on the CPUs of the NUMA node its GPU hangs off.
+    Round 1's scaling run lost half of e2e at N = 8 to the host side of eight concurrent pinned H2D streams; where the box
+    has several nodes this keeps each stream's source memory local.  A no-op on a one-node box or when sysfs says nothing."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bdf) as f:
+            txt = f.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if part:
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        have = os.sched_getaffinity(0)
+        want = cpus & have
+        if want and want != have:
+            os.sched_setaffinity(0, want)
+            return "GPU %s: bound to its node's CPUs %s (%d of %d)" % (bdf, txt, len(want), len(have))
+        return "GPU %s: local CPUs %s = every CPU of this process, nothing to bind" % (bdf, txt or "?")
+    except Exception as e:              # no sysfs entry, no such property: run unbound
+        return "unbound (%s)" % type(e).__name__
+
+
 def _dist_device(dist):
     return "cuda" if dist.get_backend() == "nccl" else "cpu"
 
@@ -317,6 +342,7 @@ def bam_level(args):
 def run_b200(args):
     from somatic_sniper_b200 import api, synth
     dist, rank, local = dist_setup(args.gpus, args.backend)
+    binding = bind_near_gpu(local) if args.gpus > 1 and args.backend == "nccl" else "single rank, unbound"
     ncol = args.columns
     cols = synth.make_columns(ncol, depth_t=args.depth_t, depth_n=args.depth_n, seed=shard_seed(rank))
     nent = int(cols["n_entries"])
@@ -592,7 +618,7 @@ def run_b200(args):
                     "prefilter": "exact hom-reference pre-filter on; %d of %d columns go on to the full model" % (survivors, ncol)
                                  if filtered else "off",
                     "resident_batches_in_flight": STREAMS, "parallelism": "region shards, %d GPU(s), no collective" % args.gpus,
-                    "timed_region_repeats": REPEATS, "ms_per_step_each_repeat": [m / args.steps for m in rep_ms],
+                    "cpu_binding": binding, "timed_region_repeats": REPEATS, "ms_per_step_each_repeat": [m / args.steps for m in rep_ms],
                     "value_spread": (max(rep_ms) - min(rep_ms)) / ms},
             "clocks": sampler.summary(),
             "gpu_launches": int(launches),
