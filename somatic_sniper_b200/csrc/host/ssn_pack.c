@@ -528,8 +528,13 @@ static int g_stream_copy = -1;
 static void copy_streaming(uint8_t *dst, const uint8_t *src, size_t n)
 {
     size_t head;
-    if (g_stream_copy < 0) { const char *e = getenv("SSN_STREAM_COPY"); g_stream_copy = e && *e ? atoi(e) != 0 : 1; }   /* measurement knob */
-    if (!g_stream_copy || n < 4096) { memcpy(dst, src, n); return; }
+    int on = __atomic_load_n(&g_stream_copy, __ATOMIC_RELAXED);           /* several pool workers get here at once */
+    if (on < 0) {
+        const char *e = getenv("SSN_STREAM_COPY");                       /* measurement knob */
+        on = e && *e ? atoi(e) != 0 : 1;
+        __atomic_store_n(&g_stream_copy, on, __ATOMIC_RELAXED);
+    }
+    if (!on || n < 4096) { memcpy(dst, src, n); return; }
     head = (size_t)(-(uintptr_t)dst & 15u);
     memcpy(dst, src, head); dst += head; src += head; n -= head;
     for (; n >= 64; n -= 64, dst += 64, src += 64) {
