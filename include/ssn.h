@@ -244,10 +244,12 @@ ssn_status ssn_pileup_time(ssn_ctx *ctx, float *total_ms, uint64_t *n_batches, i
 /* ---- BGZF blocks inflated on the device ------------------------------------------------------------------------
  * Replaces, for the BAM readers, the per-block inflateInit2 / inflate / inflateEnd of samtools-0.1.6 bgzf.c:330-353
  * (under bgzf_read :489 and bam_read1, bam.c:181-212): one warp per block (csrc/ssn_inflate_dev.cuh).  A reader thread
- * acquires a LANE (pinned input and output buffers, a stream), lays the deflate payloads of up to max_blocks blocks into
- * the input buffer back to back, describes them, and calls ssn_inflater_run: synchronous for the caller, no CPU while it
- * waits; thread-safe, one lane per calling thread at a time.  refused[i] = 1 marks a block the device decoder gave up on
- * (nothing usable at its out_off): the caller inflates it on the host, so the service never changes what is read. */
+ * acquires a LANE (pinned input and output buffers), lays the deflate payloads of up to max_blocks blocks into the input
+ * buffer back to back, describes them, and calls ssn_inflater_run: synchronous for the caller, no CPU while it waits;
+ * thread-safe, one lane per calling thread at a time.  Behind the call the requests of all threads waiting at that moment
+ * go to the device together (one launch over all their blocks, csrc/ssn_inflate_api.cu).  refused[i] = 1 marks a block
+ * the device decoder gave up on (nothing usable at its out_off): the caller inflates it on the host, so the service
+ * never changes what is read. */
 typedef struct { uint32_t in_off, in_len, out_off, out_len; } ssn_inflate_block;
 typedef struct ssn_inflater ssn_inflater;
 ssn_status ssn_inflater_create(int device, uint32_t n_lanes, uint64_t in_cap, uint64_t out_cap, uint32_t max_blocks, ssn_inflater **out);
