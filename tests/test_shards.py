@@ -337,12 +337,13 @@ def test_several_consumers_take_distinct_shards(host, big_pair):
     assert one == four and sum(c for c, _ in one.values()) > 100000
 
 
-@pytest.mark.parametrize("direct", [0, 1])
+@pytest.mark.parametrize("direct", [0, 1, 2])
 def test_readers_through_an_inflate_service(host, big_pair, direct):
     """The readers' GPU-inflate plumbing without a GPU: a service whose `run` decodes every block with the DEVICE decoder's
     source compiled for the host (ssn_inflate_dev_host) and refuses every seventh block (the reader must then inflate that
     one itself).  Lanes are handed out and given back; the columns equal the host-inflate run's.  direct = 1: the service
-    also offers host_alloc / host_free / run_to, so the readers own their output buffers and the service writes there."""
+    also offers host_alloc / host_free / run_to, so the readers own their output buffers and the service writes there.
+    direct = 2: lanes whose input buffer holds 70 000 bytes, so a batch ends where the next payload would not fit."""
     import threading
     from somatic_sniper_b200 import api
     p = big_pair
@@ -376,7 +377,7 @@ def test_readers_through_an_inflate_service(host, big_pair, direct):
                 if not L["busy"]:
                     L["busy"] = True
                     stats["acquired"] += 1
-                    pin[0] = L["i"].ctypes.data; pin_cap[0] = MAXB * 65600
+                    pin[0] = L["i"].ctypes.data; pin_cap[0] = 70000 if direct == 2 else MAXB * 65600
                     pout[0] = L["o"].ctypes.data; pout_cap[0] = MAXB * 65536
                     pmax[0] = MAXB
                     return k
@@ -403,6 +404,10 @@ def test_readers_through_an_inflate_service(host, big_pair, direct):
 
     def run(ctx, k, blk, n, in_bytes, out_bytes, refused, dst=None):
         L = lanes[k]
+        if direct == 2:
+            assert in_bytes <= 70000
+            with lock:
+                stats["runs"] = stats.get("runs", 0) + 1
         out_base = dst if dst else L["o"].ctypes.data
         if dst:
             assert dst in owned
@@ -422,7 +427,7 @@ def test_readers_through_an_inflate_service(host, big_pair, direct):
             refused[j] = 1 if rc else 0
         return 0
 
-    if direct:
+    if direct == 1:
         svc = Service(None, ACQ(acquire), REL(release), RUN(run), ALLOC(host_alloc), FREE(host_free), RUNTO(run))
     else:
         svc = Service(None, ACQ(acquire), REL(release), RUN(run), ALLOC(), FREE(), RUNTO())
@@ -439,5 +444,7 @@ def test_readers_through_an_inflate_service(host, big_pair, direct):
     pk.close()
     assert got == want
     assert stats["blocks"] > 200 and stats["refused"] > 20 and stats["acquired"] == stats["released"] > 10
-    if direct:
+    if direct == 2:
+        assert stats["runs"] * 8 > stats["blocks"]           # a handful of blocks per run, not 24
+    if direct == 1:
         assert stats["allocs"] >= 2 and stats["direct_runs"] > 10 and not owned      # every buffer came back
